@@ -1,0 +1,141 @@
+#!/usr/bin/env python3
+"""TEST INFRASTRUCTURE ONLY — builds oracle/_ref/libsiril_ref.so from the *reference's own
+sources where they lie* under /root/reference (never copied into the repo).
+
+Two kinds of input:
+  * whole, unmodified translation units compiled with shim headers
+    (oracle/shim precedes the reference include path):
+        src/stacking/rejection_float.c, src/stacking/siril_fit_linear.c,
+        src/algos/sorting.c, src/rt/rt_algo.cc
+  * line ranges of TUs that are too entangled with glib/cfitsio/opencv to compile
+    whole; they are extracted at build time into oracle/_ref/gen/*.inc (git-ignored)
+    and #included by oracle/ref_driver.c.  Each range is pinned by SHA-256 so that a
+    changed reference fails loudly instead of silently extracting the wrong lines.
+
+Outputs go only to oracle/_ref/ (git-ignored, NOT gpurun-ignored: the .so travels to the
+GPU box, /root/reference does not).
+
+Usage: python oracle/build_ref.py [--update-hashes]
+"""
+import hashlib
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("SIRIL_REFERENCE", "/root/reference")
+OUT = os.path.join(HERE, "_ref")
+GEN = os.path.join(OUT, "gen")
+
+# name -> (reference file, first line, last line, sha256 of the extracted text)
+RANGES = {
+    # --- shim content (types / macros / inlines whose exact text matters) ---
+    "siril_h_macros":    ("src/core/siril.h", 60, 81, None),
+    "siril_h_consts":    ("src/core/siril.h", 88, 99, None),
+    "siril_h_threading": ("src/core/siril.h", 359, 363, None),
+    "siril_h_imstats":   ("src/core/siril.h", 406, 424, None),
+    "settings_enums":    ("src/core/settings.h", 24, 52, None),
+    "proto_round_to_int":   ("src/core/proto.h", 208, 213, None),
+    "proto_round_to_WORD":  ("src/core/proto.h", 232, 237, None),
+    "proto_ceil_multiple":  ("src/core/proto.h", 295, 299, None),
+    "proto_truncate_WORD":  ("src/core/proto.h", 324, 328, None),
+    "proto_roundf_to_WORD": ("src/core/proto.h", 341, 346, None),
+    "proto_set_float_in_interval": ("src/core/proto.h", 384, 388, None),
+    "proto_double_ushort_to_float": ("src/core/proto.h", 418, 420, None),
+    # --- hot-path code ranges ---
+    "mm_planner":        ("src/stacking/median_and_mean.c", 261, 356, None),
+    "mm_norm01":         ("src/stacking/median_and_mean.c", 557, 582, None),
+    "mm_rejection_u16":  ("src/stacking/median_and_mean.c", 590, 1101, None),
+    "mm_noise_weights":  ("src/stacking/median_and_mean.c", 1111, 1135, None),
+    "mm_linfit_precalc": ("src/stacking/median_and_mean.c", 1491, 1499, None),
+    "stats_u16_sd_mad":  ("src/algos/statistics.c", 100, 154, None),
+    "statsf_mad_bwmv":   ("src/algos/statistics_float.c", 79, 127, None),
+    "statsf_ikss":       ("src/algos/statistics_float.c", 199, 229, None),
+    "quant_defs":        ("src/algos/quantize.c", 38, 39, None),
+    "quant_meansigma":   ("src/algos/quantize.c", 207, 317, None),
+    "quant_diffmeansigma": ("src/algos/quantize.c", 327, 422, None),
+    "quant_noise1":      ("src/algos/quantize.c", 1202, 1501, None),
+    "norm_factors":      ("src/stacking/normalization.c", 144, 181, None),
+}
+
+HASHES_FILE = os.path.join(HERE, "ref_ranges.sha256")
+
+WHOLE_TUS = [
+    ("src/stacking/rejection_float.c", "gcc"),
+    ("src/stacking/siril_fit_linear.c", "gcc"),
+    ("src/algos/sorting.c", "gcc"),
+    ("src/rt/rt_algo.cc", "g++"),
+]
+
+# reference default build class: debugoptimized (-O2) + -fno-math-errno (meson.build:36,159)
+CFLAGS = ["-O2", "-fopenmp", "-fno-math-errno", "-fPIC", "-w"]
+
+
+def load_hashes():
+    h = {}
+    if os.path.exists(HASHES_FILE):
+        for line in open(HASHES_FILE):
+            line = line.strip()
+            if line and not line.startswith("#"):
+                name, digest = line.split()
+                h[name] = digest
+    return h
+
+
+def extract(update):
+    os.makedirs(GEN, exist_ok=True)
+    pinned = load_hashes()
+    new = {}
+    for name, (rel, a, b, _) in RANGES.items():
+        path = os.path.join(REF, rel)
+        with open(path, "r", encoding="utf-8") as f:
+            lines = f.readlines()
+        text = "".join(lines[a - 1:b])
+        digest = hashlib.sha256(text.encode()).hexdigest()
+        new[name] = digest
+        if not update and name in pinned and pinned[name] != digest:
+            raise SystemExit(f"reference range {name} ({rel}:{a}-{b}) changed: sha256 mismatch")
+        with open(os.path.join(GEN, name + ".inc"), "w") as f:
+            f.write(f"/* generated from {rel}:{a}-{b} (reference, not committed) */\n")
+            f.write(text)
+    if update or not pinned:
+        with open(HASHES_FILE, "w") as f:
+            f.write("# sha256 of the reference line ranges build_ref.py extracts (lock042/siril @ a5869d93)\n")
+            for name in RANGES:
+                f.write(f"{name} {new[name]}\n")
+    # proto inlines are concatenated into one include
+    with open(os.path.join(GEN, "proto_inlines.inc"), "w") as f:
+        for name in RANGES:
+            if name.startswith("proto_"):
+                f.write(open(os.path.join(GEN, name + ".inc")).read() + "\n")
+
+
+def run(cmd):
+    print(" ".join(cmd))
+    subprocess.check_call(cmd)
+
+
+def build():
+    inc = ["-I" + os.path.join(HERE, "shim"), "-I" + OUT, "-I" + os.path.join(REF, "src")]
+    objs = []
+    for rel, cc in WHOLE_TUS:
+        obj = os.path.join(OUT, os.path.basename(rel).rsplit(".", 1)[0] + ".o")
+        run([cc] + CFLAGS + inc + ["-c", os.path.join(REF, rel), "-o", obj])
+        objs.append(obj)
+    drv = os.path.join(OUT, "ref_driver.o")
+    run(["gcc"] + CFLAGS + inc + ["-c", os.path.join(HERE, "ref_driver.c"), "-o", drv])
+    objs.append(drv)
+    run(["g++", "-shared", "-fopenmp", "-o", os.path.join(OUT, "libsiril_ref.so")] + objs + ["-lm"])
+
+
+def main():
+    if not os.path.isdir(REF):
+        print(f"{REF} not present: keeping prebuilt oracle/_ref as is")
+        return 0
+    extract("--update-hashes" in sys.argv)
+    build()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
