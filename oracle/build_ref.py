@@ -67,8 +67,20 @@ WHOLE_TUS = [
     ("src/rt/rt_algo.cc", "g++"),
 ]
 
-# reference default build class: debugoptimized (-O2) + -fno-math-errno (meson.build:36,159)
-CFLAGS = ["-O2", "-fopenmp", "-fno-math-errno", "-fPIC", "-w"]
+# reference default build class: debugoptimized (-O2) + -fno-math-errno (meson.build:36,159).
+# Two variants are built:
+#  libsiril_ref.so      "pinned order": the reference TUs are compiled WITHOUT -fopenmp.  The
+#      reference marks four per-stack reductions `#pragma omp simd reduction(+)`
+#      (statistics.h:94-102, rejection_float.c:270, median_and_mean.c:1026,1087), which makes
+#      their summation ORDER compiler- and ISA-defined (last double ulp of a sum, last float ulp
+#      of the linear-fit sigma).  Parity is pinned on the one order the C abstract machine
+#      defines — the sequential one, which is also what the reference's own scalar branches
+#      (N < 16 / N < 24) and any non-OpenMP build produce.  Row-block threading comes from
+#      ref_omp.c, the only TU compiled with -fopenmp.
+#  libsiril_ref_fast.so  everything with -fopenmp as the reference's meson build does; used only
+#      as the TIMED CPU baseline (bench.py), never for parity.
+BASE = ["-O2", "-fno-math-errno", "-fPIC", "-w"]
+VARIANTS = {"libsiril_ref.so": [], "libsiril_ref_fast.so": ["-fopenmp"]}
 
 
 def load_hashes():
@@ -117,15 +129,19 @@ def run(cmd):
 
 def build():
     inc = ["-I" + os.path.join(HERE, "shim"), "-I" + OUT, "-I" + os.path.join(REF, "src")]
-    objs = []
-    for rel, cc in WHOLE_TUS:
-        obj = os.path.join(OUT, os.path.basename(rel).rsplit(".", 1)[0] + ".o")
-        run([cc] + CFLAGS + inc + ["-c", os.path.join(REF, rel), "-o", obj])
-        objs.append(obj)
-    drv = os.path.join(OUT, "ref_driver.o")
-    run(["gcc"] + CFLAGS + inc + ["-c", os.path.join(HERE, "ref_driver.c"), "-o", drv])
-    objs.append(drv)
-    run(["g++", "-shared", "-fopenmp", "-o", os.path.join(OUT, "libsiril_ref.so")] + objs + ["-lm"])
+    for so, extra in VARIANTS.items():
+        odir = os.path.join(OUT, "obj_" + so.split(".")[0])
+        os.makedirs(odir, exist_ok=True)
+        objs = []
+        for rel, cc in WHOLE_TUS:
+            obj = os.path.join(odir, os.path.basename(rel).rsplit(".", 1)[0] + ".o")
+            run([cc] + BASE + extra + inc + ["-c", os.path.join(REF, rel), "-o", obj])
+            objs.append(obj)
+        drv = os.path.join(odir, "ref_driver.o")
+        run(["gcc"] + BASE + extra + inc + ["-c", os.path.join(HERE, "ref_driver.c"), "-o", drv])
+        omp = os.path.join(odir, "ref_omp.o")
+        run(["gcc"] + BASE + ["-fopenmp", "-c", os.path.join(HERE, "ref_omp.c"), "-o", omp])
+        run(["g++", "-shared", "-fopenmp", "-o", os.path.join(OUT, so)] + objs + [drv, omp, "-lm"])
 
 
 def main():

@@ -128,33 +128,29 @@ typedef struct {
  * [C][H][W] in the same order (the reference reads rows top-down and writes them back
  * bottom-up, :1597 — a wash in memory order).  y-shifts are what stack_read_block_data
  * (:407-448) applies at read time, x-shifts as :1617-1636. */
-int ref_stack(const ref_stack_params *p, const void *frames, void *out,
-		WORD *rej_low, WORD *rej_high, uint64_t irej[6]) {
+typedef struct {
+	const ref_stack_params *p; const void *frames; void *out; WORD *rej_low, *rej_high;
+	struct _image_block *blocks; struct _data_block *pool; struct stacking_args *args;
+	uint64_t *brej;	/* [nb_blocks][2] */
+} ref_stack_ctx;
+
+/* provided by ref_omp.c (the only TU of the pinned build compiled with -fopenmp): the
+ * reference's `omp parallel for schedule(dynamic)` over blocks (median_and_mean.c:1552) */
+void ref_parallel_for(int n, int nthreads, void (*fn)(int, int, void *), void *ctx);
+
+static void ref_stack_block(int b, int tid, void *vctx) {
+	ref_stack_ctx *cx = vctx;
+	const ref_stack_params *p = cx->p;
+	const void *frames = cx->frames; void *out = cx->out;
+	WORD *rej_low = cx->rej_low, *rej_high = cx->rej_high;
+	struct stacking_args *args = cx->args;
 	const int N = p->N, C = p->C;
 	const long H = p->H, W = p->W;
-	long naxes[3] = { W, H, C };
-	struct _image_block *blocks = NULL;
-	long largest; int nb_blocks;
-	int nthreads = p->nthreads > 0 ? p->nthreads : 1;
-	long max_rows = p->max_rows > 0 ? p->max_rows : H * C;
-	if (stack_compute_parallel_blocks(&blocks, max_rows, naxes, nthreads, &largest, &nb_blocks))
-		return -1;
-	struct _data_block *pool = calloc(nthreads, sizeof(*pool));
-	for (int t = 0; t < nthreads; t++) setup_block(&pool[t], p->is_float, N, p->rejtype);
-	struct stacking_args args;
-	setup_args(&args, N, p->rejtype, p->sig[0], p->sig[1], p->crit, p->weights);
-	memset(irej, 0, 6 * sizeof(uint64_t));
 	const size_t plane = (size_t) H * W;
 	const data_type itype = p->is_float ? DATA_FLOAT : DATA_USHORT;
-
-#pragma omp parallel for num_threads(nthreads) schedule(dynamic)
-	for (int b = 0; b < nb_blocks; b++) {
-		struct _image_block *blk = blocks + b;
-		int tid = 0;
-#ifdef _OPENMP
-		tid = omp_get_thread_num();
-#endif
-		struct _data_block *data = &pool[tid];
+	{
+		struct _image_block *blk = cx->blocks + b;
+		struct _data_block *data = &cx->pool[tid];
 		const int layer = (int) blk->channel;
 		data->layer = layer;
 		uint64_t brej[2] = { 0, 0 };
@@ -211,7 +207,7 @@ int ref_stack(const ref_stack_params *p, const void *frames, void *out,
 				const size_t o = (size_t) layer * plane + (size_t) r * W + x;
 				if (p->is_mean) {
 					int rej[2] = { 0, 0 };
-					result = mean_and_reject(&args, data, N, itype, rej);
+					result = mean_and_reject(args, data, N, itype, rej);
 					brej[0] += rej[0]; brej[1] += rej[1];
 					if (p->create_rejmaps) {
 						if (p->merge_rejmaps) rej_low[o] = truncate_to_WORD(rej[0] + rej[1]);
@@ -233,13 +229,35 @@ int ref_stack(const ref_stack_params *p, const void *frames, void *out,
 				}
 			}
 		}
-		if (p->is_mean && p->rejtype != NO_REJEC) {
-#pragma omp atomic
-			irej[layer * 2 + 0] += brej[0];
-#pragma omp atomic
-			irej[layer * 2 + 1] += brej[1];
-		}
+		cx->brej[2 * b] = brej[0]; cx->brej[2 * b + 1] = brej[1];
 	}
+}
+
+int ref_stack(const ref_stack_params *p, const void *frames, void *out,
+		WORD *rej_low, WORD *rej_high, uint64_t irej[6]) {
+	const int N = p->N, C = p->C;
+	const long H = p->H, W = p->W;
+	long naxes[3] = { W, H, C };
+	struct _image_block *blocks = NULL;
+	long largest; int nb_blocks;
+	int nthreads = p->nthreads > 0 ? p->nthreads : 1;
+	long max_rows = p->max_rows > 0 ? p->max_rows : H * C;
+	if (stack_compute_parallel_blocks(&blocks, max_rows, naxes, nthreads, &largest, &nb_blocks))
+		return -1;
+	struct _data_block *pool = calloc(nthreads, sizeof(*pool));
+	for (int t = 0; t < nthreads; t++) setup_block(&pool[t], p->is_float, N, p->rejtype);
+	struct stacking_args args;
+	setup_args(&args, N, p->rejtype, p->sig[0], p->sig[1], p->crit, p->weights);
+	memset(irej, 0, 6 * sizeof(uint64_t));
+	ref_stack_ctx cx = { p, frames, out, rej_low, rej_high, blocks, pool, &args,
+		calloc(2 * (size_t) nb_blocks, sizeof(uint64_t)) };
+	ref_parallel_for(nb_blocks, nthreads, ref_stack_block, &cx);
+	if (p->is_mean && p->rejtype != NO_REJEC)
+		for (int b = 0; b < nb_blocks; b++) {
+			irej[blocks[b].channel * 2 + 0] += cx.brej[2 * b];
+			irej[blocks[b].channel * 2 + 1] += cx.brej[2 * b + 1];
+		}
+	free(cx.brej);
 	if (p->use_32bit_output && p->output_norm) {
 		fits fit; memset(&fit, 0, sizeof(fit));
 		fit.naxes[0] = W; fit.naxes[1] = H; fit.naxes[2] = C; fit.fdata = (float *) out;
