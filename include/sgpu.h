@@ -1,0 +1,177 @@
+/*
+ * sgpu.h — C ABI of the B200 (sm_100a) rejection-stacking module.
+ *
+ * This is the drop-in boundary for ONE hot path of Siril (lock042/siril @ a5869d93): the
+ * per-pixel mean-with-rejection / median combine with normalization and weighting, i.e. what
+ * `args->method(args)` (stack_mean_with_rejection / stack_median, src/stacking/stacking.c:104,
+ * src/stacking/median_and_mean.c:1103-1109) and do_normalization (src/stacking/normalization.c:46)
+ * compute.  Plain C: pointers and sizes only, no glib, no torch, no C++ types.  Siril's glue
+ * (integration/siril/src/gpu/gpu_stack.c) and the Python harness both bind
+ * exactly these entry points.
+ *
+ * Conventions
+ *  - every function returns an ST_* code of the reference (src/stacking/stacking.h:18-24):
+ *      SGPU_OK 0, SGPU_GENERIC_ERROR -1, SGPU_SEQUENCE_ERROR -2, SGPU_CANCEL -9, SGPU_ALLOC_ERROR -10
+ *    and never throws; sgpu_last_error() gives the text.
+ *  - enum values are the reference's (src/core/settings.h:34-53, src/stacking/stacking.h:46-52).
+ *  - images are in MEMORY order as Siril holds them (fits.fdata / fits.data: FITS, bottom-up
+ *    rows), planes [layer][row][col].  A "block" is what data->pix[frame] is in the reference
+ *    (src/stacking/median_and_mean.c:382-545): for every frame, the rows [row0, row0+height) of
+ *    every layer with the frame's integer y-shift already applied at load time and zero fill
+ *    outside the frame; layout [frame][layer][row][col] ("frame-major"), resident in HBM.
+ *  - coefficient / weight arrays are [layer * nb_frames + frame] doubles, the layout of
+ *    coeff.pscale[layer][frame] / weights (normalization.c:81-96, median_and_mean.c:1115-1120).
+ *  - there is no CPU fallback: without a CUDA device every compute entry point fails with
+ *    SGPU_GENERIC_ERROR.
+ */
+#ifndef SGPU_H
+#define SGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGPU_ABI_VERSION 1
+
+enum {	/* stacking.h:18-24 */
+	SGPU_OK = 0,
+	SGPU_GENERIC_ERROR = -1,
+	SGPU_SEQUENCE_ERROR = -2,
+	SGPU_CANCEL = -9,
+	SGPU_ALLOC_ERROR = -10
+};
+
+enum { SGPU_U16 = 0, SGPU_F32 = 1 };	/* data_type: DATA_USHORT, DATA_FLOAT */
+
+enum {	/* rejection, settings.h:43-52 */
+	SGPU_NO_REJEC = 0, SGPU_PERCENTILE, SGPU_SIGMA, SGPU_MAD, SGPU_SIGMEDIAN,
+	SGPU_WINSORIZED, SGPU_LINEARFIT, SGPU_GESDT
+};
+
+enum {	/* normalization, settings.h:34-40 */
+	SGPU_NO_NORM = 0, SGPU_ADDITIVE, SGPU_MULTIPLICATIVE, SGPU_ADDITIVE_SCALING,
+	SGPU_MULTIPLICATIVE_SCALING
+};
+
+enum {	/* weightingType, stacking.h:46-52 */
+	SGPU_NO_WEIGHT = 0, SGPU_NBSTARS_WEIGHT, SGPU_WFWHM_WEIGHT, SGPU_NOISE_WEIGHT, SGPU_NBSTACK_WEIGHT
+};
+
+typedef struct sgpu_ctx sgpu_ctx;
+typedef struct sgpu_block sgpu_block;
+
+/* ---- context -------------------------------------------------------------------------------- */
+int sgpu_abi_version(void);
+/* one context per GPU / per process rank; `device` is the CUDA ordinal */
+int sgpu_ctx_create(int device, sgpu_ctx **ctx);
+void sgpu_ctx_destroy(sgpu_ctx *ctx);
+/* run all work of this context on a caller-owned cudaStream_t (NULL: the context's own stream) */
+int sgpu_ctx_set_stream(sgpu_ctx *ctx, void *cuda_stream);
+int sgpu_ctx_synchronize(sgpu_ctx *ctx);
+const char *sgpu_last_error(const sgpu_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t sgpu_launch_count(const sgpu_ctx *ctx);
+/* cooperative cancel: polled between row-block launches like processing_should_continue()
+ * (median_and_mean.c:1563); return non-zero from the callback to get SGPU_CANCEL */
+int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*should_cancel)(void *), void *user);
+
+/* pinned host memory for the upload / download legs */
+int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr);
+void sgpu_host_free(sgpu_ctx *ctx, void *ptr);
+
+/* ---- frame blocks (replaces stack_read_block_data's data->pix[], median_and_mean.c:382) ------ */
+typedef struct {
+	int nb_frames;	/* args->nb_images_to_stack */
+	int nb_layers;	/* naxes[2] */
+	int width;	/* naxes[0] */
+	int height;	/* rows held by this block (a row shard; == naxes[1] on one GPU) */
+	int dtype;	/* SGPU_U16 | SGPU_F32 */
+} sgpu_block_desc;
+
+int sgpu_block_create(sgpu_ctx *ctx, const sgpu_block_desc *desc, sgpu_block **blk);
+/* wrap caller-owned device memory of exactly [nb_frames][nb_layers][height][width] elements */
+int sgpu_block_wrap(sgpu_ctx *ctx, const sgpu_block_desc *desc, void *device_ptr, sgpu_block **blk);
+void sgpu_block_destroy(sgpu_block *blk);
+void *sgpu_block_device_ptr(sgpu_block *blk);
+/* Copy rows of one full host frame ([nb_layers][frame_height][width], memory order) into the
+ * block: block row r (r in [0,height)) is image row row0 + r and receives frame row
+ * row0 + r - shifty, or zeros where that is outside [0, frame_height) — the read-time y shift of
+ * median_and_mean.c:407-448 expressed in memory row order.  Asynchronous on the context stream;
+ * `host_frame` should be pinned for the copy to overlap. */
+int sgpu_block_upload_frame(sgpu_block *blk, int frame, const void *host_frame, int frame_height,
+		int row0, int shifty);
+
+/* ---- stacking (replaces the block loop of stack_mean_or_median, median_and_mean.c:1552-1760) -- */
+typedef struct {
+	int is_mean;			/* 1: stack_mean_with_rejection, 0: stack_median */
+	int type_of_rejection;		/* args->type_of_rejection */
+	float sig[2];			/* args->sig */
+	const float *critical_value;	/* args->critical_value (GESDT), floor(nb_frames*sig[0]) entries (host) */
+	int normalize;			/* args->normalize */
+	const double *scale, *offset, *mul;	/* args->coeff.scale/offset/mul (host), NULL when NO_NORM */
+	const double *weights;		/* args->weights (host) or NULL == NO_WEIGHT */
+	const int *shiftx;		/* per-frame integer x shift (round_to_int(dx), :1621-1623) or NULL */
+	int output_norm;		/* args->output_norm: skip the [0,1] clamp (rescale is sgpu_norm_to_0_1) */
+	int use_32bit_output;		/* args->use_32bit_output: float result, else WORD result */
+	int create_rejmaps;		/* args->create_rejmaps */
+	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
+	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine */
+} sgpu_stack_args;
+
+/* All outputs are DEVICE pointers: d_out [nb_layers][height][width] float or uint16_t,
+ * d_rej_low/high same shape uint16_t (or NULL), d_irej 6 x uint64_t laid out irej[layer][low,high]
+ * and ACCUMULATED into (zero it first).  Asynchronous on the context stream. */
+int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *args,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
+
+/* End-to-end host call: frames[f] points to a full host frame [nb_layers][height][width];
+ * shifty may be NULL.  Uploads (H2D), stacks, applies output_norm, downloads (D2H) into the host
+ * outputs and returns when they are complete.  irej may be NULL. */
+int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *const *frames,
+		const int *shifty, const sgpu_stack_args *args,
+		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
+
+/* norm_to_0_1_range (median_and_mean.c:557-582) split for row shards: min/max over non-zero
+ * samples (skip_first: the reference's scan starts at index 1 — set it on the shard that holds
+ * element 0), then the rescale with the globally reduced min/max. */
+int sgpu_minmax_nonzero(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]);
+int sgpu_rescale_0_1(sgpu_ctx *ctx, float *d_img, size_t n, float mini, float maxi);
+
+/* ---- normalization inputs (replaces compute_normalization, normalization.c:217) --------------- */
+/* imstats fields in the reference's order (core/siril.h:407-413) */
+typedef struct {
+	double total, ngoodpix, mean, median, sigma, avgDev, mad, sqrtbwmv,
+	       location, scale, min, max, normValue, bgnoise;
+} sgpu_imstats;
+
+/* statistics_internal_float / _ushort with STATS_NORM (lite: STATS_LITENORM) on one plane of
+ * nx*ny samples; `plane` is a device pointer when on_device != 0, else host memory (uploaded). */
+int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny,
+		int lite, sgpu_imstats *out);
+
+/* host-side scalar work, [nb_layers * nb_frames] arrays */
+/* _compute_estimators_for_image's choice of estimators (normalization.c:98-141) */
+int sgpu_estimators_from_stats(int normalize, int lite, const sgpu_imstats *st,
+		double *offset, double *mul, double *scale);
+/* compute_factors_from_estimators (normalization.c:144-181): estimators in, factors out */
+int sgpu_compute_factors(int normalize, int nb_layers, int nb_frames, int ref_index, int reglayer,
+		int equalizeRGB, double *offset, double *mul, double *scale);
+/* compute_noise_weights (median_and_mean.c:1111-1135) */
+int sgpu_noise_weights(int nb_layers, int nb_frames, const double *scale, const double *bgnoise,
+		double *weights);
+
+/* ---- row-block planner (stack_compute_parallel_blocks, median_and_mean.c:295-356) ------------- */
+typedef struct { long channel, start_row, end_row, height; } sgpu_image_block;	/* stacking.h:167-169 */
+int sgpu_compute_parallel_blocks(sgpu_image_block *blocks, int max_blocks, long max_number_of_rows,
+		const long naxes[3], int nb_threads, long *largest_block_height, int *nb_blocks);
+
+/* ---- synthetic frames for the benchmark (device-side generator) ---------------- */
+int sgpu_synth_fill(sgpu_ctx *ctx, sgpu_block *blk, uint64_t seed, int row0, int full_height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGPU_H */

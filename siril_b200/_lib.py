@@ -1,0 +1,125 @@
+"""ctypes binding of libsgpu.so — exactly the entry points include/sgpu.h declares."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsgpu.so")
+
+
+class SgpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"sgpu error {code}: {msg}")
+        self.code = code
+
+
+class BlockDesc(C.Structure):
+    _fields_ = [("nb_frames", C.c_int), ("nb_layers", C.c_int), ("width", C.c_int), ("height", C.c_int),
+                ("dtype", C.c_int)]
+
+
+class StackArgs(C.Structure):
+    _fields_ = [("is_mean", C.c_int), ("type_of_rejection", C.c_int), ("sig", C.c_float * 2),
+                ("critical_value", C.c_void_p), ("normalize", C.c_int),
+                ("scale", C.c_void_p), ("offset", C.c_void_p), ("mul", C.c_void_p),
+                ("weights", C.c_void_p), ("shiftx", C.c_void_p),
+                ("output_norm", C.c_int), ("use_32bit_output", C.c_int),
+                ("create_rejmaps", C.c_int), ("merge_lowhigh_rejmaps", C.c_int), ("engine", C.c_int)]
+
+
+class ImStats(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ("total", "ngoodpix", "mean", "median", "sigma", "avgDev", "mad",
+                                          "sqrtbwmv", "location", "scale", "min", "max", "normValue", "bgnoise")]
+
+    def asdict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class ImageBlock(C.Structure):
+    _fields_ = [("channel", C.c_long), ("start_row", C.c_long), ("end_row", C.c_long), ("height", C.c_long)]
+
+
+# every symbol include/sgpu.h declares: name -> (restype, argtypes)
+P = C.c_void_p
+SIGNATURES = {
+    "sgpu_abi_version": (C.c_int, []),
+    "sgpu_ctx_create": (C.c_int, [C.c_int, C.POINTER(P)]),
+    "sgpu_ctx_destroy": (None, [P]),
+    "sgpu_ctx_set_stream": (C.c_int, [P, P]),
+    "sgpu_ctx_synchronize": (C.c_int, [P]),
+    "sgpu_last_error": (C.c_char_p, [P]),
+    "sgpu_launch_count": (C.c_uint64, [P]),
+    "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
+    "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
+    "sgpu_host_free": (None, [P, P]),
+    "sgpu_block_create": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P)]),
+    "sgpu_block_wrap": (C.c_int, [P, C.POINTER(BlockDesc), P, C.POINTER(P)]),
+    "sgpu_block_destroy": (None, [P]),
+    "sgpu_block_device_ptr": (P, [P]),
+    "sgpu_block_upload_frame": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int]),
+    "sgpu_stack_block": (C.c_int, [P, P, C.POINTER(StackArgs), P, P, P, P]),
+    "sgpu_stack_host": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P), P, C.POINTER(StackArgs), P, P, P, P]),
+    "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
+    "sgpu_rescale_0_1": (C.c_int, [P, P, C.c_size_t, C.c_float, C.c_float]),
+    "sgpu_image_stats": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_int, C.POINTER(ImStats)]),
+    "sgpu_estimators_from_stats": (C.c_int, [C.c_int, C.c_int, C.POINTER(ImStats), C.POINTER(C.c_double),
+                                             C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "sgpu_compute_factors": (C.c_int, [C.c_int] * 6 + [P, P, P]),
+    "sgpu_noise_weights": (C.c_int, [C.c_int, C.c_int, P, P, P]),
+    "sgpu_compute_parallel_blocks": (C.c_int, [P, C.c_int, C.c_long, C.POINTER(C.c_long), C.c_int,
+                                               C.POINTER(C.c_long), C.POINTER(C.c_int)]),
+    "sgpu_synth_fill": (C.c_int, [P, P, C.c_uint64, C.c_int, C.c_int]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libsgpu.so; there is no fallback — a missing library is an error."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(nvcc, sm_100a). siril_b200 has no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(L, name)   # AttributeError if the library does not export a declared symbol
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+class Context:
+    """sgpu_ctx wrapper: one per GPU / rank."""
+
+    def __init__(self, device=0, stream=None):
+        self.L = lib()
+        h = P()
+        rv = self.L.sgpu_ctx_create(device, C.byref(h))
+        if rv:
+            raise SgpuError(rv, f"cannot create a context on CUDA device {device} (no GPU? there is no CPU fallback)")
+        self.h = h
+        self.device = device
+        if stream is not None:
+            self.check(self.L.sgpu_ctx_set_stream(self.h, P(stream)))
+
+    def check(self, rv):
+        if rv:
+            raise SgpuError(rv, (self.L.sgpu_last_error(self.h) or b"").decode())
+
+    def synchronize(self):
+        self.check(self.L.sgpu_ctx_synchronize(self.h))
+
+    @property
+    def launches(self):
+        return int(self.L.sgpu_launch_count(self.h))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sgpu_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

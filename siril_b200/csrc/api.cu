@@ -1,0 +1,365 @@
+// api.cu — C ABI of libsgpu.so (include/sgpu.h): context, frame blocks, the stacking entry
+// points and the host-side scalar helpers (planner, factors, weights).
+#include <cstdarg>
+#include <cmath>
+#include <new>
+#include "common.cuh"
+
+int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...) {
+	char buf[512];
+	va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+	if (ctx) ctx->err = buf;
+	return code;
+}
+
+int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what) {
+	const int code = (e == cudaErrorMemoryAllocation) ? SGPU_ALLOC_ERROR : SGPU_GENERIC_ERROR;
+	return sgpu_fail(ctx, code, "CUDA error %d (%s) in %s", (int) e, cudaGetErrorString(e), what);
+}
+
+int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes) {
+	if (bytes <= ctx->d_scratch_cap) return SGPU_OK;
+	if (ctx->d_scratch) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->d_scratch); ctx->d_scratch = nullptr; ctx->d_scratch_cap = 0; }
+	SGPU_CUDA(ctx, cudaMalloc(&ctx->d_scratch, bytes));
+	ctx->d_scratch_cap = bytes;
+	return SGPU_OK;
+}
+
+extern "C" {
+
+int sgpu_abi_version(void) { return SGPU_ABI_VERSION; }
+
+int sgpu_ctx_create(int device, sgpu_ctx **out) {
+	if (!out) return SGPU_GENERIC_ERROR;
+	*out = nullptr;
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+		fprintf(stderr, "sgpu: no usable CUDA device %d (%s); this module has no CPU fallback\n",
+				device, e == cudaSuccess ? "device ordinal out of range" : cudaGetErrorString(e));
+		return SGPU_GENERIC_ERROR;
+	}
+	sgpu_ctx *ctx = new (std::nothrow) sgpu_ctx();
+	if (!ctx) return SGPU_ALLOC_ERROR;
+	ctx->device = device;
+	if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return SGPU_GENERIC_ERROR; }
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return SGPU_GENERIC_ERROR; }
+	ctx->sm_count = prop.multiProcessorCount;
+	ctx->smem_optin = prop.sharedMemPerBlockOptin;
+	if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SGPU_GENERIC_ERROR; }
+	ctx->stream = ctx->own_stream;
+	ctx->d_params_cap = 1 << 20;
+	if (cudaMalloc(&ctx->d_params, ctx->d_params_cap) != cudaSuccess ||
+	    cudaMallocHost(&ctx->h_params, ctx->d_params_cap) != cudaSuccess) { sgpu_ctx_destroy(ctx); return SGPU_ALLOC_ERROR; }
+	*out = ctx;
+	return SGPU_OK;
+}
+
+void sgpu_ctx_destroy(sgpu_ctx *ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaDeviceSynchronize();
+	if (ctx->d_params) cudaFree(ctx->d_params);
+	if (ctx->h_params) cudaFreeHost(ctx->h_params);
+	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+	delete ctx;
+}
+
+int sgpu_ctx_set_stream(sgpu_ctx *ctx, void *s) {
+	if (!ctx) return SGPU_GENERIC_ERROR;
+	ctx->stream = s ? (cudaStream_t) s : ctx->own_stream;
+	return SGPU_OK;
+}
+
+int sgpu_ctx_synchronize(sgpu_ctx *ctx) {
+	if (!ctx) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return SGPU_OK;
+}
+
+const char *sgpu_last_error(const sgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+uint64_t sgpu_launch_count(const sgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*cb)(void *), void *user) {
+	if (!ctx) return SGPU_GENERIC_ERROR;
+	ctx->should_cancel = cb; ctx->cancel_user = user;
+	return SGPU_OK;
+}
+
+int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr) {
+	if (!ctx || !ptr) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaError_t e = cudaMallocHost(ptr, bytes);
+	if (e != cudaSuccess) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "pinned allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+	return SGPU_OK;
+}
+void sgpu_host_free(sgpu_ctx *ctx, void *ptr) { (void) ctx; if (ptr) cudaFreeHost(ptr); }
+
+/* ---- blocks ---- */
+static int check_desc(sgpu_ctx *ctx, const sgpu_block_desc *d) {
+	if (!ctx || !d) return SGPU_GENERIC_ERROR;
+	if (d->nb_frames < 1 || d->nb_layers < 1 || d->nb_layers > 3 || d->width < 1 || d->height < 0 ||
+	    (d->dtype != SGPU_U16 && d->dtype != SGPU_F32))
+		return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "bad block descriptor (%d frames, %d layers, %dx%d, dtype %d)",
+				d->nb_frames, d->nb_layers, d->width, d->height, d->dtype);
+	return SGPU_OK;
+}
+
+int sgpu_block_create(sgpu_ctx *ctx, const sgpu_block_desc *desc, sgpu_block **out) {
+	int rv = check_desc(ctx, desc); if (rv) return rv;
+	sgpu_block *b = new (std::nothrow) sgpu_block();
+	if (!b) return SGPU_ALLOC_ERROR;
+	b->ctx = ctx; b->d = *desc; b->owned = true;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaError_t e = cudaMalloc(&b->dev, b->bytes() ? b->bytes() : 16);
+	if (e != cudaSuccess) { delete b; return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "cannot allocate %zu bytes of HBM for the frame block: %s", b->bytes(), cudaGetErrorString(e)); }
+	*out = b;
+	return SGPU_OK;
+}
+
+int sgpu_block_wrap(sgpu_ctx *ctx, const sgpu_block_desc *desc, void *dev, sgpu_block **out) {
+	int rv = check_desc(ctx, desc); if (rv) return rv;
+	if (!dev) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "null device pointer");
+	sgpu_block *b = new (std::nothrow) sgpu_block();
+	if (!b) return SGPU_ALLOC_ERROR;
+	b->ctx = ctx; b->d = *desc; b->owned = false; b->dev = dev;
+	*out = b;
+	return SGPU_OK;
+}
+
+void sgpu_block_destroy(sgpu_block *b) {
+	if (!b) return;
+	if (b->owned && b->dev) { cudaStreamSynchronize(b->ctx->stream); cudaFree(b->dev); }
+	delete b;
+}
+
+void *sgpu_block_device_ptr(sgpu_block *b) { return b ? b->dev : nullptr; }
+
+int sgpu_block_upload_frame(sgpu_block *b, int frame, const void *host, int frame_height, int row0, int shifty) {
+	if (!b || !host) return SGPU_GENERIC_ERROR;
+	sgpu_ctx *ctx = b->ctx;
+	const sgpu_block_desc &d = b->d;
+	if (frame < 0 || frame >= d.nb_frames) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d out of range", frame);
+	const size_t es = b->elem(), rowb = (size_t) d.width * es;
+	// block row r <- frame row row0 + r - shifty, valid when inside [0, frame_height)
+	long lo = (long) shifty - row0; if (lo < 0) lo = 0;			// first valid block row
+	long hi = (long) frame_height + shifty - row0; if (hi > d.height) hi = d.height;	// one past last valid
+	for (int l = 0; l < d.nb_layers; l++) {
+		char *dst = (char *) b->dev + (((size_t) frame * d.nb_layers + l) * b->plane()) * es;
+		const char *src = (const char *) host + (size_t) l * frame_height * rowb;
+		if (hi <= lo) { SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) d.height * rowb, ctx->stream)); continue; }
+		if (lo > 0) SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) lo * rowb, ctx->stream));
+		if (hi < d.height) SGPU_CUDA(ctx, cudaMemsetAsync(dst + (size_t) hi * rowb, 0, (size_t) (d.height - hi) * rowb, ctx->stream));
+		SGPU_CUDA(ctx, cudaMemcpyAsync(dst + (size_t) lo * rowb, src + (size_t) (row0 + lo - shifty) * rowb,
+				(size_t) (hi - lo) * rowb, cudaMemcpyDefault, ctx->stream));
+	}
+	return SGPU_OK;
+}
+
+/* ---- stacking ---- */
+static int check_args(sgpu_ctx *ctx, const sgpu_block_desc &d, const sgpu_stack_args *a) {
+	if (!a) return SGPU_GENERIC_ERROR;
+	// median_and_mean.c:1279-1285
+	if (d.nb_frames < 2) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "Select at least two frames for stacking. Aborting.");
+	if (d.nb_frames < 3 && a->is_mean && a->type_of_rejection == SGPU_GESDT)
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "The Generalized Extreme Studentized Deviate Test needs at least three frames for stacking. Aborting.");
+	if (a->type_of_rejection < SGPU_NO_REJEC || a->type_of_rejection > SGPU_GESDT) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "unknown rejection type %d", a->type_of_rejection);
+	if (a->normalize < SGPU_NO_NORM || a->normalize > SGPU_MULTIPLICATIVE_SCALING) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "unknown normalization %d", a->normalize);
+	if (a->normalize != SGPU_NO_NORM && (!a->scale || !a->offset || !a->mul)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "normalization requested without coefficients");
+	if (a->is_mean && a->type_of_rejection == SGPU_GESDT && !a->critical_value) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "GESDT needs critical values");
+	if (!a->use_32bit_output && d.dtype == SGPU_F32) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "16-bit output needs 16-bit input");
+	return SGPU_OK;
+}
+
+// stage the small per-call arrays into the device parameter arena
+static int stage_params(sgpu_ctx *ctx, const sgpu_block_desc &d, const sgpu_stack_args *a, StackDevParams &dp) {
+	const size_t cn = (size_t) d.nb_layers * d.nb_frames;
+	size_t off = 0;
+	auto put = [&](const void *src, size_t bytes) -> const void * {
+		if (!src) return nullptr;
+		off = (off + 15) & ~(size_t) 15;
+		if (off + bytes > ctx->d_params_cap) return nullptr;
+		memcpy((char *) ctx->h_params + off, src, bytes);
+		const void *dev = (char *) ctx->d_params + off;
+		off += bytes;
+		return dev;
+	};
+	// the pinned mirror is reused by every call: make sure the previous copy has left it
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	const bool norm = a->normalize != SGPU_NO_NORM;
+	dp.scale = (const double *) put(norm ? a->scale : nullptr, cn * 8);
+	dp.offset = (const double *) put(norm ? a->offset : nullptr, cn * 8);
+	dp.mul = (const double *) put(norm ? a->mul : nullptr, cn * 8);
+	dp.weights = (const double *) put(a->is_mean ? a->weights : nullptr, cn * 8);
+	dp.shiftx = (const int *) put(a->shiftx, (size_t) d.nb_frames * 4);
+	int ncrit = 0;
+	if (a->is_mean && a->type_of_rejection == SGPU_GESDT) ncrit = (int) floor(d.nb_frames * a->sig[0]);
+	dp.crit = (const float *) put(ncrit ? a->critical_value : nullptr, (size_t) ncrit * 4);
+	if ((norm && (!dp.scale || !dp.offset || !dp.mul)) || (a->is_mean && a->weights && !dp.weights) ||
+	    (a->shiftx && !dp.shiftx) || (ncrit && !dp.crit))
+		return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "parameter arena too small for %d frames", d.nb_frames);
+	if (off) SGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_params, ctx->h_params, off, cudaMemcpyHostToDevice, ctx->stream));
+	return SGPU_OK;
+}
+
+int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej) {
+	if (!ctx || !blk) return SGPU_GENERIC_ERROR;
+	int rv = check_args(ctx, blk->d, a); if (rv) return rv;
+	if (!d_out) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "null output");
+	if (a->is_mean && a->create_rejmaps && (!d_rej_low || (!a->merge_lowhigh_rejmaps && !d_rej_high)))
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rejection maps requested without buffers");
+	if (a->is_mean && a->type_of_rejection != SGPU_NO_REJEC && !d_irej) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "null rejection counters");
+	if (ctx->should_cancel && ctx->should_cancel(ctx->cancel_user)) return sgpu_fail(ctx, SGPU_CANCEL, "cancelled");
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	StackDevParams dp;
+	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
+	return sgpu_launch_exact(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+}
+
+int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *const *frames,
+		const int *shifty, const sgpu_stack_args *a,
+		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !desc || !frames || !out) return SGPU_GENERIC_ERROR;
+	int rv = check_args(ctx, *desc, a); if (rv) return rv;
+	sgpu_block *blk = nullptr;
+	rv = sgpu_block_create(ctx, desc, &blk); if (rv) return rv;
+	const size_t npx = (size_t) desc->nb_layers * desc->height * desc->width;
+	const size_t out_es = a->use_32bit_output ? 4 : 2;
+	const int nmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
+	char *d_buf = nullptr;
+	const size_t out_bytes = (npx * out_es + 255) & ~(size_t) 255, map_bytes = (npx * 2 + 255) & ~(size_t) 255;
+	cudaError_t e = cudaMalloc(&d_buf, out_bytes + nmaps * map_bytes + 64);
+	if (e != cudaSuccess) { sgpu_block_destroy(blk); return sgpu_cuda_fail(ctx, e, "cudaMalloc(outputs)"); }
+	void *d_out = d_buf;
+	uint16_t *d_lo = nmaps >= 1 ? (uint16_t *) (d_buf + out_bytes) : nullptr;
+	uint16_t *d_hi = nmaps == 2 ? (uint16_t *) (d_buf + out_bytes + map_bytes) : nullptr;
+	uint64_t *d_irej = (uint64_t *) (d_buf + out_bytes + nmaps * map_bytes);
+	auto cleanup = [&](int code) { cudaStreamSynchronize(ctx->stream); cudaFree(d_buf); sgpu_block_destroy(blk); return code; };
+	if (cudaMemsetAsync(d_irej, 0, 48, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	for (int f = 0; f < desc->nb_frames; f++) {
+		rv = sgpu_block_upload_frame(blk, f, frames[f], desc->height, 0, shifty ? shifty[f] : 0);
+		if (rv) return cleanup(rv);
+	}
+	rv = sgpu_stack_block(ctx, blk, a, d_out, d_lo, d_hi, d_irej);
+	if (rv) return cleanup(rv);
+	if (a->use_32bit_output && a->output_norm) {
+		float mm[2];
+		rv = sgpu_minmax_nonzero(ctx, (const float *) d_out, npx, 1, mm); if (rv) return cleanup(rv);
+		rv = sgpu_rescale_0_1(ctx, (float *) d_out, npx, mm[0], mm[1]); if (rv) return cleanup(rv);
+	}
+	if (cudaMemcpyAsync(out, d_out, npx * out_es, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	if (d_lo && rej_low && cudaMemcpyAsync(rej_low, d_lo, npx * 2, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	if (d_hi && rej_high && cudaMemcpyAsync(rej_high, d_hi, npx * 2, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	uint64_t h_irej[6] = { 0 };
+	if (cudaMemcpyAsync(h_irej, d_irej, 48, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	e = cudaStreamSynchronize(ctx->stream);
+	if (e != cudaSuccess) return cleanup(sgpu_cuda_fail(ctx, e, "stack"));
+	if (irej) memcpy(irej, h_irej, 48);
+	return cleanup(SGPU_OK);
+}
+
+/* ---- host-side scalar helpers ---- */
+
+/* _compute_estimators_for_image (normalization.c:98-141): which statistic feeds which array */
+int sgpu_estimators_from_stats(int normalize, int lite, const sgpu_imstats *st, double *offset, double *mul, double *scale) {
+	if (!st || !offset || !mul || !scale) return SGPU_GENERIC_ERROR;
+	*offset = 0.0; *mul = 1.0; *scale = 1.0;	/* init_coeffs, normalization.c:81-96 */
+	switch (normalize) {
+	default:
+	case SGPU_ADDITIVE_SCALING: *scale = lite ? 1.5 * st->mad : st->scale; /* fallthrough */
+	case SGPU_ADDITIVE: *offset = lite ? st->median : st->location; break;
+	case SGPU_MULTIPLICATIVE_SCALING: *scale = lite ? 1.5 * st->mad : st->scale; /* fallthrough */
+	case SGPU_MULTIPLICATIVE: *mul = lite ? st->median : st->location; break;
+	}
+	return SGPU_OK;
+}
+
+/* compute_factors_from_estimators (normalization.c:144-181) */
+int sgpu_compute_factors(int normalize, int nb_layers, int N, int ref_index, int reglayer, int equalizeRGB,
+		double *offset, double *mul, double *scale) {
+	if (!offset || !mul || !scale || nb_layers < 1 || nb_layers > 3 || ref_index < 0 || ref_index >= N) return SGPU_GENERIC_ERROR;
+	double o0[3], m0[3], s0[3];
+	for (int l = 0; l < nb_layers; l++) {
+		o0[l] = offset[l * N + ref_index]; m0[l] = mul[l * N + ref_index]; s0[l] = scale[l * N + ref_index];
+	}
+	const int rl = reglayer > -1 ? reglayer : 1;
+	for (int l = 0; l < nb_layers; l++) {
+		const int ref = equalizeRGB ? rl : l;
+		for (int i = 0; i < N; i++) {
+			double &ps = scale[l * N + i], &po = offset[l * N + i], &pm = mul[l * N + i];
+			if (normalize == SGPU_ADDITIVE || normalize == SGPU_MULTIPLICATIVE) {
+				if (normalize == SGPU_ADDITIVE) po = ps * po - o0[ref];
+				else pm = (pm == 0) ? 1 : m0[ref] / pm;
+			} else if (normalize == SGPU_MULTIPLICATIVE_SCALING) {
+				ps = (ps == 0) ? 1 : s0[ref] / ps;
+				pm = (pm == 0) ? 1 : m0[ref] / pm;
+			} else {	/* ADDITIVE_SCALING and the switch's default */
+				ps = (ps == 0) ? 1 : s0[ref] / ps;
+				po = ps * po - o0[ref];
+			}
+		}
+	}
+	return SGPU_OK;
+}
+
+/* compute_noise_weights (median_and_mean.c:1111-1135) */
+int sgpu_noise_weights(int nb_layers, int N, const double *scale, const double *bgnoise, double *weights) {
+	if (!scale || !bgnoise || !weights) return SGPU_GENERIC_ERROR;
+	for (int l = 0; l < nb_layers; l++) {
+		double norm = 0.0;
+		for (int i = 0; i < N; i++) {
+			const double s = scale[l * N + i], b = bgnoise[l * N + i];
+			weights[l * N + i] = 1.f / (s * s * b * b);
+			norm += weights[l * N + i];
+		}
+		norm /= (double) N;
+		for (int i = 0; i < N; i++) weights[l * N + i] /= norm;
+	}
+	return SGPU_OK;
+}
+
+/* refine_blocks_candidate + stack_compute_parallel_blocks (median_and_mean.c:261-356) */
+int sgpu_compute_parallel_blocks(sgpu_image_block *blocks, int max_blocks, long max_rows, const long naxes[3],
+		int nb_threads, long *largest, int *nb_blocks) {
+	if (!naxes || !largest || !nb_blocks || nb_threads < 1 || max_rows < 1) return SGPU_GENERIC_ERROR;
+	const long H = naxes[1], C = naxes[2];
+	auto ceil_mult = [](int x, int f) { const int r = x % f; return r ? x + f - r : x; };
+	int cand = nb_threads;
+	while ((max_rows * cand) / nb_threads < H * C) cand++;
+	int factor = (C == 3) ? 3 : 1;
+	if (nb_threads < 4) {
+		if (factor != 1 && nb_threads % factor == 0) factor = nb_threads; else factor *= nb_threads;
+		cand = ceil_mult(cand, factor);
+	} else {
+		const int slack = nb_threads < 8 ? 1 : 3;
+		cand = ceil_mult(cand, factor);
+		for (;;) { const int rem = cand % nb_threads; if (rem == 0 || rem >= nb_threads - slack) break; cand += factor; }
+	}
+	*nb_blocks = cand;
+	const long hb = H * C / cand;
+	long remainder = H % (cand / C);
+	*largest = 0;
+	long ch = 0, row = 0; int j = 0;
+	do {
+		if (j >= cand) return SGPU_GENERIC_ERROR;
+		long end = row + hb - 1;
+		if (remainder > 0) { end++; remainder--; }
+		const long start = row, channel = ch;
+		if (end >= H - 1 || (H - end < hb / 10)) {
+			end = H - 1; row = 0; ch++;
+			remainder = H - (cand / C * hb);
+		} else row = end + 1;
+		const long h = end - start + 1;
+		if (blocks && j < max_blocks) { blocks[j].channel = channel; blocks[j].start_row = start; blocks[j].end_row = end; blocks[j].height = h; }
+		if (*largest < h) *largest = h;
+		j++;
+	} while (ch < C);
+	return SGPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+// common.cuh — internal types shared by the translation units of libsgpu.so
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/sgpu.h"
+
+struct sgpu_ctx {
+	int device = 0;
+	cudaStream_t own_stream = nullptr;
+	cudaStream_t stream = nullptr;
+	cudaStream_t copy_stream = nullptr;
+	std::string err;
+	uint64_t launches = 0;
+	int sm_count = 148;
+	size_t smem_optin = 0;
+	int (*should_cancel)(void *) = nullptr;
+	void *cancel_user = nullptr;
+	// small device-side parameter arena (coefficients, weights, shifts, critical values)
+	void *d_params = nullptr; size_t d_params_cap = 0;
+	void *h_params = nullptr;			// pinned mirror
+	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
+};
+
+struct sgpu_block {
+	sgpu_ctx *ctx = nullptr;
+	sgpu_block_desc d{};
+	void *dev = nullptr;
+	bool owned = false;
+	size_t elem() const { return d.dtype == SGPU_F32 ? 4 : 2; }
+	size_t plane() const { return (size_t) d.width * d.height; }
+	size_t frame_elems() const { return plane() * d.nb_layers; }
+	size_t bytes() const { return frame_elems() * d.nb_frames * elem(); }
+};
+
+int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...);
+int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what);
+int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes);
+
+#define SGPU_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return sgpu_cuda_fail((ctx), e__, #call); } while (0)
+
+// device-resident copy of the per-call parameter arrays
+struct StackDevParams {
+	const double *scale = nullptr, *offset = nullptr, *mul = nullptr, *weights = nullptr;
+	const int *shiftx = nullptr;
+	const float *crit = nullptr;
+};
+
+// engines
+int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);

@@ -1,0 +1,119 @@
+// misc.cu — output renormalization (norm_to_0_1_range, median_and_mean.c:557-582) and the
+// device-side synthetic frame generator used by bench.py / tests.
+#include <cfloat>
+#include "common.cuh"
+
+namespace sgpu {
+
+// min / max over non-zero samples; one partial per CTA, reduced by the host (<= 1184 pairs)
+__global__ void minmax_nonzero_kernel(const float *img, size_t n, size_t first, float2 *partial) {
+	float mn = FLT_MAX, mx = -FLT_MAX;
+	for (size_t i = first + (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		const float t = img[i];
+		if (t == 0.f) continue;
+		if (t < mn) mn = t;
+		if (t > mx) mx = t;
+	}
+	for (int o = 16; o; o >>= 1) {
+		mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+		mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+	}
+	__shared__ float smn[32], smx[32];
+	if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		for (int w = 1; w < (int) (blockDim.x >> 5); w++) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+		partial[blockIdx.x] = make_float2(mn, mx);
+	}
+}
+
+__global__ void rescale_kernel(float *img, size_t n, float mini, float maxi) {
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		const float v = img[i];
+		img[i] = (v == 0.f) ? 0.f : (v - mini) / (maxi - mini);
+	}
+}
+
+// counter-based generator: 64-bit mix of (seed, frame, layer, row, col, stream)
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+	z += 0x9e3779b97f4a7c15ull;
+	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+	z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+	return z ^ (z >> 31);
+}
+__device__ __forceinline__ float u01(uint64_t h) { return ((h >> 40) + 0.5f) * (1.0f / 16777216.0f); }
+
+template <typename T>
+__global__ void synth_kernel(T *dst, int N, int C, int H, int W, uint64_t seed, int row0, int fullH) {
+	const size_t plane = (size_t) H * W;
+	const size_t total = plane * C * N;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+		const int x = (int) (i % W);
+		const int r = (int) ((i / W) % H) + row0;
+		const int l = (int) ((i / plane) % C);
+		const int f = (int) (i / (plane * C));
+		const uint64_t kf = mix64(seed * 0x100000001b3ull + (uint64_t) f * 7919u + l);
+		const float g = 2.f * u01(mix64(kf ^ 1)) - 1.f, h = 2.f * u01(mix64(kf ^ 2)) - 1.f;
+		const float sky = 0.10f * (1.f + 0.02f * g), gain = 1.f + 0.05f * h;
+		const float fx = (float) x / W - 0.5f, fy = (float) r / fullH - 0.5f;
+		const float S = 0.3f * __expf(-(fx * fx + fy * fy) * 8.f) * (0.6f + 0.4f * __sinf(12.f * fx) * __cosf(9.f * fy)) ;
+		const uint64_t kp = mix64(kf + ((uint64_t) r << 32) + (uint64_t) x);
+		const float u1 = u01(mix64(kp ^ 3)), u2 = u01(mix64(kp ^ 4));
+		const float n = sqrtf(-2.f * __logf(u1)) * __cosf(6.2831853f * u2);
+		float v = gain * (sky + fabsf(S)) + 0.01f * n;
+		const float uo = u01(mix64(kp ^ 5));
+		if (uo < 1e-3f) v += 0.2f + 0.4f * u01(mix64(kp ^ 6));
+		else if (uo < 1.2e-3f) v -= 0.05f;
+		v = fminf(fmaxf(v, 1e-4f), 1.f);
+		if (sizeof(T) == 4) dst[i] = (T) v;
+		else { float q = rintf(v * 65535.f); dst[i] = (T) (q < 1.f ? 1.f : q); }
+	}
+}
+
+}  // namespace sgpu
+
+using namespace sgpu;
+
+extern "C" {
+
+int sgpu_minmax_nonzero(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]) {
+	if (!ctx || !d_img || !minmax) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const int blocks = ctx->sm_count * 8;
+	int rv = sgpu_ensure_scratch(ctx, blocks * sizeof(float2)); if (rv) return rv;
+	minmax_nonzero_kernel<<<blocks, 256, 0, ctx->stream>>>(d_img, n, skip_first ? 1 : 0, (float2 *) ctx->d_scratch);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	std::vector<float2> part(blocks);
+	SGPU_CUDA(ctx, cudaMemcpyAsync(part.data(), ctx->d_scratch, blocks * sizeof(float2), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	float mn = FLT_MAX, mx = -FLT_MAX;
+	for (auto &p : part) { if (p.x < mn) mn = p.x; if (p.y > mx) mx = p.y; }
+	minmax[0] = mn; minmax[1] = mx;
+	return SGPU_OK;
+}
+
+int sgpu_rescale_0_1(sgpu_ctx *ctx, float *d_img, size_t n, float mini, float maxi) {
+	if (!ctx || !d_img) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	rescale_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d_img, n, mini, maxi);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	return SGPU_OK;
+}
+
+int sgpu_synth_fill(sgpu_ctx *ctx, sgpu_block *blk, uint64_t seed, int row0, int full_height) {
+	if (!ctx || !blk) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const sgpu_block_desc &d = blk->d;
+	const int blocks = ctx->sm_count * 16;
+	if (d.dtype == SGPU_F32)
+		synth_kernel<float><<<blocks, 256, 0, ctx->stream>>>((float *) blk->dev, d.nb_frames, d.nb_layers, d.height, d.width, seed, row0, full_height);
+	else
+		synth_kernel<uint16_t><<<blocks, 256, 0, ctx->stream>>>((uint16_t *) blk->dev, d.nb_frames, d.nb_layers, d.height, d.width, seed, row0, full_height);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	return SGPU_OK;
+}
+
+}  // extern "C"

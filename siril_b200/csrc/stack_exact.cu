@@ -1,0 +1,179 @@
+// stack_exact.cu — kernel + launcher of the thread-per-pixel engine (see exact.cuh).
+//
+// One CTA handles `blockDim.x` consecutive pixels of one layer.  For every frame the CTA reads
+// the same pixel range of that frame's plane — consecutive threads read consecutive samples, so
+// each warp issues full 128-byte coalesced HBM reads on the frame-major layout — applies the
+// per-frame normalization in double exactly as median_and_mean.c:1644-1686 does, and parks the
+// value in the thread's shared-memory column tile[f][tid] (conflict-free: consecutive threads
+// hit consecutive banks).  The rejection / combine then runs entirely out of shared memory.
+#include "common.cuh"
+#include "exact.cuh"
+
+namespace sgpu {
+
+struct ExactParams {
+	const void *frames;	// [N][C][H][W]
+	int N, C, H, W;
+	int normalize;
+	const double *scale, *offset, *mul, *weights;	// device, [C*N]
+	const int *shiftx;	// device [N] or null
+	RejCfg rc;
+	int is_mean, output_norm, out32, rejmaps;	// rejmaps: 0 none, 1 merged, 2 low+high
+	void *out; u16 *rej_low, *rej_high;
+	unsigned long long *irej;	// [3][2]
+	void *scratch;		// global columns when the tile does not fit in shared memory
+	int use_aux;
+};
+
+// one sample, normalized (median_and_mean.c:1638-1686); x is the pixel's column, `sx` the
+// per-frame shift (0 when none)
+template <typename T>
+__device__ __forceinline__ T load_norm(const ExactParams &p, int f, int layer, size_t pix, int x) {
+	T v = (T) 0;
+	int sxv = p.shiftx ? p.shiftx[f] : 0;
+	const int xs = x - sxv;
+	if (xs >= 0 && xs < p.W) {
+		const T *plane = (const T *) p.frames + ((size_t) f * p.C + layer) * ((size_t) p.H * p.W);
+		v = __ldg(plane + pix - sxv);
+	}
+	const int ci = layer * p.N + f;
+	switch (p.normalize) {
+	default: case SGPU_NO_NORM: return v;
+	case SGPU_ADDITIVE: case SGPU_ADDITIVE_SCALING:
+		if (sizeof(T) == 4) {
+			if (v != (T) 0) { const double tmp = (double) v * p.scale[ci]; return (T) (float) (tmp - p.offset[ci]); }
+			return (T) 0;
+		} else {
+			if (v > (T) 0) { const double tmp = (double) v * p.scale[ci]; return (T) round_to_word(tmp - p.offset[ci]); }
+			return (T) 0;
+		}
+	case SGPU_MULTIPLICATIVE: case SGPU_MULTIPLICATIVE_SCALING: {
+		const double tmp = (double) v * p.scale[ci];
+		if (sizeof(T) == 4) return (T) (float) (tmp * p.mul[ci]);
+		return (T) round_to_word(tmp * p.mul[ci]);
+	}
+	}
+}
+
+template <typename T, bool SMEM>
+__global__ void __launch_bounds__(256) stack_exact_kernel(const ExactParams p) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int layer = blockIdx.y;
+	const size_t npix = (size_t) p.H * p.W;
+	const size_t pix = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+	const bool active = pix < npix;
+	Col<T> st; Col<u16> aux;
+	if (SMEM) {
+		st.p = (T *) smem_raw + threadIdx.x; st.s = blockDim.x;
+		aux.p = (u16 *) (smem_raw + (size_t) p.N * blockDim.x * sizeof(T)) + threadIdx.x; aux.s = blockDim.x;
+	} else {
+		const size_t nthreads = (size_t) gridDim.x * gridDim.y * blockDim.x;
+		const size_t gtid = ((size_t) blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+		st.p = (T *) p.scratch + gtid; st.s = (int) nthreads;
+		aux.p = (u16 *) ((T *) p.scratch + (size_t) p.N * nthreads) + gtid; aux.s = (int) nthreads;
+	}
+	int rej[2] = { 0, 0 };
+	if (active) {
+		const int x = (int) (pix % p.W);
+		const int N = p.N;
+		int f = 0;
+		for (; f + 4 <= N; f += 4) {	// 4 independent loads in flight per thread
+			const T v0 = load_norm<T>(p, f, layer, pix, x), v1 = load_norm<T>(p, f + 1, layer, pix, x);
+			const T v2 = load_norm<T>(p, f + 2, layer, pix, x), v3 = load_norm<T>(p, f + 3, layer, pix, x);
+			st.set(f, v0); st.set(f + 1, v1); st.set(f + 2, v2); st.set(f + 3, v3);
+		}
+		for (; f < N; f++) st.set(f, load_norm<T>(p, f, layer, pix, x));
+
+		double result;
+		if (p.is_mean) {
+			const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
+			auto orig = [&](int ff) { return load_norm<T>(p, ff, layer, pix, x); };
+			result = mean_and_reject<T>(st, N, p.rc, w, aux, orig, rej);
+		} else {
+			result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
+		}
+		const size_t o = (size_t) layer * npix + pix;
+		if (p.rejmaps == 1) p.rej_low[o] = truncate_to_word(rej[0] + rej[1]);
+		else if (p.rejmaps == 2) { p.rej_low[o] = truncate_to_word(rej[0]); p.rej_high[o] = truncate_to_word(rej[1]); }
+		if (p.out32) {	// median_and_mean.c:1717-1727
+			float v = (sizeof(T) == 4) ? (float) result : (float) result * .000015259022f;
+			if (!p.output_norm) { v = v < 0.f ? 0.f : v; v = v > 1.f ? 1.f : v; }
+			((float *) p.out)[o] = v;
+		} else ((u16 *) p.out)[o] = round_to_word(result);
+	}
+	if (p.is_mean && p.rc.type != SGPU_NO_REJEC) {	// irej[channel][low/high], :1748-1757
+		unsigned lo = rej[0], hi = rej[1];
+		lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
+		if ((threadIdx.x & 31) == 0 && (lo | hi)) {
+			atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
+			atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+		}
+	}
+}
+
+}  // namespace sgpu
+
+using namespace sgpu;
+
+int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej) {
+	const sgpu_block_desc &d = blk->d;
+	ExactParams p{};
+	p.frames = blk->dev; p.N = d.nb_frames; p.C = d.nb_layers; p.H = d.height; p.W = d.width;
+	p.normalize = a->normalize; p.scale = dp.scale; p.offset = dp.offset; p.mul = dp.mul;
+	p.weights = a->is_mean ? dp.weights : nullptr;
+	p.shiftx = dp.shiftx;
+	p.rc.type = a->is_mean ? a->type_of_rejection : SGPU_NO_REJEC;
+	p.rc.s0 = a->sig[0]; p.rc.s1 = a->sig[1]; p.rc.crit = dp.crit; p.rc.nb_frames = d.nb_frames;
+	p.rc.m_x = 0.f; p.rc.m_dx2 = 0.f;
+	if (p.rc.type == SGPU_LINEARFIT) {	// median_and_mean.c:1491-1499 (host, float)
+		volatile float mx = (d.nb_frames - 1) * 0.5f, acc = 0.f;
+		for (int j = 0; j < d.nb_frames; ++j) {
+			volatile float dx = j - mx;
+			volatile float sq = dx * dx;
+			volatile float diff = sq - acc;
+			volatile float xf = 1.f / (j + 1);
+			volatile float prod = diff * xf;
+			acc = acc + prod;
+		}
+		p.rc.m_x = mx; p.rc.m_dx2 = 1.f / acc;
+	}
+	p.is_mean = a->is_mean; p.output_norm = a->output_norm; p.out32 = a->use_32bit_output;
+	p.rejmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
+	p.out = d_out; p.rej_low = d_rej_low; p.rej_high = d_rej_high; p.irej = (unsigned long long *) d_irej;
+	const bool need_aux = a->is_mean && (p.rc.type == SGPU_MAD || p.rc.type == SGPU_GESDT);
+	p.use_aux = need_aux;
+	const size_t es = blk->elem();
+	const size_t per_thread = (size_t) d.nb_frames * es + (need_aux ? (size_t) d.nb_frames * 2 : 0);
+	const size_t npix = (size_t) d.height * d.width;
+	if (npix == 0 || d.nb_frames == 0) return SGPU_OK;
+
+	// largest CTA (<= 256 threads) whose tile leaves room for two CTAs per SM; else one CTA; else
+	// global columns
+	int bd = 0;
+	const size_t half = ctx->smem_optin / 2 - 1024;
+	for (int cand = 256; cand >= 32; cand >>= 1) if (per_thread * cand <= half) { bd = cand; break; }
+	if (!bd) for (int cand = 64; cand >= 32; cand >>= 1) if (per_thread * cand <= ctx->smem_optin) { bd = cand; break; }
+	const bool smem = bd != 0;
+	if (!smem) bd = 128;
+	const size_t shm = smem ? per_thread * bd : 0;
+	dim3 grid((unsigned) ((npix + bd - 1) / bd), (unsigned) d.nb_layers);
+	if (!smem) {
+		const size_t nthreads = (size_t) grid.x * grid.y * bd;
+		if ((size_t) d.nb_frames * nthreads > 0x7fffffffull)
+			return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for one launch (%d frames x %zu px)", d.nb_frames, npix);
+		int rv = sgpu_ensure_scratch(ctx, per_thread * nthreads);
+		if (rv) return rv;
+		p.scratch = ctx->d_scratch;
+	}
+	auto launch = [&](auto kern) -> int {
+		if (shm > 48 * 1024)
+			SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
+		kern<<<grid, bd, shm, ctx->stream>>>(p);
+		ctx->launches++;
+		SGPU_CUDA(ctx, cudaGetLastError());
+		return SGPU_OK;
+	};
+	if (d.dtype == SGPU_F32) return smem ? launch(stack_exact_kernel<float, true>) : launch(stack_exact_kernel<float, false>);
+	return smem ? launch(stack_exact_kernel<u16, true>) : launch(stack_exact_kernel<u16, false>);
+}

@@ -1,0 +1,335 @@
+"""Host-side mirror of the reference's stacking interface for the GPU path.
+
+Names, argument meaning and error behaviour follow the reference:
+  struct stacking_args / norm_coeff        src/stacking/stacking.h:55-117
+  main_stack                               src/stacking/stacking.c:76-108
+  stack_mean_with_rejection / stack_median src/stacking/median_and_mean.c:1103-1109
+  do_normalization                         src/stacking/normalization.c:46-78
+All computation happens in libsgpu.so (CUDA); this file only marshals arguments.
+"""
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Any, Callable, Optional
+
+import numpy as np
+
+from . import _lib
+from .enums import *  # noqa: F401,F403
+from .enums import (ADDITIVE, ADDITIVE_SCALING, GESDT, MULTIPLICATIVE, MULTIPLICATIVE_SCALING, NO_NORM, NO_REJEC,
+                    NO_WEIGHT, NOISE_WEIGHT, ST_GENERIC_ERROR, ST_OK)
+
+
+def gesdt_critical_values(nb_frames, sig0, sig1):
+    """args->critical_value as stack_mean_or_median fills it (median_and_mean.c:1479-1486):
+    t = tdist_Pinv(1 - sig[1] / (2 * size), size - 2) with the probability evaluated in FLOAT,
+    then float arithmetic.  The reference uses GSL's quantile; this harness uses scipy's."""
+    from scipy.stats import t as tdist
+    f32 = np.float32
+    n_out = int(np.floor(nb_frames * float(f32(sig0))))
+    out = np.empty(max(n_out, 0), dtype=np.float32)
+    size = nb_frames
+    for j in range(n_out):
+        p = f32(1) - f32(sig1) / f32(2 * size)
+        td = f32(tdist.ppf(float(p), size - 2))
+        num = f32(size - 1) * td
+        den = np.sqrt(f32(size)) * np.sqrt(f32(size - 2) + td * td)
+        out[j] = f32(num / den)
+        size -= 1
+    return out
+
+
+@dataclass
+class NormCoeff:
+    """norm_coeff (stacking.h:55-62): [layer][frame] doubles"""
+    offset: Optional[np.ndarray] = None
+    mul: Optional[np.ndarray] = None
+    scale: Optional[np.ndarray] = None
+
+
+@dataclass
+class StackResult:
+    """what the reference leaves in args->result / rejmap_low / rejmap_high / the log counters"""
+    data: Any = None          # [C][H][W] float32 or uint16 (torch CUDA tensor or numpy array)
+    rejmap_low: Any = None
+    rejmap_high: Any = None
+    irej: Optional[np.ndarray] = None   # [3][2] uint64: low/high rejections per channel (:1766-1772)
+
+
+@dataclass
+class StackingArgs:
+    """struct stacking_args restricted to what the hot path consumes (stacking.h:65-117).
+
+    `frames` replaces seq + image_indices: the selected frames as ONE array [N][C][H][W] in memory
+    (FITS) row order — a torch CUDA tensor (device-resident: the timed `value` path) or a numpy
+    array / list of numpy frames on the host (the end-to-end path: H2D + stack + D2H)."""
+    method: Optional[Callable[["StackingArgs"], int]] = None
+    frames: Any = None
+    ref_image: int = 0
+    lite_norm: bool = False
+    normalize: int = NO_NORM
+    coeff: NormCoeff = field(default_factory=NormCoeff)
+    force_norm: bool = False
+    output_norm: bool = False
+    use_32bit_output: bool = True
+    reglayer: int = -1
+    equalizeRGB: bool = False
+    shiftx: Optional[np.ndarray] = None   # round_to_int(dx) per frame (median_and_mean.c:1621-1623)
+    shifty: Optional[np.ndarray] = None   # round_to_int(dy) per frame (:416-418)
+    type_of_rejection: int = NO_REJEC
+    sig: tuple = (3.0, 3.0)
+    critical_value: Optional[np.ndarray] = None
+    create_rejmaps: bool = False
+    merge_lowhigh_rejmaps: bool = False
+    weighting_type: int = NO_WEIGHT
+    weights: Optional[np.ndarray] = None
+    bgnoise: Optional[np.ndarray] = None  # seq->stats[layer][idx]->bgnoise, filled by do_normalization
+    engine: int = 0
+    retval: int = ST_OK
+    result: StackResult = field(default_factory=StackResult)
+    ctx: Optional[_lib.Context] = None
+
+    @property
+    def nb_images_to_stack(self):
+        return len(self.frames)
+
+
+def _is_torch_cuda(x):
+    return type(x).__module__.startswith("torch") and getattr(x, "is_cuda", False)
+
+
+def _context(args):
+    if args.ctx is None:
+        dev, stream = 0, None
+        if _is_torch_cuda(args.frames):
+            import torch
+            dev = args.frames.device.index or 0
+            stream = torch.cuda.current_stream(args.frames.device).cuda_stream
+        args.ctx = _lib.Context(dev, stream)
+    return args.ctx
+
+
+def _shape_dtype(frames):
+    if _is_torch_cuda(frames):
+        import torch
+        n, c, h, w = frames.shape
+        if frames.dtype == torch.float32:
+            return n, c, h, w, DATA_FLOAT
+        if frames.dtype in (torch.uint16, torch.int16):
+            return n, c, h, w, DATA_USHORT
+        raise TypeError(f"unsupported frame dtype {frames.dtype}")
+    f0 = frames[0]
+    c, h, w = f0.shape
+    dt = DATA_FLOAT if f0.dtype == np.float32 else DATA_USHORT
+    if f0.dtype not in (np.float32, np.uint16):
+        raise TypeError(f"unsupported frame dtype {f0.dtype}")
+    return len(frames), c, h, w, dt
+
+
+def _fill_cargs(args, n, c, is_mean, keep):
+    a = _lib.StackArgs()
+    a.is_mean = int(is_mean)
+    a.type_of_rejection = args.type_of_rejection
+    a.sig[0], a.sig[1] = float(args.sig[0]), float(args.sig[1])
+
+    def arr(x, dt, count):
+        if x is None:
+            return None
+        x = np.ascontiguousarray(x, dtype=dt).reshape(-1)
+        if x.size != count:
+            raise ValueError(f"array has {x.size} entries, expected {count}")
+        keep.append(x)
+        return x.ctypes.data_as(C.c_void_p)
+    if is_mean and args.type_of_rejection == GESDT:
+        if args.critical_value is None:   # stack_mean_or_median computes it itself (:1479-1486)
+            args.critical_value = gesdt_critical_values(n, args.sig[0], args.sig[1])
+        a.critical_value = arr(args.critical_value, np.float32, len(args.critical_value))
+    a.normalize = args.normalize
+    if args.normalize != NO_NORM:
+        a.scale = arr(args.coeff.scale, np.float64, n * c)
+        a.offset = arr(args.coeff.offset, np.float64, n * c)
+        a.mul = arr(args.coeff.mul, np.float64, n * c)
+    # the median path ignores weights (src/core/command.c:11514-11515, 11660)
+    if is_mean and args.weighting_type != NO_WEIGHT:
+        if args.weights is None:
+            _compute_weights(args, n, c)
+        a.weights = arr(args.weights, np.float64, n * c)
+    a.shiftx = arr(args.shiftx, np.int32, n)
+    a.output_norm = int(args.output_norm)
+    a.use_32bit_output = int(args.use_32bit_output)
+    a.create_rejmaps = int(args.create_rejmaps)
+    a.merge_lowhigh_rejmaps = int(args.merge_lowhigh_rejmaps)
+    a.engine = args.engine
+    return a
+
+
+def _compute_weights(args, n, c):
+    """median_and_mean.c:1519-1539; only NOISE_WEIGHT can be derived from the frames themselves"""
+    if args.weighting_type != NOISE_WEIGHT:
+        raise _lib.SgpuError(ST_GENERIC_ERROR, "weights for this weighting type come from registration data: pass args.weights")
+    if args.normalize == NO_NORM or args.bgnoise is None:
+        # src/core/command.c:11700-11703: noise weighting needs normalization statistics
+        raise _lib.SgpuError(ST_GENERIC_ERROR, "Weighting by noise requires normalization")
+    scale = np.ascontiguousarray(args.coeff.scale, dtype=np.float64).reshape(c, n)
+    bg = np.ascontiguousarray(args.bgnoise, dtype=np.float64).reshape(c, n)
+    w = np.zeros((c, n), dtype=np.float64)
+    rv = _lib.lib().sgpu_noise_weights(c, n, scale.ctypes.data_as(C.c_void_p), bg.ctypes.data_as(C.c_void_p),
+                                       w.ctypes.data_as(C.c_void_p))
+    if rv:
+        raise _lib.SgpuError(rv, "sgpu_noise_weights")
+    args.weights = w
+
+
+def stack_mean_or_median(args: StackingArgs, is_mean: bool) -> int:
+    """stack_mean_or_median (median_and_mean.c:1261-1826) on the GPU."""
+    L = _lib.lib()
+    ctx = _context(args)
+    n, c, h, w, dt = _shape_dtype(args.frames)
+    keep = []
+    try:
+        ca = _fill_cargs(args, n, c, is_mean, keep)
+    except _lib.SgpuError as e:
+        args.retval = e.code
+        return e.code
+    desc = _lib.BlockDesc(n, c, w, h, dt)
+    out32 = bool(args.use_32bit_output)
+    nmaps = (1 if args.merge_lowhigh_rejmaps else 2) if (is_mean and args.create_rejmaps) else 0
+    res = StackResult()
+    if _is_torch_cuda(args.frames):
+        import torch
+        dev = args.frames.device
+        frames = args.frames.contiguous()
+        blk = C.c_void_p()
+        shifted = args.shifty is not None and np.any(np.asarray(args.shifty) != 0)
+        if shifted:     # the reference applies the y shift when it loads the block (:407-448)
+            ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
+            es = frames.element_size()
+            for f in range(n):
+                ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0,
+                                                    int(args.shifty[f])))
+        else:
+            ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
+        try:
+            out = torch.empty((c, h, w), dtype=torch.float32 if out32 else torch.uint16, device=dev)
+            rl = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if nmaps >= 1 else None
+            rh = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if nmaps == 2 else None
+            irej = torch.zeros(6, dtype=torch.int64, device=dev)
+            rv = L.sgpu_stack_block(ctx.h, blk, C.byref(ca), C.c_void_p(out.data_ptr()),
+                                    C.c_void_p(rl.data_ptr()) if rl is not None else None,
+                                    C.c_void_p(rh.data_ptr()) if rh is not None else None,
+                                    C.c_void_p(irej.data_ptr()))
+            if rv == 0 and out32 and args.output_norm:   # :1774-1775
+                mm = (C.c_float * 2)()
+                rv = L.sgpu_minmax_nonzero(ctx.h, C.c_void_p(out.data_ptr()), out.numel(), 1, mm)
+                if rv == 0:
+                    rv = L.sgpu_rescale_0_1(ctx.h, C.c_void_p(out.data_ptr()), out.numel(), mm[0], mm[1])
+            if rv:
+                args.retval = rv
+                args.error = (L.sgpu_last_error(ctx.h) or b"").decode()
+                return rv
+            res.data, res.rejmap_low, res.rejmap_high = out, rl, rh
+            res.irej = irej.cpu().numpy().astype(np.uint64).reshape(3, 2)
+        finally:
+            ctx.synchronize()
+            L.sgpu_block_destroy(blk)
+    else:
+        frames = [np.ascontiguousarray(f) for f in args.frames]
+        ptrs = (C.c_void_p * n)(*[f.ctypes.data_as(C.c_void_p) for f in frames])
+        out = np.empty((c, h, w), dtype=np.float32 if out32 else np.uint16)
+        rl = np.zeros((c, h, w), dtype=np.uint16) if nmaps >= 1 else None
+        rh = np.zeros((c, h, w), dtype=np.uint16) if nmaps == 2 else None
+        irej = np.zeros(6, dtype=np.uint64)
+        sy = None
+        if args.shifty is not None:
+            sy = np.ascontiguousarray(args.shifty, dtype=np.int32)
+            keep.append(sy)
+        rv = L.sgpu_stack_host(ctx.h, C.byref(desc), ptrs, sy.ctypes.data_as(C.c_void_p) if sy is not None else None,
+                               C.byref(ca), out.ctypes.data_as(C.c_void_p),
+                               rl.ctypes.data_as(C.c_void_p) if rl is not None else None,
+                               rh.ctypes.data_as(C.c_void_p) if rh is not None else None,
+                               irej.ctypes.data_as(C.c_void_p))
+        if rv:
+            args.retval = rv
+            args.error = (L.sgpu_last_error(ctx.h) or b"").decode()
+            return rv
+        res.data, res.rejmap_low, res.rejmap_high, res.irej = out, rl, rh, irej.reshape(3, 2)
+    args.result = res
+    # the callee frees coeff and weights (median_and_mean.c:1799-1805); mirrored as "consumed"
+    args.retval = ST_OK
+    return ST_OK
+
+
+def stack_mean_with_rejection(args: StackingArgs) -> int:
+    return stack_mean_or_median(args, True)
+
+
+def stack_median(args: StackingArgs) -> int:
+    return stack_mean_or_median(args, False)
+
+
+def image_stats(ctx, plane, lite=False):
+    """statistics(..., STATS_NORM | STATS_LITENORM) of one plane (torch CUDA tensor or numpy)."""
+    L = _lib.lib()
+    st = _lib.ImStats()
+    if _is_torch_cuda(plane):
+        import torch
+        plane = plane.contiguous()
+        ny, nx = plane.shape
+        dt = DATA_FLOAT if plane.dtype == torch.float32 else DATA_USHORT
+        ctx.check(L.sgpu_image_stats(ctx.h, C.c_void_p(plane.data_ptr()), 1, dt, nx, ny, int(lite), C.byref(st)))
+    else:
+        plane = np.ascontiguousarray(plane)
+        ny, nx = plane.shape
+        dt = DATA_FLOAT if plane.dtype == np.float32 else DATA_USHORT
+        ctx.check(L.sgpu_image_stats(ctx.h, plane.ctypes.data_as(C.c_void_p), 0, dt, nx, ny, int(lite), C.byref(st)))
+    return st
+
+
+def compute_estimators(args: StackingArgs, frame_indices=None):
+    """_compute_estimators_for_image over the given frames (all by default): returns
+    (offset, mul, scale, bgnoise) arrays [C][N] holding ESTIMATORS (normalization.c:98-141)."""
+    L = _lib.lib()
+    ctx = _context(args)
+    n, c, h, w, dt = _shape_dtype(args.frames)
+    off = np.zeros((c, n)); mul = np.ones((c, n)); sc = np.ones((c, n)); bg = np.zeros((c, n))
+    for f in (range(n) if frame_indices is None else frame_indices):
+        for layer in range(c):
+            st = image_stats(ctx, args.frames[f][layer], args.lite_norm)
+            o, m, s = C.c_double(), C.c_double(), C.c_double()
+            L.sgpu_estimators_from_stats(args.normalize, int(args.lite_norm), C.byref(st), C.byref(o), C.byref(m), C.byref(s))
+            off[layer, f], mul[layer, f], sc[layer, f], bg[layer, f] = o.value, m.value, s.value, st.bgnoise
+    return off, mul, sc, bg
+
+
+def finalize_factors(args: StackingArgs, off, mul, sc):
+    L = _lib.lib()
+    c, n = off.shape
+    off, mul, sc = (np.ascontiguousarray(a, dtype=np.float64) for a in (off, mul, sc))
+    rv = L.sgpu_compute_factors(args.normalize, c, n, args.ref_image, args.reglayer, int(args.equalizeRGB),
+                                off.ctypes.data_as(C.c_void_p), mul.ctypes.data_as(C.c_void_p), sc.ctypes.data_as(C.c_void_p))
+    if rv:
+        raise _lib.SgpuError(rv, "sgpu_compute_factors")
+    args.coeff = NormCoeff(offset=off, mul=mul, scale=sc)
+
+
+def do_normalization(args: StackingArgs) -> int:
+    """do_normalization (normalization.c:46-78) -> compute_normalization (:217-294)."""
+    if args.normalize == NO_NORM:
+        return ST_OK
+    try:
+        off, mul, sc, bg = compute_estimators(args)
+        args.bgnoise = bg
+        finalize_factors(args, off, mul, sc)
+    except _lib.SgpuError as e:
+        args.retval = e.code
+        return e.code
+    return ST_OK
+
+
+def main_stack(args: StackingArgs) -> int:
+    """main_stack (stacking.c:76-108): 1. normalization 2. (upscale: not on this path) 3. stack"""
+    if args.coeff.scale is None or args.force_norm:
+        args.retval = do_normalization(args)
+        if args.retval:
+            return args.retval
+    args.retval = args.method(args)
+    return args.retval

@@ -1,0 +1,86 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/sgpu.h declares,
+its host-side scalar helpers match the oracle, and compute fails loudly without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported():
+    from siril_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "sgpu.h")).read()
+    declared = set(re.findall(r"\b(sgpu_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"sgpu_last_error"} - set(_lib.SIGNATURES)
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    L = _lib.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.sgpu_abi_version() == 1
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from siril_b200 import _lib
+    with pytest.raises(_lib.SgpuError):
+        _lib.Context(0)
+
+
+def test_product_does_not_touch_oracle():
+    """the product path must never import / link / call the oracle"""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "siril_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")) or fn == "Makefile":
+                txt = open(os.path.join(dirpath, fn), errors="ignore").read()
+                for needle in ("liborc", "libsiril_ref", "from oracle", "import oracle", "oracle/"):
+                    assert needle not in txt, (fn, needle)
+
+
+def test_planner_matches_oracle(orc):
+    from siril_b200 import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(4)
+    for _ in range(200):
+        W, H = int(rng.integers(16, 9000)), int(rng.integers(16, 7000))
+        Cn = int(rng.choice([1, 3]))
+        thr = int(rng.integers(1, 33))
+        mr = int(rng.integers(1, 3 * H * Cn))
+        rv_o, blocks_o, largest_o = orc.planner(mr, W, H, Cn, thr)
+        blocks = (_lib.ImageBlock * 4096)()
+        naxes = (C.c_long * 3)(W, H, Cn)
+        largest, nb = C.c_long(0), C.c_int(0)
+        rv = L.sgpu_compute_parallel_blocks(blocks, 4096, mr, naxes, thr, C.byref(largest), C.byref(nb))
+        assert (rv == 0) == (rv_o == 0)
+        if rv == 0:
+            got = np.array([[b.channel, b.start_row, b.end_row, b.height] for b in blocks[:nb.value]])
+            assert np.array_equal(got, blocks_o) and largest.value == largest_o
+
+
+def test_factors_and_weights_match_oracle(orc):
+    from siril_b200 import _lib
+    from oracle import oracle as O
+    L = _lib.lib()
+    rng = np.random.default_rng(6)
+    for Cn in (1, 3):
+        N = 11
+        off, mul, sc = (rng.uniform(0.05, 0.2, (Cn, N)) for _ in range(3))
+        sc[0, 3] = 0.0
+        mul[Cn - 1, 5] = 0.0
+        for nrm in (O.ADDITIVE, O.MULTIPLICATIVE, O.ADDITIVE_SCALING, O.MULTIPLICATIVE_SCALING):
+            for eq in (False, True):
+                exp = orc.compute_factors(nrm, off, mul, sc, 2, reglayer=-1 if Cn == 1 else 1, equalize_rgb=eq and Cn == 3)
+                a, b, c = (np.array(x, copy=True) for x in (off, mul, sc))
+                rv = L.sgpu_compute_factors(nrm, Cn, N, 2, -1 if Cn == 1 else 1, int(eq and Cn == 3),
+                                            a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p))
+                assert rv == 0
+                for x, y in zip((a, b, c), exp):
+                    assert np.array_equal(x, y)
+        s = rng.uniform(0.8, 1.2, (Cn, N)); bg = rng.uniform(1e-3, 2e-3, (Cn, N))
+        w = np.zeros((Cn, N))
+        assert L.sgpu_noise_weights(Cn, N, s.ctypes.data_as(C.c_void_p), bg.ctypes.data_as(C.c_void_p), w.ctypes.data_as(C.c_void_p)) == 0
+        assert np.array_equal(w, orc.noise_weights(s, bg))
