@@ -68,7 +68,9 @@ int sgpu_abi_version(void);
 /* one context per GPU / per process rank; `device` is the CUDA ordinal */
 int sgpu_ctx_create(int device, sgpu_ctx **ctx);
 void sgpu_ctx_destroy(sgpu_ctx *ctx);
-/* run all work of this context on a caller-owned cudaStream_t (NULL: the context's own stream) */
+/* Run all work of this context on a caller-owned cudaStream_t.  NULL means CUDA's legacy default
+ * stream (the runtime API's convention), not "none": a context that is never given a stream uses a
+ * private non-blocking stream of its own. */
 int sgpu_ctx_set_stream(sgpu_ctx *ctx, void *cuda_stream);
 int sgpu_ctx_synchronize(sgpu_ctx *ctx);
 const char *sgpu_last_error(const sgpu_ctx *ctx);

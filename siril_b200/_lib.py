@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsgpu.so")
+LIB_PATH = os.environ.get("SGPU_LIB") or os.path.join(HERE, "libsgpu.so")
 
 
 class SgpuError(RuntimeError):

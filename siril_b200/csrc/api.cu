@@ -71,7 +71,7 @@ void sgpu_ctx_destroy(sgpu_ctx *ctx) {
 
 int sgpu_ctx_set_stream(sgpu_ctx *ctx, void *s) {
 	if (!ctx) return SGPU_GENERIC_ERROR;
-	ctx->stream = s ? (cudaStream_t) s : ctx->own_stream;
+	ctx->stream = (cudaStream_t) s;	/* NULL is CUDA's legacy default stream, as everywhere in the runtime API */
 	return SGPU_OK;
 }
 

@@ -15,6 +15,8 @@
 #include <cfloat>
 #include <cuda_runtime.h>
 
+#define SGPU_HD __host__ __device__
+
 namespace sgpu {
 
 typedef uint16_t u16;
@@ -23,8 +25,8 @@ typedef uint16_t u16;
 template <typename T>
 struct Col {
 	T *p; int s;
-	__device__ __forceinline__ T get(int i) const { return p[(unsigned) i * (unsigned) s]; }
-	__device__ __forceinline__ void set(int i, T v) const { p[(unsigned) i * (unsigned) s] = v; }
+	SGPU_HD __forceinline__ T get(int i) const { return p[(unsigned) i * (unsigned) s]; }
+	SGPU_HD __forceinline__ void set(int i, T v) const { p[(unsigned) i * (unsigned) s] = v; }
 };
 
 struct RejCfg {
@@ -32,26 +34,26 @@ struct RejCfg {
 };
 
 // ---- rounding helpers (src/core/proto.h:208-237, 324-346) ----
-__device__ __forceinline__ u16 round_to_word(double x) {
+SGPU_HD __forceinline__ u16 round_to_word(double x) {
 	x += 0.5; x = x > 65535.0 ? 65535.0 : x; x = x < 0.0 ? 0.0 : x; return (u16) x;
 }
-__device__ __forceinline__ u16 roundf_to_word(float f) {
+SGPU_HD __forceinline__ u16 roundf_to_word(float f) {
 	f += 0.5f; f = f > 65535.f ? 65535.f : f; f = f < 0.f ? 0.f : f; return (u16) f;
 }
-__device__ __forceinline__ int round_to_int_d(double x) {
+SGPU_HD __forceinline__ int round_to_int_d(double x) {
 	x = x > 2147483646.5 ? 2147483646.5 : x; x = x < -2147483647.5 ? -2147483647.5 : x;
 	return (int) (x + (x >= 0.0 ? 0.5 : -0.5));
 }
-__device__ __forceinline__ u16 truncate_to_word(int x) { x = x < 0 ? 0 : x; x = x > 65535 ? 65535 : x; return (u16) x; }
+SGPU_HD __forceinline__ u16 truncate_to_word(int x) { x = x < 0 ? 0 : x; x = x > 65535 ? 65535 : x; return (u16) x; }
 
-__device__ __forceinline__ float to_f(float v) { return v; }
-__device__ __forceinline__ float to_f(u16 v) { return (float) v; }
+SGPU_HD __forceinline__ float to_f(float v) { return v; }
+SGPU_HD __forceinline__ float to_f(u16 v) { return (float) v; }
 
 // ---- sorting / selection ----
 // ascending in-place sort; the result of a sort is unique so the scheme is free: insertion for
 // short columns, heapsort beyond (sorting.c:110-186 quicksort_f/_s)
 template <typename T>
-__device__ void sort_col(Col<T> a, int n) {
+SGPU_HD void sort_col(Col<T> a, int n) {
 	if (n <= 16) {
 		for (int i = 1; i < n; i++) {
 			T v = a.get(i); int j = i - 1;
@@ -89,16 +91,16 @@ __device__ void sort_col(Col<T> a, int n) {
 // front ends (:366-415, :468-513), reproduced including the permutation left in `a`
 template <typename T> struct MedSmall;
 template <> struct MedSmall<float> {	// float network averages the middles IN FLOAT
-	static __device__ __forceinline__ double even(float x, float y) { return (x + y) / 2.0; }
-	static __device__ __forceinline__ double evenq(float x, float y) { return ((double) x + y) / 2.0; }
+	static SGPU_HD __forceinline__ double even(float x, float y) { return (x + y) / 2.0; }
+	static SGPU_HD __forceinline__ double evenq(float x, float y) { return ((double) x + y) / 2.0; }
 };
 template <> struct MedSmall<u16> {
-	static __device__ __forceinline__ double even(u16 x, u16 y) { return ((int) x + (int) y) / 2.0; }
-	static __device__ __forceinline__ double evenq(u16 x, u16 y) { return ((double) x + (double) y) / 2.0; }
+	static SGPU_HD __forceinline__ double even(u16 x, u16 y) { return ((int) x + (int) y) / 2.0; }
+	static SGPU_HD __forceinline__ double evenq(u16 x, u16 y) { return ((double) x + (double) y) / 2.0; }
 };
 
 template <typename T>
-__device__ double quickmedian_col(Col<T> a, int n) {
+SGPU_HD double quickmedian_col(Col<T> a, int n) {
 	if (n <= 0) return 0.0;
 	const int k = n / 2;
 	if (n < 9) {
@@ -125,8 +127,8 @@ __device__ double quickmedian_col(Col<T> a, int n) {
 // ---- per-stack statistics ----
 // siril_stats_float_sd (statistics.h:82-107); `cl`/`cu` apply the accumulated winsorization
 // clamp on the fly (the reference's w_stack, rejection_float.c:228-236)
-__device__ __forceinline__ float clampw(float v, float lo, float hi) { float t = lo > v ? lo : v; return hi < t ? hi : t; }
-__device__ float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, float cu = FLT_MAX, int off = 0) {
+SGPU_HD __forceinline__ float clampw(float v, float lo, float hi) { float t = lo > v ? lo : v; return hi < t ? hi : t; }
+SGPU_HD float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, float cu = FLT_MAX, int off = 0) {
 	double sum = 0.0, vsum = 0.0;
 	for (int i = 0; i < N; i++) sum += (double) clampw(d.get(off + i), cl, cu);
 	const float mean = (float) (sum / N);
@@ -135,7 +137,7 @@ __device__ float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, floa
 	return sqrtf((float) (vsum / (N - 1)));
 }
 // siril_stats_ushort_sd_32 / _64 (statistics.c:100-127)
-__device__ float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
+SGPU_HD float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
 	unsigned long long isum = 0;
 	for (int i = 0; i < N; i++) { u16 v = d.get(i); v = v < cl ? cl : v; v = v > cu ? cu : v; isum += v; }
 	const float mean = (float) (((double) isum) / ((double) N));
@@ -147,7 +149,7 @@ __device__ float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
 	return sqrtf((float) (acc / (N - 1)));
 }
 // the GESDT-only WORD variant (median_and_mean.c:649-662) on the window [off, off+N)
-__device__ float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
+SGPU_HD float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
 	double acc = 0.0;
 	for (int i = 0; i < N; i++) acc += d.get(off + i);
 	const float mean = (float) (acc / N);
@@ -161,7 +163,7 @@ __device__ float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
 // 79-101, sorting.c:644-649, rt_algo.cc:38-171): approximate median of |x - median| from an
 // n-bin histogram with in-bin interpolation.  `aux` receives the bin index of every sample and
 // is then sorted, which yields the same cumulative counts as the reference's histogram.
-__device__ float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
+SGPU_HD float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
 	const float med = (float) m;
 	float mn = fabsf(d.get(0) - med), mx = mn;
 	for (int i = 1; i < n; i++) { const float v = fabsf(d.get(i) - med); mn = v < mn ? v : mn; mx = mx < v ? v : mx; }
@@ -191,7 +193,7 @@ __device__ float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
 }
 // siril_stats_ushort_mad (statistics.c:133-154): exact median of |x - round(median)| (the
 // 65536-bin histogram median of sorting.c:577-642 is the exact sorted median)
-__device__ float mad_u16(Col<u16> d, int n, double m, Col<u16> aux) {
+SGPU_HD float mad_u16(Col<u16> d, int n, double m, Col<u16> aux) {
 	const int med = round_to_int_d(m);
 	for (int i = 0; i < n; i++) { int v = (int) d.get(i) - med; aux.set(i, (u16) (v < 0 ? -v : v)); }
 	sort_col(aux, n);
@@ -202,7 +204,7 @@ __device__ float mad_u16(Col<u16> d, int n, double m, Col<u16> aux) {
 
 // siril_fit_linear (siril_fit_linear.c:25-48) with xf[i] = 1.f / (i + 1)
 template <typename T>
-__device__ void fit_linear(Col<T> y, float m_x, float m_dx2, int n, float *c0, float *c1) {
+SGPU_HD void fit_linear(Col<T> y, float m_x, float m_dx2, int n, float *c0, float *c1) {
 	float m_y = to_f(y.get(0));
 	for (int i = 1; i < n; i++) m_y += (to_f(y.get(i)) - m_y) * (1.f / (i + 1));
 	float m_dxdy = 0.f, dx = -m_x;
@@ -215,12 +217,12 @@ __device__ void fit_linear(Col<T> y, float m_x, float m_dx2, int n, float *c0, f
 }
 
 // sigma_clipping_float (rejection_float.c:49-60) / sigma_clipping (median_and_mean.c:608-621)
-__device__ __forceinline__ int sclip(float px, float sigma, float lo, float hi, float med, int rej[2]) {
+SGPU_HD __forceinline__ int sclip(float px, float sigma, float lo, float hi, float med, int rej[2]) {
 	if (med - px > sigma * lo) { rej[0]++; return -1; }
 	else if (px - med > sigma * hi) { rej[1]++; return 1; }
 	return 0;
 }
-__device__ __forceinline__ int sclip(u16 px, float sigma, float lo, float hi, float med, int rej[2]) {
+SGPU_HD __forceinline__ int sclip(u16 px, float sigma, float lo, float hi, float med, int rej[2]) {
 	if (med - px > lo * sigma) { rej[0]++; return -1; }
 	else if (px - med > hi * sigma) { rej[1]++; return 1; }
 	return 0;
@@ -228,7 +230,7 @@ __device__ __forceinline__ int sclip(u16 px, float sigma, float lo, float hi, fl
 
 // the shared "clip with the N - r <= 4 guard, compact in place" pass of SIGMA / MAD / WINSORIZED
 template <typename T>
-__device__ __forceinline__ int clip_pass(Col<T> st, int N, int &r, float var, float lo, float hi, float med, int rej[2]) {
+SGPU_HD __forceinline__ int clip_pass(Col<T> st, int N, int &r, float var, float lo, float hi, float med, int rej[2]) {
 	int o = 0;
 	for (int f = 0; f < N; f++) {
 		const T v = st.get(f);
@@ -240,13 +242,13 @@ __device__ __forceinline__ int clip_pass(Col<T> st, int N, int &r, float var, fl
 }
 
 template <typename T> struct Pre { };
-template <> struct Pre<float> { static __device__ __forceinline__ bool need(int t) { return t == 1 || t == 2 || t == 3; } };	// rejection_float.c:147-157
-template <> struct Pre<u16> { static __device__ __forceinline__ bool need(int t) { return t >= 1 && t <= 5; } };		// median_and_mean.c:747-759
+template <> struct Pre<float> { static SGPU_HD __forceinline__ bool need(int t) { return t == 1 || t == 2 || t == 3; } };	// rejection_float.c:147-157
+template <> struct Pre<u16> { static SGPU_HD __forceinline__ bool need(int t) { return t >= 1 && t <= 5; } };		// median_and_mean.c:747-759
 
 // apply_rejection_float / apply_rejection_ushort.  Returns the kept count; `st` holds the kept
 // samples in front exactly as the reference leaves them.
 template <typename T>
-__device__ int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux, int rej[2]) {
+SGPU_HD int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux, int rej[2]) {
 	int N = nb, kept = 0, r = 0, first = 1, changed;
 	for (int f = 0; f < N; f++) { const T v = st.get(f); if (v != (T) 0) { if (f != kept) st.set(kept, v); kept++; } }
 	if (kept <= 1) return kept;
@@ -317,6 +319,9 @@ __device__ int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux,
 					cl = clampw(cl, m0, m1); cu = clampw(cu, m0, m1);
 					sigma0 = sigma;
 					sigma = 1.134f * sd_f32(sf, N, nullptr, cl, cu);
+#ifdef SGPU_DEBUG_WINSOR
+					printf("winsor N=%d med=%.9g m0=%.9g m1=%.9g cl=%.9g cu=%.9g sigma0=%.9g sigma=%.9g\n", N, fmed, m0, m1, cl, cu, sigma0, sigma);
+#endif
 				} while (fabsf(sigma - sigma0) > sigma0 * 0.0005f);
 			} else {
 				Col<u16> sw = { (u16 *) st.p, st.s };
@@ -412,7 +417,7 @@ __device__ int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux,
 // mean_and_reject (median_and_mean.c:956-1101).  `orig(f)` re-reads the normalized sample of
 // frame f (the reference's o_stack copy); w == nullptr is NO_WEIGHT.
 template <typename T, typename OrigFn>
-__device__ double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const double *w, Col<u16> aux,
+SGPU_HD double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const double *w, Col<u16> aux,
 		OrigFn orig, int rej[2]) {
 	const int kept = apply_rejection(st, nb, c, aux, rej);
 	if (kept == 0) return quickmedian_col(st, nb);

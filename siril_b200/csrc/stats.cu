@@ -1,7 +1,431 @@
-// stats.cu — per-image statistics for normalization (K3).  Placeholder until the kernels land.
+// stats.cu — per-image statistics that feed normalization and noise weighting (K3):
+// statistics_internal_float (src/algos/statistics_float.c:281-481) / statistics_internal_ushort
+// (src/algos/statistics.c:233-443) with option STATS_NORM or STATS_LITENORM, i.e.
+//   min/max, ngoodpix/mean/sigma (FnMeanSigma, src/algos/quantize.c:207-317),
+//   bgnoise (FnNoise1, quantize.c:1202-1488), histogram median (src/rt/rt_algo.cc:38-171 for
+//   float, src/algos/sorting.c:577-642 for WORD), MAD, and IKSSlite location/scale
+//   (statistics_float.c:199-229, bwmv :103-127).
+// Every pass is a memory-bound sweep of one plane; integer histograms make the medians
+// independent of the summation order, so they are bit-identical to the CPU; the double sums
+// (mean, sigma, bwmv, row noise) are reduced in a fixed tree order (deterministic run to run)
+// and agree with the sequential CPU sums to ~1e-15 relative.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
 #include "common.cuh"
+
+namespace sgpu {
+
+typedef uint16_t u16;
+static constexpr int NB = 592;		// CTAs per sweep: 4 per SM on 148 SMs
+static constexpr int NT = 256;
+
+__device__ __forceinline__ float ldf(const float *p, size_t i, float) { return p[i]; }
+__device__ __forceinline__ float ldf(const u16 *p, size_t i, float inv) { return (float) p[i] * inv; }
+
+// block-wide reduction in a fixed order (xor tree inside each warp, then warps 0..n-1 in turn);
+// every thread returns the result
+template <typename V, typename Op>
+__device__ __forceinline__ V block_reduce(V v, Op op, V *sh) {
+	for (int o = 16; o; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+	if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+	__syncthreads();
+	V acc = sh[0];
+	for (int k = 1; k < (int) (blockDim.x >> 5); k++) acc = op(acc, sh[k]);
+	__syncthreads();
+	return acc;
+}
+
+struct BasicPartial {
+	double sum, sum2;
+	unsigned long long ngood, isum, isum2;
+	float mn, mx, nzmn, nzmx;
+};
+
+// pass A: min/max of all (non-NaN) samples, count/sum/sum2 and min/max of the non-null ones
+template <typename T>
+__global__ void basic_kernel(const T *d, size_t n, BasicPartial *out) {
+	__shared__ double shd[32]; __shared__ float shf[32]; __shared__ unsigned long long shu[32];
+	double sum = 0, sum2 = 0; unsigned long long ng = 0, is = 0, is2 = 0;
+	float mn = FLT_MAX, mx = -FLT_MAX, nzmn = FLT_MAX, nzmx = -FLT_MAX;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		const T raw = d[i];
+		const float v = (float) raw;
+		if (sizeof(T) == 4 && v != v) continue;
+		mn = fminf(mn, v); mx = fmaxf(mx, v);
+		if (raw != (T) 0) {
+			ng++; nzmn = fminf(nzmn, v); nzmx = fmaxf(nzmx, v);
+			if (sizeof(T) == 4) { const double x = (double) v; sum += x; sum2 += x * x; }
+			else { const unsigned long long x = (unsigned long long) raw; is += x; is2 += x * x; }
+		}
+	}
+	auto addd = [](double a, double b) { return a + b; };
+	auto addu = [](unsigned long long a, unsigned long long b) { return a + b; };
+	auto fmn = [](float a, float b) { return fminf(a, b); };
+	auto fmx = [](float a, float b) { return fmaxf(a, b); };
+	sum = block_reduce(sum, addd, shd); sum2 = block_reduce(sum2, addd, shd);
+	ng = block_reduce(ng, addu, shu); is = block_reduce(is, addu, shu); is2 = block_reduce(is2, addu, shu);
+	mn = block_reduce(mn, fmn, shf); mx = block_reduce(mx, fmx, shf);
+	nzmn = block_reduce(nzmn, fmn, shf); nzmx = block_reduce(nzmx, fmx, shf);
+	if (threadIdx.x == 0) out[blockIdx.x] = BasicPartial{ sum, sum2, ng, is, is2, mn, mx, nzmn, nzmx };
+}
+
+// selection predicate + transform shared by the min/max, histogram and bwmv sweeps:
+// sample is used when non-null (and inside [lo, hi] when ranged); value = x or |x - c|
+struct Sel { int ranged; float lo, hi; int absdev; float c; float inv; };
+
+template <typename T>
+__device__ __forceinline__ bool sel_value(const T *d, size_t i, const Sel &s, float &val, float &x) {
+	const T raw = d[i];
+	if (raw == (T) 0) return false;
+	x = ldf(d, i, s.inv);
+	if (x != x) return false;
+	if (s.ranged && !(x >= s.lo && x <= s.hi)) return false;
+	val = s.absdev ? fabsf(x - s.c) : x;
+	return true;
+}
+
+struct MMPartial { float mn, mx; unsigned long long cnt; };
+
+template <typename T>
+__global__ void minmax_sel_kernel(const T *d, size_t n, Sel s, MMPartial *out) {
+	__shared__ float shf[32]; __shared__ unsigned long long shu[32];
+	float mn = FLT_MAX, mx = -FLT_MAX; unsigned long long cnt = 0;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		float v, x;
+		if (!sel_value(d, i, s, v, x)) continue;
+		mn = fminf(mn, v); mx = fmaxf(mx, v); cnt++;
+	}
+	mn = block_reduce(mn, [](float a, float b) { return fminf(a, b); }, shf);
+	mx = block_reduce(mx, [](float a, float b) { return fmaxf(a, b); }, shf);
+	cnt = block_reduce(cnt, [](unsigned long long a, unsigned long long b) { return a + b; }, shu);
+	if (threadIdx.x == 0) out[blockIdx.x] = MMPartial{ mn, mx, cnt };
+}
+
+// histogram of (uint16_t)(scale * (val - mn)) — findMinMaxPercentile's binning (rt_algo.cc:99)
+template <typename T>
+__global__ void hist_float_kernel(const T *d, size_t n, Sel s, float mn, float scale, unsigned *hist) {
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		float v, x;
+		if (!sel_value(d, i, s, v, x)) continue;
+		const unsigned bin = (unsigned) (u16) (scale * (v - mn));
+		atomicAdd(&hist[bin], 1u);
+	}
+}
+
+// exact histogram of WORD samples, or of |x - med| (siril_stats_ushort_mad, statistics.c:133-154)
+__global__ void hist_u16_kernel(const u16 *d, size_t n, int absdev, int med, unsigned *hist) {
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		const u16 raw = d[i];
+		if (raw == 0) continue;
+		int v = raw;
+		if (absdev) { v -= med; v = v < 0 ? -v : v; v &= 0xffff; }
+		atomicAdd(&hist[v], 1u);
+	}
+}
+
+struct BwPartial { double up, down; };
+// siril_stats_float_bwmv (statistics_float.c:103-127)
+template <typename T>
+__global__ void bwmv_kernel(const T *d, size_t n, Sel s, float median, float factor, BwPartial *out) {
+	__shared__ double shd[32];
+	double up = 0, down = 0;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		float v, x;
+		if (!sel_value(d, i, s, v, x)) continue;
+		const float im = x - median;
+		const float yi = im * factor;
+		const float yi2 = fabsf(yi) < 1.f ? yi * yi : 1.f;
+		const float q = 1 - yi2;
+		const float t = im * (q * q);
+		up += (double) (t * t);
+		down += (double) (q * (1 - 5 * yi2));
+	}
+	auto addd = [](double a, double b) { return a + b; };
+	up = block_reduce(up, addd, shd); down = block_reduce(down, addd, shd);
+	if (threadIdx.x == 0) out[blockIdx.x] = BwPartial{ up, down };
+}
+
+// FnNoise1_float / FnNoise1_ushort (quantize.c:1343-1488 / :1202-1341), one CTA per row:
+// first differences of consecutive valid pixels, then <= 3 passes of 5-sigma clipping of the
+// differences around their mean; row value = sigma, or -1 when the row yields < 2 differences.
+template <typename T>
+__global__ void noise_rows_kernel(const T *d, long nx, long ny, double *rowsd) {
+	extern __shared__ unsigned char sm[];
+	float *vals = (float *) sm;				// nx floats: valid pixels, then differences
+	unsigned char *keep = (unsigned char *) (vals + nx);
+	__shared__ int cnts[NT + 1];
+	__shared__ double shd[32]; __shared__ unsigned long long shu[32];
+	auto addd = [](double a, double b) { return a + b; };
+	auto addu = [](unsigned long long a, unsigned long long b) { return a + b; };
+	for (long row = blockIdx.x; row < ny; row += gridDim.x) {
+		const T *rp = d + row * nx;
+		const int chunk = (int) ((nx + NT - 1) / NT);
+		const long b0 = (long) threadIdx.x * chunk, b1 = b0 + chunk < nx ? b0 + chunk : nx;
+		int c = 0;
+		for (long i = b0; i < b1; i++) { const float v = (float) rp[i]; if (rp[i] != (T) 0 && v == v) c++; }
+		cnts[threadIdx.x + 1] = c;
+		if (threadIdx.x == 0) cnts[0] = 0;
+		__syncthreads();
+		if (threadIdx.x == 0) for (int k = 1; k <= NT; k++) cnts[k] += cnts[k - 1];
+		__syncthreads();
+		int o = cnts[threadIdx.x];
+		const int M = cnts[NT];
+		for (long i = b0; i < b1; i++) { const float v = (float) rp[i]; if (rp[i] != (T) 0 && v == v) vals[o++] = v; }
+		__syncthreads();
+		const int nd = M - 1;					// number of differences
+		// differences in place, in batches: read the pairs, barrier, write (no read/write hazard)
+		for (int base = 0; base < nd; base += NT * 8) {
+			float tmp[8];
+			#pragma unroll
+			for (int k = 0; k < 8; k++) { const int i = base + k * NT + threadIdx.x; tmp[k] = i < nd ? vals[i] - vals[i + 1] : 0.f; }
+			__syncthreads();
+			#pragma unroll
+			for (int k = 0; k < 8; k++) { const int i = base + k * NT + threadIdx.x; if (i < nd) { vals[i] = tmp[k]; keep[i] = 1; } }
+			__syncthreads();
+		}
+		if (nd < 2) { if (threadIdx.x == 0) rowsd[row] = -1.0; __syncthreads(); continue; }
+		double mean = 0, stdev = 0;
+		unsigned long long nv = nd;
+		for (int iter = 0; iter <= 3; iter++) {
+			double s = 0, s2 = 0; unsigned long long kk = 0;
+			for (int i = threadIdx.x; i < nd; i += NT) {
+				if (!keep[i]) continue;
+				if (iter > 0) {
+					const float dv = vals[i];
+					const double dev = (sizeof(T) == 4) ? fabs((double) (dv - (float) mean)) : fabs((double) dv - mean);
+					if (!(dev < 5. * stdev)) { keep[i] = 0; continue; }
+				}
+				const double x = (double) vals[i]; s += x; s2 += x * x; kk++;
+			}
+			s = block_reduce(s, addd, shd); s2 = block_reduce(s2, addd, shd); kk = block_reduce(kk, addu, shu);
+			if (iter > 0 && kk == nv) break;		// nothing clipped: keep previous mean/stdev
+			nv = kk;
+			if (nv > 1) { mean = s / (double) nv; stdev = sqrt((s2 / (double) nv) - (mean * mean)); }
+			else if (nv == 1) { mean = s; stdev = 0.0; }
+			else { mean = 0.; stdev = 0.; }
+			if (iter == 0 && !(stdev > 0.)) break;
+			__syncthreads();
+		}
+		if (threadIdx.x == 0) rowsd[row] = stdev;
+		__syncthreads();
+	}
+}
+
+}  // namespace sgpu
+
+using namespace sgpu;
+
+namespace {
+
+struct Sweep {
+	sgpu_ctx *ctx; const void *d; int dtype; size_t n;
+	unsigned *d_hist; void *d_part; void *h_part;
+};
+
+// rt_algo.cc:112-138 on a finished histogram (minPrct = maxPrct = 0.5, outputs aliased)
+float finish_hist_median_float(const unsigned *histo, size_t n, float mn, float mx, float scale) {
+	size_t k = 0, count = 0;
+	const float thresh = 0.5f * n;
+	while (count < thresh) count += histo[k++];
+	float v;
+	if (k > 0) {
+		const size_t count_ = count - histo[k - 1];
+		const float c0 = count - thresh;
+		const float c1 = thresh - count_;
+		v = (c1 * k + c0 * (k - 1)) / (c0 + c1);
+	} else v = k;
+	v /= scale; v += mn;
+	{ const float t = v < mx ? v : mx; v = mn < t ? t : mn; }
+	return v;
+}
+
+// sorting.c:624-641 on a finished 65536-bin histogram
+double finish_hist_median_u16(const unsigned *h, size_t n) {
+	unsigned i = 0, j = 0, k = (unsigned) (n / 2), sum = 0;
+	if (n % 2 == 0) { for (; sum <= k - 1; j++) sum += h[j]; i = j; }
+	for (; sum <= k; i++) sum += h[i];
+	return (n % 2 == 0) ? (double) (i + j - 2) / 2.0 : (double) (i - 1);
+}
+
+template <typename T>
+int minmax_sel(Sweep &w, const Sel &s, float &mn, float &mx, size_t &cnt) {
+	sgpu_ctx *ctx = w.ctx;
+	minmax_sel_kernel<T><<<NB, NT, 0, ctx->stream>>>((const T *) w.d, w.n, s, (MMPartial *) w.d_part);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(MMPartial), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	const MMPartial *p = (const MMPartial *) w.h_part;
+	mn = FLT_MAX; mx = -FLT_MAX; cnt = 0;
+	for (int i = 0; i < NB; i++) { mn = std::min(mn, p[i].mn); mx = std::max(mx, p[i].mx); cnt += p[i].cnt; }
+	return SGPU_OK;
+}
+
+// histogram_median_float of the selected / transformed samples (sorting.c:644-649)
+template <typename T>
+int hist_median_float(Sweep &w, const Sel &s, float mn, float mx, size_t cnt, float &median) {
+	sgpu_ctx *ctx = w.ctx;
+	if (fabsf(mx - mn) == 0.f) { median = mn; return SGPU_OK; }		// rt_algo.cc:78-81
+	const unsigned hs = (unsigned) std::min<size_t>(65536, cnt);
+	const float scale = (hs - 1) / (mx - mn);
+	SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
+	hist_float_kernel<T><<<NB, NT, 0, ctx->stream>>>((const T *) w.d, w.n, s, mn, scale, w.d_hist);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	std::vector<unsigned> h(65536);
+	SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	median = finish_hist_median_float(h.data(), cnt, mn, mx, scale);
+	return SGPU_OK;
+}
+
+// IKSSlite (statistics_float.c:199-229) on the non-null samples of the plane (converted with
+// `inv` for WORD data, statistics.c:416-426)
+template <typename T>
+int ikss(Sweep &w, float inv, float median, float mad, double &location, double &scale) {
+	sgpu_ctx *ctx = w.ctx;
+	const float xlow = median - 6.0 * mad, xhigh = median + 6.0 * mad;
+	Sel s{ 1, xlow, xhigh, 0, 0.f, inv };
+	float mn, mx; size_t kept;
+	int rv = minmax_sel<T>(w, s, mn, mx, kept); if (rv) return rv;
+	if (kept == 0) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "IKSS: no sample within 6 MAD of the median");
+	float loc;
+	rv = hist_median_float<T>(w, s, mn, mx, kept, loc); if (rv) return rv;
+	location = loc;
+	Sel sa{ 1, xlow, xhigh, 1, (float) location, inv };
+	float amn, amx; size_t c2;
+	rv = minmax_sel<T>(w, sa, amn, amx, c2); if (rv) return rv;
+	float mad2;
+	rv = hist_median_float<T>(w, sa, amn, amx, kept, mad2); if (rv) return rv;
+	if (mad2 == 0.0f) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "MAD is null. Statistics cannot be computed.");
+	double bw = 0.0;
+	if (mad2 > 0.f) {
+		const float factor = 1.f / (9.f * mad2);
+		bwmv_kernel<T><<<NB, NT, 0, ctx->stream>>>((const T *) w.d, w.n, s, (float) location, factor, (BwPartial *) w.d_part);
+		ctx->launches++;
+		SGPU_CUDA(ctx, cudaGetLastError());
+		SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(BwPartial), cudaMemcpyDeviceToHost, ctx->stream));
+		SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+		const BwPartial *p = (const BwPartial *) w.h_part;
+		double up = 0, down = 0;
+		for (int i = 0; i < NB; i++) { up += p[i].up; down += p[i].down; }
+		bw = down ? kept * (up / (down * down)) : 0.0;
+	}
+	scale = sqrt(bw) * .991;
+	return SGPU_OK;
+}
+
+template <typename T>
+int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu_imstats *out) {
+	const size_t n = (size_t) nx * ny;
+	const size_t part_bytes = NB * 64;
+	const size_t need = 65536 * sizeof(unsigned) + part_bytes + (size_t) ny * sizeof(double) + 256;
+	int rv = sgpu_ensure_scratch(ctx, need); if (rv) return rv;
+	Sweep w{ ctx, d, sizeof(T) == 4 ? SGPU_F32 : SGPU_U16, n, (unsigned *) ctx->d_scratch,
+		 (char *) ctx->d_scratch + 65536 * sizeof(unsigned), nullptr };
+	double *d_rows = (double *) ((char *) w.d_part + part_bytes);
+	std::vector<unsigned char> hp(part_bytes);
+	w.h_part = hp.data();
+	memset(out, 0, sizeof(*out));
+
+	// pass A
+	basic_kernel<T><<<NB, NT, 0, ctx->stream>>>(d, n, (BasicPartial *) w.d_part);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(BasicPartial), cudaMemcpyDeviceToHost, ctx->stream));
+	// pass B (bgnoise) queued behind it
+	if (nx >= 3) {
+		const size_t shm = (size_t) nx * 5 + 16;
+		if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rows of %ld pixels do not fit in shared memory", nx);
+		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(noise_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
+		noise_rows_kernel<T><<<(unsigned) std::min<long>(ny, 148 * 8), NT, shm, ctx->stream>>>(d, nx, ny, d_rows);
+		ctx->launches++;
+		SGPU_CUDA(ctx, cudaGetLastError());
+	}
+	std::vector<double> rows(nx >= 3 ? ny : 0);
+	if (nx >= 3) SGPU_CUDA(ctx, cudaMemcpyAsync(rows.data(), d_rows, (size_t) ny * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+	const BasicPartial *bp = (const BasicPartial *) w.h_part;
+	double sum = 0, sum2 = 0; unsigned long long ngood = 0, isum = 0, isum2 = 0;
+	float mn = FLT_MAX, mx = -FLT_MAX, nzmn = FLT_MAX, nzmx = -FLT_MAX;
+	for (int i = 0; i < NB; i++) {
+		sum += bp[i].sum; sum2 += bp[i].sum2; ngood += bp[i].ngood; isum += bp[i].isum; isum2 += bp[i].isum2;
+		mn = std::min(mn, bp[i].mn); mx = std::max(mx, bp[i].mx); nzmn = std::min(nzmn, bp[i].nzmn); nzmx = std::max(nzmx, bp[i].nzmx);
+	}
+	if (sizeof(T) == 2) { sum = (double) isum; sum2 = (double) isum2; }
+	const double normValue = sizeof(T) == 4 ? 1.0 : 65535.0;
+	double mean, sigma;							// quantize.c:293-315
+	if (ngood > 1) { mean = sum / ngood; sigma = sqrt((sum2 / ngood) - (mean * mean)); }
+	else if (ngood == 1) { mean = sum; sigma = 0.0; }
+	else { mean = 0.; sigma = 0.; }
+	double bgnoise = 0.0;							// quantize.c:1470-1484
+	{
+		std::vector<double> v;
+		for (double r : rows) if (r >= 0.0) v.push_back(r);
+		if (v.size() == 1) bgnoise = v[0];
+		else if (v.size() > 1) { std::sort(v.begin(), v.end()); bgnoise = (v[(v.size() - 1) / 2] + v[v.size() / 2]) / 2.; }
+		bgnoise *= .70710678;
+	}
+	out->total = (double) n; out->ngoodpix = (double) ngood; out->mean = mean; out->sigma = sigma;
+	out->min = mn; out->max = mx; out->normValue = normValue; out->bgnoise = bgnoise;
+	if (ngood == 0) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "image has no non-null pixel");	// statistics_float.c:399-403
+
+	double median, mad, location = 0, scale = 0;
+	if (sizeof(T) == 4) {
+		Sel s{ 0, 0.f, 0.f, 0, 0.f, 1.f };
+		float med;
+		rv = hist_median_float<T>(w, s, nzmn, nzmx, ngood, med); if (rv) return rv;
+		median = med;
+		Sel sa{ 0, 0.f, 0.f, 1, med, 1.f };
+		float amn, amx, madf; size_t c;
+		rv = minmax_sel<T>(w, sa, amn, amx, c); if (rv) return rv;
+		rv = hist_median_float<T>(w, sa, amn, amx, ngood, madf); if (rv) return rv;
+		mad = madf;
+		if (!lite) { rv = ikss<T>(w, 1.f, med, madf, location, scale); if (rv) return rv; }
+	} else {
+		std::vector<unsigned> h(65536);
+		for (int pass = 0; pass < 2; pass++) {
+			const int imed = pass ? (int) (median + (median >= 0.0 ? 0.5 : -0.5)) : 0;		// round_to_int
+			SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
+			hist_u16_kernel<<<NB, NT, 0, ctx->stream>>>((const u16 *) d, n, pass, imed, w.d_hist);
+			ctx->launches++;
+			SGPU_CUDA(ctx, cudaGetLastError());
+			SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+			SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+			const double m = finish_hist_median_u16(h.data(), ngood);
+			if (pass == 0) median = m; else mad = (double) (float) m;
+		}
+		if (!lite) {									// statistics.c:409-438
+			const float inv = (float) (1.0 / normValue);
+			const float medf = (float) median * inv, madf = (float) mad * inv;
+			rv = ikss<T>(w, inv, medf, madf, location, scale); if (rv) return rv;
+			location *= normValue; scale *= normValue;
+		}
+	}
+	out->median = median; out->mad = mad; out->location = location; out->scale = scale;
+	return SGPU_OK;
+}
+
+}  // namespace
+
 extern "C" int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny,
 		int lite, sgpu_imstats *out) {
-	(void) plane; (void) on_device; (void) dtype; (void) nx; (void) ny; (void) lite; (void) out;
-	return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "sgpu_image_stats: not built yet");
+	if (!ctx || !plane || !out || nx < 1 || ny < 1) return SGPU_GENERIC_ERROR;
+	if (dtype != SGPU_F32 && dtype != SGPU_U16) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "bad dtype");
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t bytes = (size_t) nx * ny * (dtype == SGPU_F32 ? 4 : 2);
+	void *staged = nullptr;
+	const void *d = plane;
+	if (!on_device) {
+		SGPU_CUDA(ctx, cudaMalloc(&staged, bytes));
+		cudaError_t e = cudaMemcpyAsync(staged, plane, bytes, cudaMemcpyHostToDevice, ctx->stream);
+		if (e != cudaSuccess) { cudaFree(staged); return sgpu_cuda_fail(ctx, e, "upload plane"); }
+		d = staged;
+	}
+	int rv = dtype == SGPU_F32 ? image_stats_impl<float>(ctx, (const float *) d, nx, ny, lite, out)
+				   : image_stats_impl<uint16_t>(ctx, (const uint16_t *) d, nx, ny, lite, out);
+	if (staged) { cudaStreamSynchronize(ctx->stream); cudaFree(staged); }
+	return rv;
 }

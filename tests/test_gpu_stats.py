@@ -1,0 +1,105 @@
+"""GPU parity of the normalization inputs (K3/K4): per-image statistics, estimators, factors and
+noise weights against the oracle.  Histogram-derived quantities (ngoodpix, min, max, median, MAD,
+IKSS location) are order-independent and must be bit-exact; double reductions (mean, sigma,
+bgnoise, IKSS scale) are summed in a different (tree) order than the sequential CPU loop and are
+held to 1e-12 relative."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+EXACT = ("total", "ngoodpix", "min", "max", "median", "mad", "location", "normValue")
+CLOSE = ("mean", "sigma", "bgnoise", "scale")
+
+
+def make_image(rng, H, W, dtype, zeros=0.01):
+    yy, xx = np.mgrid[0:H, 0:W]
+    img = 0.1 + 0.15 * np.exp(-((yy - H / 2) ** 2 + (xx - W / 3) ** 2) / (0.05 * H * W)) + 0.01 * rng.standard_normal((H, W))
+    hot = rng.random((H, W)) < 0.002
+    img[hot] += rng.uniform(0.2, 0.7, hot.sum())
+    img = np.clip(img, 1e-4, 1.0)
+    if zeros:
+        img[rng.random((H, W)) < zeros] = 0
+        img[:3, :] = 0          # black border rows, as registered frames have
+        img[:, -5:] = 0
+    if dtype == np.uint16:
+        return np.round(img * 65535).astype(np.uint16)
+    return img.astype(np.float32)
+
+
+def check(got, exp):
+    for k in EXACT:
+        assert got[k] == exp[k], (k, got[k], exp[k])
+    for k in CLOSE:
+        assert got[k] == pytest.approx(exp[k], rel=1e-12, abs=1e-300), (k, got[k], exp[k])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+@pytest.mark.parametrize("lite", [False, True], ids=["ikss", "lite"])
+@pytest.mark.parametrize("shape", [(64, 96), (257, 1031), (40, 5), (1200, 1600)])
+def test_image_stats(orc, dtype, lite, shape):
+    import siril_b200 as sb
+    from siril_b200.stacking import image_stats
+    rng = np.random.default_rng(shape[0] * 7 + shape[1])
+    img = make_image(rng, *shape, dtype)
+    ctx = sb.Context(0, torch.cuda.current_stream().cuda_stream)
+    exp = orc.image_stats(img, lite)
+    got_host = image_stats(ctx, img, lite).asdict()
+    check(got_host, exp)
+    t = torch.from_numpy(img.view(np.int16) if dtype == np.uint16 else img).cuda()
+    if dtype == np.uint16:
+        t = t.view(torch.uint16)
+    got_dev = image_stats(ctx, t, lite).asdict()
+    assert got_dev == got_host     # deterministic reductions: host-staged and resident agree bit for bit
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+@pytest.mark.parametrize("nrm", [O.ADDITIVE, O.MULTIPLICATIVE, O.ADDITIVE_SCALING, O.MULTIPLICATIVE_SCALING], ids=["add", "mul", "addscale", "mulscale"])
+def test_do_normalization_and_weights(orc, dtype, nrm):
+    """main_stack steps 1+3 end to end: stats -> estimators -> factors (-> noise weights) -> stack"""
+    import siril_b200 as sb
+    rng = np.random.default_rng(17)
+    N, Cn, H, W = 7, 3, 48, 80
+    fr = np.stack([np.stack([make_image(rng, H, W, dtype, zeros=0.005) for _ in range(Cn)]) for _ in range(N)])
+    gains = 1 + 0.2 * rng.random(N)
+    if dtype == np.uint16:
+        fr = np.clip(np.round(fr * gains[:, None, None, None] * 0.8), 0, 65535).astype(np.uint16)
+        dev = torch.from_numpy(fr.view(np.int16)).cuda().view(torch.uint16)
+    else:
+        fr = (fr * gains[:, None, None, None] * 0.8).astype(np.float32)
+        dev = torch.from_numpy(fr).cuda()
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=dev, normalize=nrm, ref_image=2,
+                           type_of_rejection=sb.WINSORIZED, sig=(3, 3), weighting_type=sb.NOISE_WEIGHT,
+                           equalizeRGB=True, reglayer=1, create_rejmaps=True)
+    assert sb.do_normalization(args) == 0
+    # oracle: the same pipeline on the CPU
+    off = np.zeros((Cn, N)); mul = np.ones((Cn, N)); sc = np.ones((Cn, N)); bg = np.zeros((Cn, N))
+    for f in range(N):
+        for l in range(Cn):
+            st = orc.image_stats(fr[f, l], False)
+            bg[l, f] = st["bgnoise"]
+            if nrm in (O.ADDITIVE_SCALING, O.MULTIPLICATIVE_SCALING):
+                sc[l, f] = st["scale"]
+            if nrm in (O.ADDITIVE, O.ADDITIVE_SCALING):
+                off[l, f] = st["location"]
+            else:
+                mul[l, f] = st["location"]
+    eo, em, es = orc.compute_factors(nrm, off, mul, sc, 2, reglayer=1, equalize_rgb=True)
+    for got, exp in ((args.coeff.offset, eo), (args.coeff.mul, em), (args.coeff.scale, es)):
+        assert np.allclose(got, exp, rtol=1e-12, atol=0)
+    np.testing.assert_allclose(args.bgnoise, bg, rtol=1e-12)
+    ew = orc.noise_weights(es, bg)
+    # stack with the GPU's own coefficients on both sides: stacking parity is independent of the
+    # 1e-15 differences in the coefficients
+    coeff = sb.NormCoeff(offset=args.coeff.offset.copy(), mul=args.coeff.mul.copy(), scale=args.coeff.scale.copy())
+    assert args.method(args) == 0
+    np.testing.assert_allclose(args.weights, ew, rtol=1e-11)
+    o = orc.stack(fr, rejection=O.WINSORIZED, sig=(3, 3), normalize=nrm, scale=coeff.scale, offset=coeff.offset, mul=coeff.mul,
+                  weights=args.weights, create_rejmaps=True)
+    out = args.result.data.cpu().numpy()
+    assert np.array_equal(args.result.irej, o["irej"])
+    rel = np.abs(out - o["out"]) / np.maximum(np.abs(o["out"]), 1e-30)
+    assert rel.max() <= 1e-6
