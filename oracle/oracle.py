@@ -3,6 +3,8 @@
 Two interchangeable back-ends with the same Python surface:
   Oracle("port")      -> oracle/liborc.so           (our plain-C restatement, stack_oracle.c)
   Oracle("reference") -> oracle/_ref/libsiril_ref.so (the reference's own sources, build_ref.py)
+  Oracle("reference_fast") -> oracle/_ref/libsiril_ref_fast.so (same sources, -fopenmp incl. the
+                        `omp simd` reductions; used only as the TIMED CPU baseline)
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 import this module.  The product (siril_b200) never does.
@@ -67,7 +69,7 @@ def ensure_built(kind="port"):
         if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
             subprocess.check_call(["make", "-C", HERE, "liborc.so"], stdout=subprocess.DEVNULL)
         return so
-    so = os.path.join(HERE, "_ref", "libsiril_ref.so")
+    so = os.path.join(HERE, "_ref", "libsiril_ref_fast.so" if kind == "reference_fast" else "libsiril_ref.so")
     if not os.path.exists(so) and os.path.isdir("/root/reference"):
         subprocess.check_call(["python3", os.path.join(HERE, "build_ref.py")], stdout=subprocess.DEVNULL)
     return so
