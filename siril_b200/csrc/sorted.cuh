@@ -1,0 +1,372 @@
+// sorted.cuh — rejection and combine on a pixel stack that is ALREADY SORTED ascending (zeros
+// removed in mean mode).  This is "phase B" of the sorted engine (stack_sorted.cu): phase A sorts
+// every pixel stack cooperatively in registers (bitonic network across the lanes of a warp) and
+// parks it in shared memory; phase B then runs one thread per pixel over its sorted stack.
+//
+// What the order buys.  With the stack sorted, every order statistic the reference needs is a
+// lookup: the median (quickmedian_float, sorting.c:240-273) is the middle element(s); the kept
+// set of percentile / sigma / winsorized clipping is a contiguous rank range [a, b) because the
+// reference's float predicates (rejection_float.c:31-60) are monotone in the sample value, so a
+// clip pass is a walk inwards from both ends; linear-fit clipping and GESDT sort the stack
+// themselves (rejection_float.c:262, :311).
+//
+// How identical decisions are kept without the reference's per-element passes.
+//  - clip predicates are evaluated with the reference's own float operations on the boundary
+//    elements, so they are exact given the sigma they are fed;
+//  - the standard deviation (siril_stats_float_sd, statistics.h:82-107: double sum, float mean,
+//    float deviations squared in float, double accumulation, float sqrt) is NOT re-accumulated
+//    element by element: running sums sum(x-K), sum((x-K)^2) are kept in double and down-dated as
+//    samples leave, which gives the real-number sigma to ~1e-15.  The reference's float sigma
+//    differs from it by at most ~3e-7 relative (analysis in DESIGN.md §4.3), so each decision is
+//    taken for BOTH ends of the interval sigma*(1 -+ delta) (delta = 1e-6, plus the float-mean
+//    rounding term); if the two ends disagree on any sample — it sits within 1e-6 relative of a
+//    clip threshold — the pixel is NOT decided here: it is reported as FAST_FALLBACK and redone
+//    by the exact engine (exact.cuh), which replays the reference operation by operation.
+//  - the same fallback takes every pixel whose result depends on the order quickselect leaves
+//    the stack in (the `N - r <= 4` guard regime), the `median == 0` / `kept == 0`
+//    paths whose output is the median of a partially compacted stack, and non-finite samples.
+//  - linear-fit clipping is replayed in float exactly as the reference does it (the sorted
+//    order is canonical there), GESDT uses the down-dated sums with the same interval test on
+//    every Grubbs decision that can change the outcome.
+//
+// Everything is __host__ __device__ so that tests/helpers/sorted_host.cu can run it on the CPU
+// against the oracle.
+#pragma once
+#include "exact.cuh"
+#include "../../include/sgpu.h"
+
+namespace sgpu {
+
+enum { FAST_DONE = 0, FAST_FALLBACK = 1 };
+
+#ifdef SGPU_FAST_DEBUG	// host-side test builds only: why a stack was handed to the exact engine
+static int g_fast_reason = 0;
+SGPU_HD inline void fast_why(int x) {
+#ifndef __CUDA_ARCH__
+	g_fast_reason = x;
+#endif
+}
+#define FAST_WHY(x) fast_why(x)
+#else
+#define FAST_WHY(x) ((void) 0)
+#endif
+
+#define SGPU_DELTA_SD 1.0e-6f	// half-width of the interval put around a float sd
+#define SGPU_DELTA_WS 2.0e-6f	// same for the winsorized sigma (error feeds back through the clamp bounds)
+
+struct FastRes {
+	int status;	// FAST_DONE | FAST_FALLBACK
+	int kept;	// number of samples kept
+	double sum;	// their sum
+	float pmin, pmax;	// their range (the weighted combine re-selects by value, median_and_mean.c:1045-1070)
+};
+
+// sum(x - K) and sum((x - K)^2) in double; K is a sample near the middle of the stack so that the
+// variance below has no cancellation to speak of
+struct Sums {
+	double K, S1, S2;
+	SGPU_HD __forceinline__ void init(float k) { K = (double) k; S1 = 0.0; S2 = 0.0; }
+	SGPU_HD __forceinline__ void add(float x) { const double y = (double) x - K; S1 += y; S2 = fma(y, y, S2); }
+	SGPU_HD __forceinline__ void sub(float x) { const double y = (double) x - K; S1 -= y; S2 = fma(-y, y, S2); }
+	SGPU_HD __forceinline__ double sum(int n) const { return S1 + (double) n * K; }
+	SGPU_HD __forceinline__ double mean(int n) const { return K + S1 / (double) n; }
+	SGPU_HD __forceinline__ double var(int n) const { return (S2 - S1 * S1 / (double) n) / (double) (n - 1); }
+};
+
+// interval [lo, hi] that contains the reference's float sd of the n samples summarised by S;
+// `scale` is the 1.134f of the winsorized estimate (1 otherwise).  false: degenerate, fall back.
+SGPU_HD __forceinline__ bool sd_interval(double var, double mean, int n, float delta, float scale, float *lo, float *hi) {
+	if (!(var >= 0.0)) return false;
+	// the reference subtracts a mean rounded to float: sum (x - m~)^2 = sum (x - m)^2 + n (m - m~)^2
+	const double e = fabs(mean) * 5.9604645e-08;	// >= half an ulp of the float mean
+	const double var_hi = var + e * e * (double) n / (double) (n - 1);
+	const float s_lo = scale * sqrtf((float) var), s_hi = scale * sqrtf((float) var_hi);
+	*lo = s_lo * (1.f - delta); *hi = s_hi * (1.f + delta);
+	return *hi < FLT_MAX;
+}
+
+// quickmedian_float / quickmedian of the rank range [a, a+n) (sorting.c:195-273; n < 9 goes
+// through the sorting networks, whose float version averages the middles in float, :366-415)
+template <bool U16, class Acc>
+SGPU_HD __forceinline__ double median_sorted(const Acc &s, int a, int n) {
+	const int k = n >> 1;
+	if (n & 1) return (double) s(a + k);
+	const float x = s(a + k - 1), y = s(a + k);
+	if (!U16 && n < 9) return (x + y) / 2.0;
+	return ((double) x + (double) y) / 2.0;
+}
+
+template <class Acc>
+SGPU_HD __forceinline__ void finish_range(const Acc &s, int a, int b, const Sums &S, FastRes &o) {
+	o.status = FAST_DONE; o.kept = b - a; o.sum = S.sum(b - a); o.pmin = s(a); o.pmax = s(b - 1);
+}
+
+// ---- NO_REJEC / kept <= 1 -----------------------------------------------------------------------
+template <class Acc>
+SGPU_HD void fast_all(const Acc &s, int n, FastRes &o) {
+	double sum = 0.0;
+	for (int i = 0; i < n; i++) sum += (double) s(i);
+	o.status = FAST_DONE; o.kept = n; o.sum = sum;
+	o.pmin = n ? s(0) : 0.f; o.pmax = n ? s(n - 1) : 0.f;
+}
+
+// ---- PERCENTILE (rejection_float.c:31-44,160-173 / median_and_mean.c:590-603,762-776) ----------
+template <bool U16, class Acc>
+SGPU_HD void fast_percentile(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+	const double median = median_sorted<U16>(s, 0, n);
+	const float medf = (float) median;
+	if (U16 ? (medf == 0.f) : (median == 0.0)) { o.status = FAST_FALLBACK; return; }
+	int a = 0, b = n;
+	if (!U16) {
+		while (a < b && medf - s(a) > medf * c.s0) a++;
+		while (b > a && s(b - 1) - medf > medf * c.s1) b--;
+	} else {
+		while (a < b && (medf - s(a)) / medf > c.s0) a++;
+		while (b > a && (s(b - 1) - medf) / medf > c.s1) b--;
+	}
+	if (a >= b) { o.status = FAST_FALLBACK; return; }	// kept == 0: median of the compacted stack
+	rej[0] += a; rej[1] += n - b;
+	double sum = 0.0;
+	for (int i = a; i < b; i++) sum += (double) s(i);
+	o.status = FAST_DONE; o.kept = b - a; o.sum = sum; o.pmin = s(a); o.pmax = s(b - 1);
+}
+
+// one sigma-clip pass over the kept range [a, b) with the sd known to lie in [slo, shi]:
+// 0 = decided (a2, b2 set), 1 = undecidable here
+template <class Acc>
+SGPU_HD __forceinline__ int clip_range(const Acc &s, int a, int b, float medf, float slo, float shi, float s0, float s1,
+		int *a2o, int *b2o) {
+	int a2 = a, b2 = b;
+	const float tl = shi * s0, th = shi * s1;	// sigma_clipping_float: `sigma * sigmalow`
+	while (a2 < b && medf - s(a2) > tl) a2++;
+	while (b2 > a2 && s(b2 - 1) - medf > th) b2--;
+	if (a2 >= b2) return 1;
+	if (medf - s(a2) > slo * s0 || s(b2 - 1) - medf > slo * s1) return 1;	// the low end of the interval rejects more
+	*a2o = a2; *b2o = b2;
+	return 0;
+}
+
+// ---- SIGMA (rejection_float.c:174-209 / median_and_mean.c:777-813) ------------------------------
+template <bool U16, class Acc>
+SGPU_HD void fast_sigma(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	{
+		const double median = median_sorted<U16>(s, 0, n);
+		if (U16 ? ((float) median == 0.f) : (median == 0.0)) return;
+	}
+	Sums S; S.init(s(n >> 1));
+	for (int i = 0; i < n; i++) S.add(s(i));
+	int a = 0, b = n, r = 0;
+	for (;;) {
+		const int nn = b - a;
+		if (nn - r <= 4) break;		// the guard refuses every rejection of this pass
+		float slo, shi;
+		if (!sd_interval(S.var(nn), S.mean(nn), nn, SGPU_DELTA_SD, 1.f, &slo, &shi)) return;
+		const float medf = (float) median_sorted<U16>(s, a, nn);
+		int a2, b2;
+		if (clip_range(s, a, b, medf, slo, shi, c.s0, c.s1, &a2, &b2)) return;
+		const int K = (a2 - a) + (b - b2);
+		if (K == 0) break;
+		if (nn - r - K < 4) return;	// the guard would cut this pass short: order dependent
+		for (int i = a; i < a2; i++) S.sub(s(i));
+		for (int i = b2; i < b; i++) S.sub(s(i));
+		rej[0] += a2 - a; rej[1] += b - b2; r += K; a = a2; b = b2;
+		if (b - a <= 3) break;
+	}
+	finish_range(s, a, b, S, o);
+}
+
+// ---- WINSORIZED, float samples (rejection_float.c:223-259) --------------------------------------
+template <class Acc>
+SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	Sums S; S.init(s(n >> 1));
+	for (int i = 0; i < n; i++) S.add(s(i));
+	int a = 0, b = n, r = 0;
+	for (;;) {
+		const int nn = b - a;
+		if (nn - r <= 4) break;
+		const double var0 = S.var(nn);
+		if (!(var0 >= 0.0)) return;
+		float sigma = sqrtf((float) var0), sigma0;
+		const float medf = (float) median_sorted<false>(s, a, nn);
+		// w_stack = stack clamped to [cl, cu]; [ia, ib) is the part the clamp leaves alone
+		int ia = a, ib = b, it = 0;
+		Sums In = S;
+		float cl = -FLT_MAX, cu = FLT_MAX;
+		double varw, meanw;
+		for (;;) {
+			const float m0 = medf - 1.5f * sigma, m1 = medf + 1.5f * sigma;
+			const float ncl = clampw(cl, m0, m1), ncu = clampw(cu, m0, m1);
+			if (ncl < cl || ncu > cu) return;	// clamp bounds only ever tighten with sane data
+			cl = ncl; cu = ncu;
+			while (ia < ib && s(ia) < cl) { In.sub(s(ia)); ia++; }
+			while (ib > ia && s(ib - 1) > cu) { ib--; In.sub(s(ib)); }
+			const double yl = (double) cl - In.K, yh = (double) cu - In.K;
+			const double nl = (double) (ia - a), nh = (double) (b - ib);
+			const double W1 = In.S1 + nl * yl + nh * yh;
+			const double W2 = In.S2 + nl * yl * yl + nh * yh * yh;
+			varw = (W2 - W1 * W1 / (double) nn) / (double) (nn - 1);
+			meanw = In.K + W1 / (double) nn;
+			if (!(varw >= 0.0)) return;
+			sigma0 = sigma;
+			sigma = 1.134f * sqrtf((float) varw);
+			const float d = fabsf(sigma - sigma0), thr = sigma0 * 0.0005f;
+			if (fabsf(d - thr) <= 2.f * SGPU_DELTA_WS * sigma0) return;	// convergence test too close to call
+			if (!(d > thr)) break;
+			if (++it > 64) return;
+		}
+		float slo, shi;
+		if (!sd_interval(varw, meanw, nn, SGPU_DELTA_WS, 1.134f, &slo, &shi)) return;
+		int a2, b2;
+		if (clip_range(s, a, b, medf, slo, shi, c.s0, c.s1, &a2, &b2)) return;
+		const int K = (a2 - a) + (b - b2);
+		if (K == 0) break;
+		if (nn - r - K < 4) return;
+		for (int i = a; i < a2; i++) S.sub(s(i));
+		for (int i = b2; i < b; i++) S.sub(s(i));
+		rej[0] += a2 - a; rej[1] += b - b2; r += K; a = a2; b = b2;
+		if (b - a <= 3) break;
+	}
+	finish_range(s, a, b, S, o);
+}
+
+// ---- LINEARFIT (rejection_float.c:260-300 / median_and_mean.c:868-902) --------------------------
+// replayed in float exactly as the reference does: its quicksort leaves the canonical ascending
+// order, which is what `s` already holds (and compaction keeps it), so nothing here depends on
+// anything but the values.  `xf` is the reference's table 1.f / (i + 1) (median_and_mean.c:1493).
+template <class Acc>
+SGPU_HD void fast_linearfit(Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+	int N = n, r = 0, changed;
+	do {
+		float m_y = s(0);
+		for (int i = 1; i < N; i++) m_y += (s(i) - m_y) * (1.f / (i + 1));
+		float m_dxdy = 0.f, dx = -c.m_x;
+		for (int i = 0; i < N; i++, dx += 1.f) {
+			const float dy = s(i) - m_y;
+			m_dxdy += (dx * dy - m_dxdy) * (1.f / (i + 1));
+		}
+		const float a = m_dxdy * c.m_dx2;	// slope
+		const float b = m_y - c.m_x * a;	// intercept
+		float sigma = 0.f;
+		for (int f = 0; f < N; f++) sigma += fabsf(s(f) - (a * f + b));
+		sigma /= (float) N;
+		int out = 0;
+		for (int f = 0; f < N; f++) {
+			const float v = s(f); int flag = 0;
+			if (N - r > 4) {
+				if (a * f + b - v > sigma * c.s0) { rej[0]++; flag = -1; r++; }
+				else if (v - a * f - b > sigma * c.s1) { rej[1]++; flag = 1; r++; }
+			}
+			if (!flag) { if (f != out) s.set(out, v); out++; }
+		}
+		changed = N != out; N = out;
+	} while (changed && N > 3);
+	double sum = 0.0;
+	for (int i = 0; i < N; i++) sum += (double) s(i);
+	o.status = FAST_DONE; o.kept = N; o.sum = sum; o.pmin = N ? s(0) : 0.f; o.pmax = N ? s(N - 1) : 0.f;
+}
+
+// ---- GESDT (rejection_float.c:301-348 / median_and_mean.c:903-948) ------------------------------
+// The reference removes, max_outliers times, whichever end of the sorted window deviates most
+// from the window mean (grubbs_stat, :82-98), records whether G = dev / sd beats the critical
+// value, and confirm_outliers (median_and_mean.c:685-701) then rejects every iteration up to the
+// last one that did (never fewer than two).  The window mean and sd come from the down-dated
+// sums; the quirk that a high-end removal flags index size-1 of the SHRUNK window in the
+// ORIGINAL sorted stack (:333, `out[iter].i = max_index`) is reproduced: after k low removals
+// it flags the element k places below the one it removed.
+template <bool U16, class Acc>
+SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	const int removed = nb - n;
+	double median;
+	if (n & 1) median = (double) s(n / 2);
+	else if (U16) median = ((double) s((n - 1) / 2) + (double) s(n / 2)) / 2.0;
+	else median = (s((n - 1) / 2) + s(n / 2)) / 2.0;	// gsl_stats_float_median_from_sorted_data: float add
+	if (U16) median = (double) (float) median;
+	int max_out = (int) ((float) nb * c.s0);
+	if (removed >= max_out) { fast_all(s, n, o); return; }
+	max_out -= removed;
+	if (2 * max_out >= n || n - max_out < 3) { FAST_WHY(71); return; }	// flagged positions could collide: leave it to the exact engine
+	Sums S; S.init(s(n >> 1));
+	for (int i = 0; i < n; i++) S.add(s(i));
+	const double total = S.sum(n);
+	const bool exact_sums = U16 || (s(0) > 0.f && s(n - 1) <= s(0) * 65536.f && n <= 2048);
+	int lo = 0, clo = 0, chi = 0, first_low = -1;
+	double fsum = 0.0;
+	int last = -1, amb = -1, s_clo = 0, s_chi = 0, s_first_low = -1, s_nl = 0;
+	double s_fsum = 0.0;
+	for (int it = 0, size = n; it < max_out; it++, size--) {
+		// grubbs_stat's mean is (float) (sum / N) with the sum in double.  When every partial sum is
+		// exact in double (samples of one sign within 2^16 of each other, or integers) S.sum() IS
+		// the reference's sum, so the float mean is bit-identical, ties included; otherwise the
+		// reference's own summation order matters whenever the quotient sits on a rounding boundary
+		const double avg_d = S.sum(size) / (double) size;
+		const float avg = (float) avg_d;
+		if (!exact_sums) {
+			const double tiny = fabs(avg_d) * 1e-12;
+			if ((float) (avg_d + tiny) != avg || (float) (avg_d - tiny) != avg) { FAST_WHY(72); return; }
+		}
+		float slo, shi;
+		if (!sd_interval(S.var(size), avg_d, size, SGPU_DELTA_SD, 1.f, &slo, &shi)) { FAST_WHY(73); return; }
+		const float xl = s(lo), xh = s(lo + size - 1);
+		float dev = avg - xl;
+		const float md2 = xh - avg;
+		const bool low_end = !(md2 > dev);
+		if (!low_end) dev = md2;
+		if (it > 1) {
+			const float cr = c.crit[it + removed];
+			if (dev / shi > cr) last = -2;	// certainly an outlier: snapshot below
+			else if (dev / slo > cr) amb = it;
+		}
+		float xrem, xflag;
+		if (low_end) { xrem = xl; xflag = xl; lo++; if (first_low < 0) first_low = it; }
+		else { xrem = xh; xflag = s(n - 1 - it); }
+		S.sub(xrem);
+		if ((double) xrem >= median) chi++; else clo++;
+		fsum += (double) xflag;
+		if (it <= 1 || last == -2) { last = it; s_clo = clo; s_chi = chi; s_fsum = fsum; s_first_low = first_low; s_nl = lo; }
+	}
+	if (amb > last) { FAST_WHY(74); return; }
+	rej[0] += s_clo; rej[1] += s_chi;
+	o.status = FAST_DONE; o.kept = n - (last + 1); o.sum = total - s_fsum;
+	o.pmin = s(s_nl);
+	o.pmax = (s_first_low >= 0) ? s(n - 1 - s_first_low) : s(n - last - 2);
+}
+
+// ---- combine: mean_and_reject (median_and_mean.c:956-1101) on the sorted stack ------------------
+// `s` holds the n non-zero samples ascending; nb is the full stack size; orig(f) re-reads the
+// normalized sample of frame f (the reference's o_stack).  status FAST_FALLBACK: result unset.
+template <bool U16, class Acc, typename OrigFn>
+SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const double *w, OrigFn orig,
+		int rej[2], int *status) {
+	FastRes o; o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
+	if (n == 0) { *status = FAST_DONE; return 0.0; }	// all samples null: median of zeros
+	if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(s, n, o);
+	else switch (c.type) {
+	case SGPU_PERCENTILE: fast_percentile<U16>(s, n, c, rej, o); break;
+	case SGPU_SIGMA: fast_sigma<U16>(s, n, c, rej, o); break;
+	case SGPU_WINSORIZED: if (U16) o.status = FAST_FALLBACK; else fast_winsorized(s, n, c, rej, o); break;
+	case SGPU_LINEARFIT: fast_linearfit(s, n, c, rej, o); break;
+	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, rej, o); break;
+	default: o.status = FAST_FALLBACK; break;	// MAD, SIGMEDIAN: exact engine
+	}
+	*status = o.status;
+	if (o.status != FAST_DONE || o.kept == 0) { *status = FAST_FALLBACK; return 0.0; }
+	if (w) {
+		double sum = 0.0, norm = 0.0;
+		for (int f = 0; f < nb; f++) {
+			const float v = orig(f);
+			if (v >= o.pmin && v <= o.pmax && v != 0.f) { sum += (double) v * w[f]; norm += w[f]; }
+		}
+		if (norm == 0. || sum == 0.) {
+			sum = 0.;
+			for (int f = 0; f < nb; f++) { const float v = orig(f); if (v >= o.pmin && v <= o.pmax && v > 0) sum += (double) v; }
+			return sum / (double) o.kept;
+		}
+		return sum / norm;
+	}
+	return o.sum / (double) o.kept;
+}
+
+}  // namespace sgpu
