@@ -25,6 +25,14 @@ int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes) {
 	return SGPU_OK;
 }
 
+int sgpu_ensure_list(sgpu_ctx *ctx, size_t bytes) {
+	if (bytes <= ctx->d_list_cap) return SGPU_OK;
+	if (ctx->d_list) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->d_list); ctx->d_list = nullptr; ctx->d_list_cap = 0; }
+	SGPU_CUDA(ctx, cudaMalloc(&ctx->d_list, bytes));
+	ctx->d_list_cap = bytes;
+	return SGPU_OK;
+}
+
 extern "C" {
 
 int sgpu_abi_version(void) { return SGPU_ABI_VERSION; }
@@ -64,6 +72,7 @@ void sgpu_ctx_destroy(sgpu_ctx *ctx) {
 	if (ctx->d_params) cudaFree(ctx->d_params);
 	if (ctx->h_params) cudaFreeHost(ctx->h_params);
 	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+	if (ctx->d_list) cudaFree(ctx->d_list);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
 	delete ctx;
@@ -218,6 +227,10 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
 	StackDevParams dp;
 	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
+	// engine: 0 automatic (sorted engine where it applies), 1 exact thread-per-pixel, 2 sorted or fail
+	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
+	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
+		return sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	return sgpu_launch_exact(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 }
 

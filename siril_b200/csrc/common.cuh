@@ -23,6 +23,7 @@ struct sgpu_ctx {
 	void *d_params = nullptr; size_t d_params_cap = 0;
 	void *h_params = nullptr;			// pinned mirror
 	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
+	void *d_list = nullptr; size_t d_list_cap = 0;		// sorted engine: pixels handed to the exact engine
 };
 
 struct sgpu_block {
@@ -39,6 +40,7 @@ struct sgpu_block {
 int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...);
 int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what);
 int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes);
+int sgpu_ensure_list(sgpu_ctx *ctx, size_t bytes);
 
 #define SGPU_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return sgpu_cuda_fail((ctx), e__, #call); } while (0)
 
@@ -50,5 +52,8 @@ struct StackDevParams {
 };
 
 // engines
+bool sgpu_sorted_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
+int sgpu_launch_sorted(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);

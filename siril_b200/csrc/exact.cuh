@@ -128,7 +128,7 @@ SGPU_HD double quickmedian_col(Col<T> a, int n) {
 // siril_stats_float_sd (statistics.h:82-107); `cl`/`cu` apply the accumulated winsorization
 // clamp on the fly (the reference's w_stack, rejection_float.c:228-236)
 SGPU_HD __forceinline__ float clampw(float v, float lo, float hi) { float t = lo > v ? lo : v; return hi < t ? hi : t; }
-SGPU_HD float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, float cu = FLT_MAX, int off = 0) {
+SGPU_HD inline float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, float cu = FLT_MAX, int off = 0) {
 	double sum = 0.0, vsum = 0.0;
 	for (int i = 0; i < N; i++) sum += (double) clampw(d.get(off + i), cl, cu);
 	const float mean = (float) (sum / N);
@@ -137,7 +137,7 @@ SGPU_HD float sd_f32(Col<float> d, int N, float *m, float cl = -FLT_MAX, float c
 	return sqrtf((float) (vsum / (N - 1)));
 }
 // siril_stats_ushort_sd_32 / _64 (statistics.c:100-127)
-SGPU_HD float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
+SGPU_HD inline float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
 	unsigned long long isum = 0;
 	for (int i = 0; i < N; i++) { u16 v = d.get(i); v = v < cl ? cl : v; v = v > cu ? cu : v; isum += v; }
 	const float mean = (float) (((double) isum) / ((double) N));
@@ -149,7 +149,7 @@ SGPU_HD float sd_u16(Col<u16> d, int N, u16 cl = 0, u16 cu = 65535) {
 	return sqrtf((float) (acc / (N - 1)));
 }
 // the GESDT-only WORD variant (median_and_mean.c:649-662) on the window [off, off+N)
-SGPU_HD float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
+SGPU_HD inline float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
 	double acc = 0.0;
 	for (int i = 0; i < N; i++) acc += d.get(off + i);
 	const float mean = (float) (acc / N);
@@ -163,7 +163,7 @@ SGPU_HD float sd_u16_gesdt(Col<u16> d, int off, int N, float *m) {
 // 79-101, sorting.c:644-649, rt_algo.cc:38-171): approximate median of |x - median| from an
 // n-bin histogram with in-bin interpolation.  `aux` receives the bin index of every sample and
 // is then sorted, which yields the same cumulative counts as the reference's histogram.
-SGPU_HD float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
+SGPU_HD inline float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
 	const float med = (float) m;
 	float mn = fabsf(d.get(0) - med), mx = mn;
 	for (int i = 1; i < n; i++) { const float v = fabsf(d.get(i) - med); mn = v < mn ? v : mn; mx = mx < v ? v : mx; }
@@ -193,7 +193,7 @@ SGPU_HD float mad_f32(Col<float> d, int n, double m, Col<u16> aux) {
 }
 // siril_stats_ushort_mad (statistics.c:133-154): exact median of |x - round(median)| (the
 // 65536-bin histogram median of sorting.c:577-642 is the exact sorted median)
-SGPU_HD float mad_u16(Col<u16> d, int n, double m, Col<u16> aux) {
+SGPU_HD inline float mad_u16(Col<u16> d, int n, double m, Col<u16> aux) {
 	const int med = round_to_int_d(m);
 	for (int i = 0; i < n; i++) { int v = (int) d.get(i) - med; aux.set(i, (u16) (v < 0 ? -v : v)); }
 	sort_col(aux, n);

@@ -6,62 +6,41 @@
 // per-frame normalization in double exactly as median_and_mean.c:1644-1686 does, and parks the
 // value in the thread's shared-memory column tile[f][tid] (conflict-free: consecutive threads
 // hit consecutive banks).  The rejection / combine then runs entirely out of shared memory.
-#include "common.cuh"
-#include "exact.cuh"
+//
+// LIST mode: the sorted engine (stack_sorted.cu) hands over the pixels it cannot decide; the same
+// kernel then walks p.list (entries (layer << 30) | pixel, count on the device) grid-stride.
+#include "kparams.cuh"
 
 namespace sgpu {
 
-struct ExactParams {
-	const void *frames;	// [N][C][H][W]
-	int N, C, H, W;
-	int normalize;
-	const double *scale, *offset, *mul, *weights;	// device, [C*N]
-	const int *shiftx;	// device [N] or null
-	RejCfg rc;
-	int is_mean, output_norm, out32, rejmaps;	// rejmaps: 0 none, 1 merged, 2 low+high
-	void *out; u16 *rej_low, *rej_high;
-	unsigned long long *irej;	// [3][2]
-	void *scratch;		// global columns when the tile does not fit in shared memory
-	int use_aux;
-};
-
-// one sample, normalized (median_and_mean.c:1638-1686); x is the pixel's column, `sx` the
-// per-frame shift (0 when none)
 template <typename T>
-__device__ __forceinline__ T load_norm(const ExactParams &p, int f, int layer, size_t pix, int x) {
-	T v = (T) 0;
-	int sxv = p.shiftx ? p.shiftx[f] : 0;
-	const int xs = x - sxv;
-	if (xs >= 0 && xs < p.W) {
-		const T *plane = (const T *) p.frames + ((size_t) f * p.C + layer) * ((size_t) p.H * p.W);
-		v = __ldg(plane + pix - sxv);
+__device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, size_t pix, Col<T> st, Col<u16> aux, int rej[2]) {
+	const size_t npix = (size_t) p.H * p.W;
+	const int x = (int) (pix % p.W);
+	const int N = p.N;
+	int f = 0;
+	for (; f + 4 <= N; f += 4) {	// 4 independent loads in flight per thread
+		const T v0 = load_norm<T>(p, f, layer, pix, x), v1 = load_norm<T>(p, f + 1, layer, pix, x);
+		const T v2 = load_norm<T>(p, f + 2, layer, pix, x), v3 = load_norm<T>(p, f + 3, layer, pix, x);
+		st.set(f, v0); st.set(f + 1, v1); st.set(f + 2, v2); st.set(f + 3, v3);
 	}
-	const int ci = layer * p.N + f;
-	switch (p.normalize) {
-	default: case SGPU_NO_NORM: return v;
-	case SGPU_ADDITIVE: case SGPU_ADDITIVE_SCALING:
-		if (sizeof(T) == 4) {
-			if (v != (T) 0) { const double tmp = (double) v * p.scale[ci]; return (T) (float) (tmp - p.offset[ci]); }
-			return (T) 0;
-		} else {
-			if (v > (T) 0) { const double tmp = (double) v * p.scale[ci]; return (T) round_to_word(tmp - p.offset[ci]); }
-			return (T) 0;
-		}
-	case SGPU_MULTIPLICATIVE: case SGPU_MULTIPLICATIVE_SCALING: {
-		const double tmp = (double) v * p.scale[ci];
-		if (sizeof(T) == 4) return (T) (float) (tmp * p.mul[ci]);
-		return (T) round_to_word(tmp * p.mul[ci]);
+	for (; f < N; f++) st.set(f, load_norm<T>(p, f, layer, pix, x));
+
+	double result;
+	if (p.is_mean) {
+		const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
+		auto orig = [&](int ff) { return load_norm<T>(p, ff, layer, pix, x); };
+		result = mean_and_reject<T>(st, N, p.rc, w, aux, orig, rej);
+	} else {
+		result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
 	}
-	}
+	store_result<T>(p, (size_t) layer * npix + pix, result, rej);
 }
 
-template <typename T, bool SMEM>
-__global__ void __launch_bounds__(256) stack_exact_kernel(const ExactParams p) {
+template <typename T, bool SMEM, bool LIST>
+__global__ void __launch_bounds__(256) stack_exact_kernel(const StackParams p) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	const int layer = blockIdx.y;
 	const size_t npix = (size_t) p.H * p.W;
-	const size_t pix = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-	const bool active = pix < npix;
 	Col<T> st; Col<u16> aux;
 	if (SMEM) {
 		st.p = (T *) smem_raw + threadIdx.x; st.s = blockDim.x;
@@ -72,41 +51,31 @@ __global__ void __launch_bounds__(256) stack_exact_kernel(const ExactParams p) {
 		st.p = (T *) p.scratch + gtid; st.s = (int) nthreads;
 		aux.p = (u16 *) ((T *) p.scratch + (size_t) p.N * nthreads) + gtid; aux.s = (int) nthreads;
 	}
-	int rej[2] = { 0, 0 };
-	if (active) {
-		const int x = (int) (pix % p.W);
-		const int N = p.N;
-		int f = 0;
-		for (; f + 4 <= N; f += 4) {	// 4 independent loads in flight per thread
-			const T v0 = load_norm<T>(p, f, layer, pix, x), v1 = load_norm<T>(p, f + 1, layer, pix, x);
-			const T v2 = load_norm<T>(p, f + 2, layer, pix, x), v3 = load_norm<T>(p, f + 3, layer, pix, x);
-			st.set(f, v0); st.set(f + 1, v1); st.set(f + 2, v2); st.set(f + 3, v3);
+	if (!LIST) {
+		const int layer = blockIdx.y;
+		const size_t pix = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+		int rej[2] = { 0, 0 };
+		if (pix < npix) exact_pixel<T>(p, layer, pix, st, aux, rej);
+		if (p.is_mean && p.rc.type != SGPU_NO_REJEC) {	// irej[channel][low/high], :1748-1757
+			unsigned lo = rej[0], hi = rej[1];
+			lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
+			if ((threadIdx.x & 31) == 0 && (lo | hi)) {
+				atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
+				atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+			}
 		}
-		for (; f < N; f++) st.set(f, load_norm<T>(p, f, layer, pix, x));
-
-		double result;
-		if (p.is_mean) {
-			const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
-			auto orig = [&](int ff) { return load_norm<T>(p, ff, layer, pix, x); };
-			result = mean_and_reject<T>(st, N, p.rc, w, aux, orig, rej);
-		} else {
-			result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
-		}
-		const size_t o = (size_t) layer * npix + pix;
-		if (p.rejmaps == 1) p.rej_low[o] = truncate_to_word(rej[0] + rej[1]);
-		else if (p.rejmaps == 2) { p.rej_low[o] = truncate_to_word(rej[0]); p.rej_high[o] = truncate_to_word(rej[1]); }
-		if (p.out32) {	// median_and_mean.c:1717-1727
-			float v = (sizeof(T) == 4) ? (float) result : (float) result * .000015259022f;
-			if (!p.output_norm) { v = v < 0.f ? 0.f : v; v = v > 1.f ? 1.f : v; }
-			((float *) p.out)[o] = v;
-		} else ((u16 *) p.out)[o] = round_to_word(result);
-	}
-	if (p.is_mean && p.rc.type != SGPU_NO_REJEC) {	// irej[channel][low/high], :1748-1757
-		unsigned lo = rej[0], hi = rej[1];
-		lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
-		if ((threadIdx.x & 31) == 0 && (lo | hi)) {
-			atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
-			atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+	} else {
+		const unsigned count = *p.list_count;
+		const unsigned stride = gridDim.x * blockDim.x;
+		for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += stride) {
+			const unsigned ent = p.list[e];
+			const int layer = (int) (ent >> 30);
+			int rej[2] = { 0, 0 };
+			exact_pixel<T>(p, layer, (size_t) (ent & 0x3fffffffu), st, aux, rej);
+			if (p.is_mean && (rej[0] | rej[1])) {
+				if (rej[0]) atomicAdd(&p.irej[layer * 2], (unsigned long long) rej[0]);
+				if (rej[1]) atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) rej[1]);
+			}
 		}
 	}
 }
@@ -115,10 +84,10 @@ __global__ void __launch_bounds__(256) stack_exact_kernel(const ExactParams p) {
 
 using namespace sgpu;
 
-int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+void sgpu_fill_stack_params(StackParams &p, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej) {
 	const sgpu_block_desc &d = blk->d;
-	ExactParams p{};
+	p = StackParams{};
 	p.frames = blk->dev; p.N = d.nb_frames; p.C = d.nb_layers; p.H = d.height; p.W = d.width;
 	p.normalize = a->normalize; p.scale = dp.scale; p.offset = dp.offset; p.mul = dp.mul;
 	p.weights = a->is_mean ? dp.weights : nullptr;
@@ -141,21 +110,40 @@ int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 	p.is_mean = a->is_mean; p.output_norm = a->output_norm; p.out32 = a->use_32bit_output;
 	p.rejmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
 	p.out = d_out; p.rej_low = d_rej_low; p.rej_high = d_rej_high; p.irej = (unsigned long long *) d_irej;
-	const bool need_aux = a->is_mean && (p.rc.type == SGPU_MAD || p.rc.type == SGPU_GESDT);
-	p.use_aux = need_aux;
-	const size_t es = blk->elem();
-	const size_t per_thread = (size_t) d.nb_frames * es + (need_aux ? (size_t) d.nb_frames * 2 : 0);
-	const size_t npix = (size_t) d.height * d.width;
-	if (npix == 0 || d.nb_frames == 0) return SGPU_OK;
+	p.use_aux = a->is_mean && (p.rc.type == SGPU_MAD || p.rc.type == SGPU_GESDT);
+}
 
-	// largest CTA (<= 256 threads) whose tile leaves room for two CTAs per SM; else one CTA; else
-	// global columns
+// CTA shape of the exact engine for this stack depth: largest CTA (<= 256 threads) whose tile
+// leaves room for two CTAs per SM; else one CTA; else global columns (bd = 128, smem = false)
+static void exact_shape(sgpu_ctx *ctx, size_t per_thread, int *bd_out, bool *smem_out) {
 	int bd = 0;
 	const size_t half = ctx->smem_optin / 2 - 1024;
 	for (int cand = 256; cand >= 32; cand >>= 1) if (per_thread * cand <= half) { bd = cand; break; }
 	if (!bd) for (int cand = 64; cand >= 32; cand >>= 1) if (per_thread * cand <= ctx->smem_optin) { bd = cand; break; }
-	const bool smem = bd != 0;
-	if (!smem) bd = 128;
+	*smem_out = bd != 0;
+	*bd_out = bd ? bd : 128;
+}
+
+template <typename K>
+static int launch_kernel(sgpu_ctx *ctx, K kern, dim3 grid, int bd, size_t shm, const StackParams &p) {
+	if (shm > 48 * 1024)
+		SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
+	kern<<<grid, bd, shm, ctx->stream>>>(p);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	return SGPU_OK;
+}
+
+int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej) {
+	const sgpu_block_desc &d = blk->d;
+	StackParams p;
+	sgpu_fill_stack_params(p, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	const size_t per_thread = (size_t) d.nb_frames * blk->elem() + (p.use_aux ? (size_t) d.nb_frames * 2 : 0);
+	const size_t npix = (size_t) d.height * d.width;
+	if (npix == 0 || d.nb_frames == 0) return SGPU_OK;
+	int bd; bool smem;
+	exact_shape(ctx, per_thread, &bd, &smem);
 	const size_t shm = smem ? per_thread * bd : 0;
 	dim3 grid((unsigned) ((npix + bd - 1) / bd), (unsigned) d.nb_layers);
 	if (!smem) {
@@ -166,14 +154,29 @@ int sgpu_launch_exact(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 		if (rv) return rv;
 		p.scratch = ctx->d_scratch;
 	}
-	auto launch = [&](auto kern) -> int {
-		if (shm > 48 * 1024)
-			SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
-		kern<<<grid, bd, shm, ctx->stream>>>(p);
-		ctx->launches++;
-		SGPU_CUDA(ctx, cudaGetLastError());
-		return SGPU_OK;
-	};
-	if (d.dtype == SGPU_F32) return smem ? launch(stack_exact_kernel<float, true>) : launch(stack_exact_kernel<float, false>);
-	return smem ? launch(stack_exact_kernel<u16, true>) : launch(stack_exact_kernel<u16, false>);
+	if (d.dtype == SGPU_F32)
+		return smem ? launch_kernel(ctx, stack_exact_kernel<float, true, false>, grid, bd, shm, p)
+			    : launch_kernel(ctx, stack_exact_kernel<float, false, false>, grid, bd, shm, p);
+	return smem ? launch_kernel(ctx, stack_exact_kernel<u16, true, false>, grid, bd, shm, p)
+		    : launch_kernel(ctx, stack_exact_kernel<u16, false, false>, grid, bd, shm, p);
+}
+
+int sgpu_launch_exact_list(sgpu_ctx *ctx, sgpu_block *blk, StackParams p) {
+	const sgpu_block_desc &d = blk->d;
+	const size_t per_thread = (size_t) d.nb_frames * blk->elem() + (p.use_aux ? (size_t) d.nb_frames * 2 : 0);
+	int bd; bool smem;
+	exact_shape(ctx, per_thread, &bd, &smem);
+	const size_t shm = smem ? per_thread * bd : 0;
+	// a fixed grid that walks the list: the count only exists on the device
+	dim3 grid((unsigned) (ctx->sm_count * 2), 1);
+	if (!smem) {
+		int rv = sgpu_ensure_scratch(ctx, per_thread * (size_t) grid.x * bd);
+		if (rv) return rv;
+		p.scratch = ctx->d_scratch;
+	}
+	if (d.dtype == SGPU_F32)
+		return smem ? launch_kernel(ctx, stack_exact_kernel<float, true, true>, grid, bd, shm, p)
+			    : launch_kernel(ctx, stack_exact_kernel<float, false, true>, grid, bd, shm, p);
+	return smem ? launch_kernel(ctx, stack_exact_kernel<u16, true, true>, grid, bd, shm, p)
+		    : launch_kernel(ctx, stack_exact_kernel<u16, false, true>, grid, bd, shm, p);
 }

@@ -15,6 +15,17 @@ NAMES = ["none", "percentile", "sigma", "mad", "sigmedian", "winsorized", "linea
 SIGS = {O.NO_REJEC: (3, 3), O.PERCENTILE: (0.2, 0.3), O.SIGMA: (3, 3), O.MAD: (3, 3), O.SIGMEDIAN: (3, 3),
         O.WINSORIZED: (3, 3), O.LINEARFIT: (5, 5), O.GESDT: (0.3, 0.05)}
 REL_TOL = 1e-6   # float stacked pixels (north_star)
+ENGINE = 0       # sgpu_stack_args.engine: 0 automatic (sorted engine where it applies), 1 exact engine
+
+
+@pytest.fixture(autouse=True, params=[0, 1], ids=["auto", "exact"])
+def engine(request):
+    """every parity test runs through both engines: the automatic choice (the sorted engine with
+    its exact-engine fallback list) and the exact thread-per-pixel engine alone"""
+    global ENGINE
+    ENGINE = request.param
+    yield request.param
+    ENGINE = 0
 
 
 def synth(rng, N, Cn, H, W, dtype, zeros=0.002, hot=0.01):
@@ -58,7 +69,8 @@ def run_gpu(fr, device_resident=True, **kw):
                            coeff=sb.NormCoeff(offset=kw.pop("offset", None), mul=kw.pop("mul", None), scale=kw.pop("scale", None)),
                            weights=kw.pop("weights", None), shiftx=kw.pop("shiftx", None), shifty=kw.pop("shifty", None),
                            output_norm=kw.pop("output_norm", False), use_32bit_output=kw.pop("use_32bit_output", True),
-                           create_rejmaps=kw.pop("create_rejmaps", False), merge_lowhigh_rejmaps=kw.pop("merge_rejmaps", False))
+                           create_rejmaps=kw.pop("create_rejmaps", False), merge_lowhigh_rejmaps=kw.pop("merge_rejmaps", False),
+                           engine=ENGINE)
     if args.weights is not None:
         args.weighting_type = sb.NOISE_WEIGHT
     assert not kw, kw
@@ -209,3 +221,24 @@ def test_config_c1_shape(orc):
     o = orc.stack(host, **kw)
     compare(g, o, "C1")
     assert g["irej"][0].sum() > 0
+
+
+@pytest.mark.parametrize("case", [
+    (100, np.float32, O.WINSORIZED), (100, np.float32, O.SIGMA), (200, np.float32, None), (300, np.float32, O.GESDT),
+    (300, np.float32, O.SIGMA), (500, np.uint16, O.LINEARFIT), (130, np.uint16, O.GESDT), (257, np.uint16, O.SIGMA),
+    (65, np.float32, O.PERCENTILE), (600, np.float32, O.SIGMA), (1100, np.uint16, None)],
+    ids=lambda c: f"{c[0]}-{np.dtype(c[1]).name}-{'median' if c[2] is None else NAMES[c[2]]}")
+def test_deep_stacks(orc, case):
+    """stack depths of the benchmark configs (BASELINE.json C2..C5) on a small image: every
+    register-tile variant of the sorted engine (32 .. 2048 slots)"""
+    N, dtype, algo = case
+    rng = np.random.default_rng(N)
+    fr = synth(rng, N, 1, 6, 70, dtype, zeros=0.001, hot=0.002)
+    k = 65535 if dtype == np.uint16 else 1
+    kw = dict(normalize=O.ADDITIVE_SCALING, scale=1 + 0.02 * rng.standard_normal((1, N)),
+              offset=0.002 * rng.standard_normal((1, N)) * k, mul=np.ones((1, N)))
+    if algo is None:
+        kw.update(is_mean=False)
+    else:
+        kw.update(rejection=algo, sig=SIGS[algo], create_rejmaps=True)
+    compare(run_gpu(fr, **dict(kw)), orc.stack(fr, **kw), str(case))
