@@ -351,10 +351,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's rows per GPU")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
+    if args.height:
+        wl = wl[:2] + (args.height,) + wl[3:-1] + (wl[-1] + f" [PROFILING SUBSET: {args.height} rows]",)
     if args.impl == "reference":
         return run_reference(args, wl)
     return run_ours(args, wl)

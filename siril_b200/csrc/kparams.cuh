@@ -21,6 +21,8 @@ struct StackParams {
 	// pixels the sorted engine hands to the exact engine: entries (layer << 30) | pixel
 	unsigned *list; unsigned *list_count;
 	int ld;			// sorted engine: shared-memory row pitch per pixel, in floats
+	int is_u16;		// sorted engine: sample type is a run-time switch there (fewer kernel variants)
+	int need_sums;		// sorted engine: phase A leaves sum(x-K), sum((x-K)^2) beside each sorted stack
 };
 
 // one sample, normalized (median_and_mean.c:1638-1686); x is the pixel's column

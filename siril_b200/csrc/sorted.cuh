@@ -63,15 +63,42 @@ struct FastRes {
 
 // sum(x - K) and sum((x - K)^2) in double; K is a sample near the middle of the stack so that the
 // variance below has no cancellation to speak of
+// correctly rounded 1 / n (a division on the host, MUFU.RCP64H + Newton steps on the device)
+SGPU_HD __forceinline__ double rcp_d(int n) {
+#ifdef __CUDA_ARCH__
+	return __drcp_rn((double) n);
+#else
+	return 1.0 / (double) n;
+#endif
+}
+// a / n correctly rounded without the division routine (Markstein: y = RN(1/n), q = RN(a y),
+// r = a - q n exactly by FMA, q' = RN(q + r y)); tests/test_sorted_host.py checks it against `/`
+SGPU_HD __forceinline__ double div_by_int(double a, int n) {
+	const double y = rcp_d(n), b = (double) n;
+	const double q = a * y;
+	const double r = fma(-q, b, a);
+	return fma(r, y, q);
+}
+
 struct Sums {
 	double K, S1, S2;
 	SGPU_HD __forceinline__ void init(float k) { K = (double) k; S1 = 0.0; S2 = 0.0; }
 	SGPU_HD __forceinline__ void add(float x) { const double y = (double) x - K; S1 += y; S2 = fma(y, y, S2); }
 	SGPU_HD __forceinline__ void sub(float x) { const double y = (double) x - K; S1 -= y; S2 = fma(-y, y, S2); }
 	SGPU_HD __forceinline__ double sum(int n) const { return S1 + (double) n * K; }
-	SGPU_HD __forceinline__ double mean(int n) const { return K + S1 / (double) n; }
-	SGPU_HD __forceinline__ double var(int n) const { return (S2 - S1 * S1 / (double) n) / (double) (n - 1); }
+	SGPU_HD __forceinline__ double mean(int n) const { return K + S1 * rcp_d(n); }
+	SGPU_HD __forceinline__ double var(int n) const { return (S2 - S1 * S1 * rcp_d(n)) * rcp_d(n - 1); }
 };
+
+// the pre-accumulated sums of the whole stack (phase A leaves them beside the sorted stack), or,
+// where there are none (host tests), a pass over the stack
+template <class Acc>
+SGPU_HD __forceinline__ Sums sums_of(const Acc &s, int n, const Sums *S0) {
+	if (S0) return *S0;
+	Sums S; S.init(s(n >> 1));
+	for (int i = 0; i < n; i++) S.add(s(i));
+	return S;
+}
 
 // interval [lo, hi] that contains the reference's float sd of the n samples summarised by S;
 // `scale` is the 1.134f of the winsorized estimate (1 otherwise).  false: degenerate, fall back.
@@ -103,16 +130,17 @@ SGPU_HD __forceinline__ void finish_range(const Acc &s, int a, int b, const Sums
 
 // ---- NO_REJEC / kept <= 1 -----------------------------------------------------------------------
 template <class Acc>
-SGPU_HD void fast_all(const Acc &s, int n, FastRes &o) {
+SGPU_HD void fast_all(const Acc &s, int n, const Sums *S0, FastRes &o) {
 	double sum = 0.0;
-	for (int i = 0; i < n; i++) sum += (double) s(i);
+	if (S0) sum = S0->sum(n);
+	else for (int i = 0; i < n; i++) sum += (double) s(i);
 	o.status = FAST_DONE; o.kept = n; o.sum = sum;
 	o.pmin = n ? s(0) : 0.f; o.pmax = n ? s(n - 1) : 0.f;
 }
 
 // ---- PERCENTILE (rejection_float.c:31-44,160-173 / median_and_mean.c:590-603,762-776) ----------
 template <bool U16, class Acc>
-SGPU_HD void fast_percentile(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+SGPU_HD void fast_percentile(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
 	const double median = median_sorted<U16>(s, 0, n);
 	const float medf = (float) median;
 	if (U16 ? (medf == 0.f) : (median == 0.0)) { o.status = FAST_FALLBACK; return; }
@@ -127,7 +155,11 @@ SGPU_HD void fast_percentile(const Acc &s, int n, const RejCfg &c, int rej[2], F
 	if (a >= b) { o.status = FAST_FALLBACK; return; }	// kept == 0: median of the compacted stack
 	rej[0] += a; rej[1] += n - b;
 	double sum = 0.0;
-	for (int i = a; i < b; i++) sum += (double) s(i);
+	if (S0) {	// the whole-stack sum less what was rejected
+		sum = S0->sum(n);
+		for (int i = 0; i < a; i++) sum -= (double) s(i);
+		for (int i = b; i < n; i++) sum -= (double) s(i);
+	} else for (int i = a; i < b; i++) sum += (double) s(i);
 	o.status = FAST_DONE; o.kept = b - a; o.sum = sum; o.pmin = s(a); o.pmax = s(b - 1);
 }
 
@@ -148,14 +180,13 @@ SGPU_HD __forceinline__ int clip_range(const Acc &s, int a, int b, float medf, f
 
 // ---- SIGMA (rejection_float.c:174-209 / median_and_mean.c:777-813) ------------------------------
 template <bool U16, class Acc>
-SGPU_HD void fast_sigma(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+SGPU_HD void fast_sigma(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
 	o.status = FAST_FALLBACK;
 	{
 		const double median = median_sorted<U16>(s, 0, n);
 		if (U16 ? ((float) median == 0.f) : (median == 0.0)) return;
 	}
-	Sums S; S.init(s(n >> 1));
-	for (int i = 0; i < n; i++) S.add(s(i));
+	Sums S = sums_of(s, n, S0);
 	int a = 0, b = n, r = 0;
 	for (;;) {
 		const int nn = b - a;
@@ -178,15 +209,15 @@ SGPU_HD void fast_sigma(const Acc &s, int n, const RejCfg &c, int rej[2], FastRe
 
 // ---- WINSORIZED, float samples (rejection_float.c:223-259) --------------------------------------
 template <class Acc>
-SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
+SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
 	o.status = FAST_FALLBACK;
-	Sums S; S.init(s(n >> 1));
-	for (int i = 0; i < n; i++) S.add(s(i));
+	Sums S = sums_of(s, n, S0);
 	int a = 0, b = n, r = 0;
 	for (;;) {
 		const int nn = b - a;
 		if (nn - r <= 4) break;
-		const double var0 = S.var(nn);
+		const double rn = rcp_d(nn), rn1 = rcp_d(nn - 1);
+		const double var0 = (S.S2 - S.S1 * S.S1 * rn) * rn1;
 		if (!(var0 >= 0.0)) return;
 		float sigma = sqrtf((float) var0), sigma0;
 		const float medf = (float) median_sorted<false>(s, a, nn);
@@ -206,8 +237,8 @@ SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, int rej[2], F
 			const double nl = (double) (ia - a), nh = (double) (b - ib);
 			const double W1 = In.S1 + nl * yl + nh * yh;
 			const double W2 = In.S2 + nl * yl * yl + nh * yh * yh;
-			varw = (W2 - W1 * W1 / (double) nn) / (double) (nn - 1);
-			meanw = In.K + W1 / (double) nn;
+			varw = (W2 - W1 * W1 * rn) * rn1;
+			meanw = In.K + W1 * rn;
 			if (!(varw >= 0.0)) return;
 			sigma0 = sigma;
 			sigma = 1.134f * sqrtf((float) varw);
@@ -276,7 +307,7 @@ SGPU_HD void fast_linearfit(Acc &s, int n, const RejCfg &c, int rej[2], FastRes 
 // ORIGINAL sorted stack (:333, `out[iter].i = max_index`) is reproduced: after k low removals
 // it flags the element k places below the one it removed.
 template <bool U16, class Acc>
-SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, int rej[2], FastRes &o) {
+SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
 	o.status = FAST_FALLBACK;
 	const int removed = nb - n;
 	double median;
@@ -285,11 +316,10 @@ SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, int rej[2]
 	else median = (s((n - 1) / 2) + s(n / 2)) / 2.0;	// gsl_stats_float_median_from_sorted_data: float add
 	if (U16) median = (double) (float) median;
 	int max_out = (int) ((float) nb * c.s0);
-	if (removed >= max_out) { fast_all(s, n, o); return; }
+	if (removed >= max_out) { fast_all(s, n, S0, o); return; }
 	max_out -= removed;
 	if (2 * max_out >= n || n - max_out < 3) { FAST_WHY(71); return; }	// flagged positions could collide: leave it to the exact engine
-	Sums S; S.init(s(n >> 1));
-	for (int i = 0; i < n; i++) S.add(s(i));
+	Sums S = sums_of(s, n, S0);
 	const double total = S.sum(n);
 	const bool exact_sums = U16 || (s(0) > 0.f && s(n - 1) <= s(0) * 65536.f && n <= 2048);
 	int lo = 0, clo = 0, chi = 0, first_low = -1;
@@ -301,7 +331,7 @@ SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, int rej[2]
 		// exact in double (samples of one sign within 2^16 of each other, or integers) S.sum() IS
 		// the reference's sum, so the float mean is bit-identical, ties included; otherwise the
 		// reference's own summation order matters whenever the quotient sits on a rounding boundary
-		const double avg_d = S.sum(size) / (double) size;
+		const double avg_d = div_by_int(S.sum(size), size);
 		const float avg = (float) avg_d;
 		if (!exact_sums) {
 			const double tiny = fabs(avg_d) * 1e-12;
@@ -339,16 +369,16 @@ SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, int rej[2]
 // normalized sample of frame f (the reference's o_stack).  status FAST_FALLBACK: result unset.
 template <bool U16, class Acc, typename OrigFn>
 SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const double *w, OrigFn orig,
-		int rej[2], int *status) {
+		const Sums *S0, int rej[2], int *status) {
 	FastRes o; o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
 	if (n == 0) { *status = FAST_DONE; return 0.0; }	// all samples null: median of zeros
-	if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(s, n, o);
+	if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(s, n, S0, o);
 	else switch (c.type) {
-	case SGPU_PERCENTILE: fast_percentile<U16>(s, n, c, rej, o); break;
-	case SGPU_SIGMA: fast_sigma<U16>(s, n, c, rej, o); break;
-	case SGPU_WINSORIZED: if (U16) o.status = FAST_FALLBACK; else fast_winsorized(s, n, c, rej, o); break;
+	case SGPU_PERCENTILE: fast_percentile<U16>(s, n, c, S0, rej, o); break;
+	case SGPU_SIGMA: fast_sigma<U16>(s, n, c, S0, rej, o); break;
+	case SGPU_WINSORIZED: if (U16) o.status = FAST_FALLBACK; else fast_winsorized(s, n, c, S0, rej, o); break;
 	case SGPU_LINEARFIT: fast_linearfit(s, n, c, rej, o); break;
-	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, rej, o); break;
+	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, S0, rej, o); break;
 	default: o.status = FAST_FALLBACK; break;	// MAD, SIGMEDIAN: exact engine
 	}
 	*status = o.status;

@@ -15,7 +15,7 @@ struct HostAcc {
 
 // returns status (FAST_DONE / FAST_FALLBACK); *mean, rej[2] filled when FAST_DONE
 extern "C" int sorted_host_mean_and_reject(int is_float, const void *stack, int N, int rejtype, float s0, float s1,
-		const float *crit, const double *weights, int layer, int rej[2], double *mean) {
+		const float *crit, const double *weights, int layer, int rej[2], double *mean, int use_s0) {
 	RejCfg c{ rejtype, s0, s1, crit, N, 0.f, 0.f };
 	if (rejtype == 6) {
 		volatile float mx = (N - 1) * 0.5f, acc = 0.f;
@@ -33,10 +33,22 @@ extern "C" int sorted_host_mean_and_reject(int is_float, const void *stack, int 
 	rej[0] = rej[1] = 0;
 	int status;
 	auto orig = [&](int f) { return o[f]; };
-	*mean = is_float ? fast_mean_and_reject<false>(acc, n, N, c, w, orig, rej, &status)
-			 : fast_mean_and_reject<true>(acc, n, N, c, w, orig, rej, &status);
+	// phase A's pre-accumulated sums: 8 lane partials around a sample from the bulk, then a tree
+	Sums S0, part[8];
+	if (use_s0 && n > 0) {
+		const float K = s[((n / 2) / 16) * 16];
+		for (int t = 0; t < 8; t++) part[t].init(K);
+		for (int i = 0; i < n; i++) part[(i / 16) % 8].add(s[i]);
+		for (int m = 1; m < 8; m <<= 1) for (int t = 0; t < 8; t += 2 * m) { part[t].S1 += part[t + m].S1; part[t].S2 += part[t + m].S2; }
+		S0 = part[0];
+	}
+	const Sums *ps = (use_s0 && n > 0) ? &S0 : nullptr;
+	*mean = is_float ? fast_mean_and_reject<false>(acc, n, N, c, w, orig, ps, rej, &status)
+			 : fast_mean_and_reject<true>(acc, n, N, c, w, orig, ps, rej, &status);
 	return status;
 }
+
+extern "C" double sorted_host_div_by_int(double a, int n) { return div_by_int(a, n); }
 
 extern "C" double sorted_host_median(int is_float, const void *stack, int N) {
 	std::vector<float> s(N);

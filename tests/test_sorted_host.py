@@ -34,7 +34,9 @@ def sh():
     L = C.CDLL(SO)
     L.sorted_host_mean_and_reject.restype = C.c_int
     L.sorted_host_mean_and_reject.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,
-                                              C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+                                              C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_int]
+    L.sorted_host_div_by_int.restype = C.c_double
+    L.sorted_host_div_by_int.argtypes = [C.c_double, C.c_int]
     L.sorted_host_median.restype = C.c_double
     L.sorted_host_median.argtypes = [C.c_int, C.c_void_p, C.c_int]
     return L
@@ -69,19 +71,22 @@ def make_stack(rng, n, dtype, kind):
     return base.astype(np.float32)
 
 
-def run_fast(sh, st, algo, sig, crit=None, weights=None):
+def run_fast(sh, st, algo, sig, crit=None, weights=None, use_s0=1):
     rej = (C.c_int * 2)()
     mean = C.c_double()
     cr = None if crit is None else np.ascontiguousarray(crit, dtype=np.float32)
     w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float64)
     status = sh.sorted_host_mean_and_reject(int(st.dtype == np.float32), st.ctypes.data_as(C.c_void_p), len(st), algo,
                                             sig[0], sig[1], None if cr is None else cr.ctypes.data_as(C.c_void_p),
-                                            None if w is None else w.ctypes.data_as(C.c_void_p), 0, rej, C.byref(mean))
+                                            None if w is None else w.ctypes.data_as(C.c_void_p), 0, rej, C.byref(mean), use_s0)
     return status, mean.value, rej[0], rej[1]
 
 
 def check(sh, orc, st, algo, sig, crit=None, weights=None):
-    status, m, lo, hi = run_fast(sh, st, algo, sig, crit, weights)
+    s_a, m_a, lo_a, hi_a = run_fast(sh, st, algo, sig, crit, weights, use_s0=0)
+    status, m, lo, hi = run_fast(sh, st, algo, sig, crit, weights, use_s0=1)
+    if s_a == 0 and status == 0:   # own sums or phase A's pre-accumulated ones: same decisions
+        assert (lo, hi) == (lo_a, hi_a) and abs(m - m_a) <= 1e-12 * max(abs(m), 1e-30)
     if status != 0:
         return False
     om, olo, ohi = orc.mean_and_reject(st, algo, sig, crit=crit, weights=weights)
@@ -138,3 +143,12 @@ def test_median_sorted(sh, orc, dtype):
             m = sh.sorted_host_median(int(dtype == np.float32), st.ctypes.data_as(C.c_void_p), n)
             om, _ = orc.quickmedian(st)
             assert m == om, (n, kind, m, om)
+
+
+def test_div_by_int(sh):
+    """the Markstein division used for GESDT's window mean is the correctly rounded quotient"""
+    rng = np.random.default_rng(11)
+    for _ in range(20000):
+        n = int(rng.integers(1, 2049))
+        a = float(np.float32(rng.uniform(0, 1))) * int(rng.integers(1, 4 * n)) if rng.random() < 0.5 else float(rng.uniform(-1e3, 1e3))
+        assert sh.sorted_host_div_by_int(a, n) == a / n, (a, n)
