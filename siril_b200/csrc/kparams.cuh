@@ -22,6 +22,7 @@ struct StackParams {
 	unsigned *list; unsigned *list_count;
 	int ld;			// sorted engine: shared-memory row pitch per pixel, in floats
 	int is_u16;		// sorted engine: sample type is a run-time switch there (fewer kernel variants)
+	int use_tma, tile_rows, box_rows;	// sorted engine: TMA tile load (f32, no x shift, plane a multiple of 16 bytes); rows held / rows per TMA box
 	int need_sums;		// sorted engine: phase A leaves sum(x-K), sum((x-K)^2) beside each sorted stack
 };
 

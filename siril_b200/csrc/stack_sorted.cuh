@@ -22,18 +22,53 @@
 //         decide identically to the reference are appended to a list that the exact engine
 //         (stack_exact.cu, LIST mode) processes right after on the same stream.
 #pragma once
+#include <cuda.h>
 #include "kparams.cuh"
 #include "sorted.cuh"
 
 namespace sgpu {
 
 constexpr int TILE_PX = 32;
-constexpr int SORT_WARPS = 4;
 #define SGPU_INF __int_as_float(0x7f800000)
 
 __device__ __forceinline__ int sw_idx(int row, int px) { return row * TILE_PX + ((((px >> 2) ^ (row & 7)) << 2) | (px & 3)); }
 
+// ---- TMA (cp.async.bulk.tensor) + mbarrier, raw PTX ----
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+	// bounded: a tile that never arrives (bad tensor map) must fault, not hang the GPU
+	for (unsigned spin = 0; spin < (1u << 24); spin++) {
+		unsigned done;
+		asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+		if (done) return;
+	}
+	__trap();
+}
+// box (32 px, 1 layer, rows) of the [frame][layer][pixel] tensor at (pix0, layer, row0)
+__device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, int c0, int c1, int c2, unsigned long long *bar) {
+	asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+		:: "r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+
 constexpr int pow2_ceil(int x) { int p = 1; while (p < x) p <<= 1; return p; }
+
+// one compare-exchange step between lanes t and t ^ lm: the lane with `keep_min` keeps the
+// minimum of each slot pair, the other the maximum
+template <int RE>
+__device__ __forceinline__ void lane_step(float (&v)[RE], int lm, bool keep_min) {
+#pragma unroll
+	for (int j = 0; j < RE; j++) {
+		const float r = __shfl_xor_sync(0xffffffffu, v[j], lm);
+		v[j] = keep_min ? fminf(v[j], r) : fmaxf(v[j], r);
+	}
+}
 
 // ascending sort of the T*RE slots held by the T lanes of a group; slot (j, t) has index j*T + t
 template <int LT, int RE>
@@ -43,14 +78,8 @@ __device__ __forceinline__ void group_sort(float (&v)[RE], int t) {
 	for (int k = 2; k <= NS; k <<= 1) {
 		// flip step: index i against i ^ (k - 1), minimum to the lower index
 		if (k <= T) {
-			const bool keep_min = (t & (k >> 1)) == 0;
-#pragma unroll
-			for (int j = 0; j < RE; j++) {
-				const float b = __shfl_xor_sync(0xffffffffu, v[j], k - 1);
-				v[j] = keep_min ? fminf(v[j], b) : fmaxf(v[j], b);
-			}
+			lane_step<RE>(v, k - 1, (t & (k >> 1)) == 0);
 		} else {
-			constexpr int dummy = 0; (void) dummy;
 			const int jm = (k >> LT) - 1, hb = k >> (LT + 1);	// register flip mask, the bit that tells lower from upper
 #pragma unroll
 			for (int j = 0; j < RE; j++) {
@@ -75,12 +104,7 @@ __device__ __forceinline__ void group_sort(float (&v)[RE], int t) {
 					}
 				}
 			} else {
-				const bool keep_min = (t & s) == 0;
-#pragma unroll
-				for (int j = 0; j < RE; j++) {
-					const float b = __shfl_xor_sync(0xffffffffu, v[j], s);
-					v[j] = keep_min ? fminf(v[j], b) : fmaxf(v[j], b);
-				}
+				lane_step<RE>(v, s, (t & s) == 0);
 			}
 		}
 	}
@@ -108,7 +132,7 @@ __device__ __forceinline__ float normalize_sample(T v, double c0, double c1) {
 
 // load + normalize the tile: lane = pixel, warp w takes frames w, w + 4, ...  All raw loads of a
 // batch are issued before the first one is used, so U of them are in flight per thread.
-template <typename T, int MODE, bool SHIFT>
+template <typename T, int MODE, bool SHIFT, int SORT_WARPS>
 __device__ __forceinline__ void load_tile(const StackParams &p, float *rows, int layer, size_t pix0, size_t npix, int warp, int lane) {
 	const size_t pix = pix0 + lane;
 	const bool in = pix < npix;
@@ -139,34 +163,50 @@ __device__ __forceinline__ void load_tile(const StackParams &p, float *rows, int
 	}
 }
 
-template <typename T>
+template <typename T, int NW>
 __device__ __forceinline__ void load_tile_any(const StackParams &p, float *rows, int layer, size_t pix0, size_t npix, int warp, int lane) {
 	const int mode = p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2);
 	if (p.shiftx) {
-		if (mode == 0) load_tile<T, 0, true>(p, rows, layer, pix0, npix, warp, lane);
-		else if (mode == 1) load_tile<T, 1, true>(p, rows, layer, pix0, npix, warp, lane);
-		else load_tile<T, 2, true>(p, rows, layer, pix0, npix, warp, lane);
+		if (mode == 0) load_tile<T, 0, true, NW>(p, rows, layer, pix0, npix, warp, lane);
+		else if (mode == 1) load_tile<T, 1, true, NW>(p, rows, layer, pix0, npix, warp, lane);
+		else load_tile<T, 2, true, NW>(p, rows, layer, pix0, npix, warp, lane);
 	} else {
-		if (mode == 0) load_tile<T, 0, false>(p, rows, layer, pix0, npix, warp, lane);
-		else if (mode == 1) load_tile<T, 1, false>(p, rows, layer, pix0, npix, warp, lane);
-		else load_tile<T, 2, false>(p, rows, layer, pix0, npix, warp, lane);
+		if (mode == 0) load_tile<T, 0, false, NW>(p, rows, layer, pix0, npix, warp, lane);
+		else if (mode == 1) load_tile<T, 1, false, NW>(p, rows, layer, pix0, npix, warp, lane);
+		else load_tile<T, 2, false, NW>(p, rows, layer, pix0, npix, warp, lane);
 	}
 }
 
-template <int LT, int RE>
-__global__ void __launch_bounds__(SORT_WARPS * 32, (RE > 44 ? 3 : (RE > 25 ? 4 : 6))) stack_sorted_kernel(const StackParams p) {
+template <int LT, int RE, int SORT_WARPS>
+__global__ void __launch_bounds__(SORT_WARPS * 32, (RE > 44 ? 12 : (RE > 25 ? 16 : 24)) / SORT_WARPS) stack_sorted_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int TL = 1 << LT, Q = 32 >> LT;	// lanes per pixel, pixels per warp and round
-	extern __shared__ __align__(16) float smem[];	// Sums sums[32], int cnt[32], int bad[32], then rows[N][32]
+	extern __shared__ __align__(1024) unsigned char smem_raw[];	// rows[..][32] (1024-aligned: TMA swizzle), Sums[32], cnt[32], bad[32], mbarrier
 	const int N = p.N;
-	Sums *sums = (Sums *) smem;
+	float *rows = (float *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+	Sums *sums = (Sums *) (rows + (size_t) p.tile_rows * TILE_PX);
 	int *cnt = (int *) (sums + TILE_PX), *bad = cnt + TILE_PX;
-	float *rows = (float *) (bad + TILE_PX);
+	unsigned long long *bar = (unsigned long long *) (bad + TILE_PX);
 	const int layer = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * TILE_PX;
 
-	if (p.is_u16) load_tile_any<u16>(p, rows, layer, pix0, npix, warp, lane);
-	else load_tile_any<float>(p, rows, layer, pix0, npix, warp, lane);
-	__syncthreads();
+	if (p.use_tma) {
+		// one thread has the TMA unit fetch the whole (32 px x N frames) tile: raw samples, rows
+		// swizzled exactly as sw_idx() expects; normalization happens when phase A reads them
+		if (threadIdx.x == 0) mbar_init(bar, 1);
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			mbar_expect_tx(bar, (unsigned) (p.tile_rows * TILE_PX * sizeof(float)));
+			for (int r0 = 0; r0 < p.tile_rows; r0 += p.box_rows)
+				tma_load_3d(rows + (size_t) r0 * TILE_PX, &tmap, (int) pix0, layer, r0, bar);
+		}
+		mbar_wait(bar, 0);
+	} else {
+		if (p.is_u16) load_tile_any<u16, SORT_WARPS>(p, rows, layer, pix0, npix, warp, lane);
+		else load_tile_any<float, SORT_WARPS>(p, rows, layer, pix0, npix, warp, lane);
+		__syncthreads();
+	}
+	const int tma_mode = !p.use_tma ? 0 : (p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2));
+	const double *nc0 = p.scale + layer * N, *nc1 = (tma_mode == 1 ? p.offset : p.mul) + layer * N;
 
 	// ---- phase A: sort, Q pixels per warp and round ----
 	{
@@ -182,6 +222,8 @@ __global__ void __launch_bounds__(SORT_WARPS * 32, (RE > 44 ? 3 : (RE > 25 ? 4 :
 				float x = SGPU_INF;
 				if (i < N) {
 					x = rows[sw_idx(i, px)];
+					if (tma_mode == 1) x = normalize_sample<float, 1>(x, nc0[i], nc1[i]);
+					else if (tma_mode == 2) x = normalize_sample<float, 2>(x, nc0[i], nc1[i]);
 					if (!(fabsf(x) < SGPU_INF)) { weird = 1; x = SGPU_INF; }
 					else if (p.is_mean && x == 0.f) x = SGPU_INF;
 					else n++;
@@ -262,15 +304,16 @@ __global__ void __launch_bounds__(SORT_WARPS * 32, (RE > 44 ? 3 : (RE > 25 ? 4 :
 
 }  // namespace sgpu
 
-// one instantiation per (lanes per pixel, slots per lane); defined in stack_sorted_inst*.cu
-template <int LT, int RE>
-int sgpu_launch_sorted_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, dim3 grid, size_t shm);
+// one instantiation per (lanes per pixel, slots per lane, warps per CTA); defined in stack_sorted_inst*.cu
+template <int LT, int RE, int NW>
+int sgpu_launch_sorted_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm);
 
-#define SGPU_SORTED_VARIANT(LT, RE) \
-	template <> int sgpu_launch_sorted_variant<LT, RE>(sgpu_ctx *ctx, const sgpu::StackParams &p, dim3 grid, size_t shm) { \
-		auto kern = sgpu::stack_sorted_kernel<LT, RE>; \
+#define SGPU_SORTED_VARIANT(LT, RE, NW) \
+	template <> int sgpu_launch_sorted_variant<LT, RE, NW>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
+		auto kern = sgpu::stack_sorted_kernel<LT, RE, NW>; \
+		const CUtensorMap tm = tmap ? *tmap : CUtensorMap{}; \
 		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm)); \
-		kern<<<grid, sgpu::SORT_WARPS * 32, shm, ctx->stream>>>(p); \
+		kern<<<grid, NW * 32, shm, ctx->stream>>>(p, tm); \
 		ctx->launches++; \
 		SGPU_CUDA(ctx, cudaGetLastError()); \
 		return SGPU_OK; \
