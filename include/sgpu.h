@@ -76,6 +76,9 @@ int sgpu_ctx_synchronize(sgpu_ctx *ctx);
 const char *sgpu_last_error(const sgpu_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 uint64_t sgpu_launch_count(const sgpu_ctx *ctx);
+/* number of pixels the last sgpu_stack_block / sgpu_stack_host call of this context handed from the
+ * register / sorted engine to the exact engine (diagnostic; synchronizes the context stream) */
+uint64_t sgpu_handover_count(sgpu_ctx *ctx);
 /* cooperative cancel: polled between row-block launches like processing_should_continue()
  * (median_and_mean.c:1563); return non-zero from the callback to get SGPU_CANCEL */
 int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*should_cancel)(void *), void *user);
@@ -120,7 +123,7 @@ typedef struct {
 	int use_32bit_output;		/* args->use_32bit_output: float result, else WORD result */
 	int create_rejmaps;		/* args->create_rejmaps */
 	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
-	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine */
+	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 3: force the register engine */
 } sgpu_stack_args;
 
 /* All outputs are DEVICE pointers: d_out [nb_layers][height][width] float or uint16_t,

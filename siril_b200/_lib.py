@@ -48,6 +48,7 @@ SIGNATURES = {
     "sgpu_ctx_synchronize": (C.c_int, [P]),
     "sgpu_last_error": (C.c_char_p, [P]),
     "sgpu_launch_count": (C.c_uint64, [P]),
+    "sgpu_handover_count": (C.c_uint64, [P]),
     "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_host_free": (None, [P, P]),
@@ -112,6 +113,11 @@ class Context:
     @property
     def launches(self):
         return int(self.L.sgpu_launch_count(self.h))
+
+    @property
+    def handovers(self):
+        """pixels the last stack call handed from the register / sorted engine to the exact engine"""
+        return int(self.L.sgpu_handover_count(self.h))
 
     def close(self):
         if getattr(self, "h", None):

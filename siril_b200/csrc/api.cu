@@ -92,6 +92,14 @@ int sgpu_ctx_synchronize(sgpu_ctx *ctx) {
 
 const char *sgpu_last_error(const sgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 uint64_t sgpu_launch_count(const sgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+uint64_t sgpu_handover_count(sgpu_ctx *ctx) {
+	if (!ctx || !ctx->d_list || !ctx->list_used) return 0;
+	unsigned n = 0;
+	if (cudaSetDevice(ctx->device) != cudaSuccess) return 0;
+	if (cudaMemcpyAsync(&n, ctx->d_list, sizeof n, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return 0;
+	if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return 0;
+	return n;
+}
 
 int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*cb)(void *), void *user) {
 	if (!ctx) return SGPU_GENERIC_ERROR;
@@ -227,8 +235,13 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
 	StackDevParams dp;
 	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
-	// engine: 0 automatic (sorted engine where it applies), 1 exact thread-per-pixel, 2 sorted or fail
+	// engine: 0 automatic (register engine, else sorted engine, else exact), 1 exact thread-per-pixel,
+	// 2 sorted or fail, 3 register or fail
+	if (a->engine == 3 && !sgpu_reg_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the register engine does not cover this configuration");
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
+	ctx->list_used = false;
+	if ((a->engine == 0 || a->engine == 3) && sgpu_reg_supports(blk->d, a))
+		return sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
 		return sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	return sgpu_launch_exact(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);

@@ -23,7 +23,7 @@ struct sgpu_ctx {
 	void *d_params = nullptr; size_t d_params_cap = 0;
 	void *h_params = nullptr;			// pinned mirror
 	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
-	void *d_list = nullptr; size_t d_list_cap = 0;		// sorted engine: pixels handed to the exact engine
+	void *d_list = nullptr; size_t d_list_cap = 0; bool list_used = false;		// sorted engine: pixels handed to the exact engine
 };
 
 struct sgpu_block {
@@ -52,6 +52,9 @@ struct StackDevParams {
 };
 
 // engines
+bool sgpu_reg_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
+int sgpu_launch_reg(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 bool sgpu_sorted_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_sorted(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);

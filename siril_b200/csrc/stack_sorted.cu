@@ -100,6 +100,7 @@ int sgpu_launch_sorted(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	int rv = sgpu_ensure_list(ctx, list_bytes); if (rv) return rv;
 	p.list_count = (unsigned *) ctx->d_list; p.list = p.list_count + 1;
 	SGPU_CUDA(ctx, cudaMemsetAsync(p.list_count, 0, sizeof(unsigned), ctx->stream));
+	ctx->list_used = true;
 	p.is_u16 = d.dtype == SGPU_U16;
 	p.need_sums = a->is_mean && a->type_of_rejection != SGPU_LINEARFIT;
 	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes

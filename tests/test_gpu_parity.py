@@ -15,13 +15,14 @@ NAMES = ["none", "percentile", "sigma", "mad", "sigmedian", "winsorized", "linea
 SIGS = {O.NO_REJEC: (3, 3), O.PERCENTILE: (0.2, 0.3), O.SIGMA: (3, 3), O.MAD: (3, 3), O.SIGMEDIAN: (3, 3),
         O.WINSORIZED: (3, 3), O.LINEARFIT: (5, 5), O.GESDT: (0.3, 0.05)}
 REL_TOL = 1e-6   # float stacked pixels (north_star)
-ENGINE = 0       # sgpu_stack_args.engine: 0 automatic (sorted engine where it applies), 1 exact engine
+ENGINE = 0       # sgpu_stack_args.engine: 0 automatic, 1 exact engine, 2 sorted engine, 3 register engine
 
 
-@pytest.fixture(autouse=True, params=[0, 1], ids=["auto", "exact"])
+@pytest.fixture(autouse=True, params=[0, 1, 2], ids=["auto", "exact", "sorted"])
 def engine(request):
-    """every parity test runs through both engines: the automatic choice (the sorted engine with
-    its exact-engine fallback list) and the exact thread-per-pixel engine alone"""
+    """every parity test runs through the automatic choice (register engine, else sorted engine,
+    each with its exact-engine hand-over list), the exact thread-per-pixel engine alone, and the
+    sorted engine wherever it applies (test_gpu_reg.py forces the register engine)"""
     global ENGINE
     ENGINE = request.param
     yield request.param
@@ -74,10 +75,14 @@ def run_gpu(fr, device_resident=True, **kw):
     if args.weights is not None:
         args.weighting_type = sb.NOISE_WEIGHT
     assert not kw, kw
-    if args.normalize != O.NO_NORM:
-        rv = args.method(args)       # coefficients supplied: step 3 of main_stack only
-    else:
-        rv = sb.main_stack(args)
+    def go():
+        if args.normalize != O.NO_NORM:
+            return args.method(args)       # coefficients supplied: step 3 of main_stack only
+        return sb.main_stack(args)
+    rv = go()
+    if rv != 0 and ENGINE == 2 and "does not cover" in str(getattr(args, "error", "")):
+        args.engine = 0                    # configuration outside the sorted engine: automatic choice
+        rv = go()
     assert rv == 0, getattr(args, "error", rv)
     r = args.result
     return dict(out=to_np(r.data) if device_resident else r.data,
