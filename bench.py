@@ -268,6 +268,7 @@ def run_ours(args, wl):
     total_ms = ev[0].elapsed_time(ev[-1])
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
     launches = ctx.launches - launches0
+    handed = ctx.handovers
     clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -330,7 +331,8 @@ def run_ours(args, wl):
                        "frames": n, "width": w, "height_per_gpu": h, "layers": c,
                        "l2": "inputs larger than L2 (%.1f GB per GPU per step)" % (n * c * h * w * es / 1e9),
                        "sharding": "row shards, one per rank; output rows gathered to rank 0 with NCCL" if world > 1 else "single GPU",
-                       "stats_ms": stats_ms},
+                       "stats_ms": stats_ms,
+                       "handed_to_exact_engine_px": handed},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": "stack_exact_kernel", "kernel_ms": kernel_ms_max,
                          "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0},

@@ -123,7 +123,7 @@ typedef struct {
 	int use_32bit_output;		/* args->use_32bit_output: float result, else WORD result */
 	int create_rejmaps;		/* args->create_rejmaps */
 	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
-	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 3: force the register engine */
+	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 3: force the register engine; 4: force the thread-sort engine */
 } sgpu_stack_args;
 
 /* All outputs are DEVICE pointers: d_out [nb_layers][height][width] float or uint16_t,

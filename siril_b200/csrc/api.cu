@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cmath>
 #include <new>
+#include <cstdlib>
 #include "common.cuh"
 
 int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...) {
@@ -236,12 +237,23 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	StackDevParams dp;
 	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
 	// engine: 0 automatic (register engine, else sorted engine, else exact), 1 exact thread-per-pixel,
-	// 2 sorted or fail, 3 register or fail
+	// 2 sorted or fail, 3 register or fail, 4 thread-sort or fail
 	if (a->engine == 3 && !sgpu_reg_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the register engine does not cover this configuration");
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
 	ctx->list_used = false;
-	if ((a->engine == 0 || a->engine == 3) && sgpu_reg_supports(blk->d, a))
+	sgpu_stack_args forced;
+	if (a->engine == 0) if (const char *e = getenv("SGPU_ENGINE")) {	// tuning aid: force an engine from the environment
+		forced = *a; forced.engine = atoi(e);
+		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 3 && sgpu_reg_supports(blk->d, a)) ||
+		    (forced.engine == 4 && sgpu_tsort_supports(blk->d, a)) || forced.engine == 1) a = &forced;
+	}
+	// automatic (by measurement on B200, profiles/): the register engine beyond 128 frames where it
+	// applies, the sorted engine otherwise; the thread-sort engine only when asked for
+	if ((a->engine == 3 || (a->engine == 0 && blk->d.nb_frames > 128)) && sgpu_reg_supports(blk->d, a))
 		return sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	if (a->engine == 4 && sgpu_tsort_supports(blk->d, a))
+		return sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	if (a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the thread-sort engine does not cover this configuration");
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
 		return sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	return sgpu_launch_exact(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);

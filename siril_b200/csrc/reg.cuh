@@ -21,10 +21,7 @@
 //            sorted.cuh does, removed from the running sums and overwritten with NaN, which no
 //            later comparison selects.
 // Decisions are identical to the reference's or the pixel is handed over (FAST_FALLBACK) to the
-// exact engine: same protocol, same interval argument as sorted.cuh.  The one test that is too
-// often close to call that way — the convergence test of the winsorized sigma iteration — is
-// instead settled in place by replaying the iteration with the reference's own float arithmetic
-// (reg_sd_exact), which is order independent.  Pixels with null (zero) or non-finite samples, the
+// exact engine: same protocol, same interval argument as sorted.cuh.  Pixels with null (zero) or non-finite samples, the
 // guard regime `N - r <= 4` and medians that fall out of the window twice are handed over too.
 //
 // __host__ __device__ with T == 1 on the host: tests/helpers/reg_host.cu runs the same code on
@@ -142,30 +139,6 @@ SGPU_HD __forceinline__ void reg_sums(const float (&v)[RE], const Group<T> &g, i
 		if (j & 1) { b1 += y; b2 = fma(y, y, b2); } else { a1 += y; a2 = fma(y, y, a2); }
 	}
 	*S1 = g.sum(a1 + b1); *S2 = g.sum(a2 + b2);
-}
-
-// siril_stats_float_sd (statistics.h:82-107) of the samples in the registers clamped to [cl, cu],
-// operation by operation: double sum -> float mean -> float deviations squared in float ->
-// double sum -> float sqrt.  The double sums of floats are exact (hence order independent) unless
-// the samples span more than ~2^20 in magnitude.  NaN slots are skipped.
-template <int T, int RE>
-SGPU_HD float reg_sd_exact(const float (&v)[RE], const Group<T> &g, int n, float cl, float cu, float *meanf) {
-	double a = 0.0, b = 0.0;
-#pragma unroll
-	for (int j = 0; j < RE; j++) {
-		const double w = (v[j] == v[j]) ? (double) clampw(v[j], cl, cu) : 0.0;
-		if (j & 1) b += w; else a += w;
-	}
-	const float mean = (float) (g.sum(a + b) / n);
-	a = 0.0; b = 0.0;
-#pragma unroll
-	for (int j = 0; j < RE; j++) {
-		const float e = clampw(v[j], cl, cu) - mean;
-		const double q = (v[j] == v[j]) ? (double) (e * e) : 0.0;
-		if (j & 1) b += q; else a += q;
-	}
-	if (meanf) *meanf = mean;
-	return sqrtf((float) (g.sum(a + b) / (n - 1)));
 }
 
 // ---- the window of order statistics around the median ---------------------------------------------
@@ -364,57 +337,56 @@ SGPU_HD __forceinline__ bool reg_clip(float (&v)[RE], const Group<T> &g, float m
 	return !g.any(amb);
 }
 
-// The winsorized sigma (rejection_float.c:223-237) of the n samples in the registers.
-// exact == 0: sums in double, result as an interval [*slo, *shi]; returns 0 ok, 1 hand the pixel
-// over, 2 the convergence test was too close to call.  exact != 0: the reference's float
-// arithmetic replayed (bit-identical sigma, *slo == *shi); returns 0 or 1.
+// The winsorized sigma (rejection_float.c:223-237) of the n samples in the registers, as an interval
+// [*slo, *shi] that holds the reference's float value.  Where the reference's convergence test is
+// too close to call, the iteration goes on and the sigma it would have stopped with is kept inside
+// the interval (the clip pass hands the pixel over only if a sample falls between the two ends).
+// returns 0 ok, 1 hand the pixel over.
 template <int T, int RE>
-SGPU_HD int reg_winsor_sigma(const float (&v)[RE], const Group<T> &g, int n, const RegState &s, float medf, int exact, float *slo, float *shi) {
-	float sigma = 0.f, sigma0 = 0.f;
-	float cl = -FLT_MAX, cu = FLT_MAX;
-	double varw = 0.0, meanw = 0.0;
+SGPU_HD int reg_winsor_sigma(const float (&v)[RE], const Group<T> &g, int n, const RegState &s, float medf, float *slo, float *shi) {
+	double varw = reg_var(s, n), meanw = 0.0;
+	if (!(varw >= 0.0)) { REG_WHY(106); return 1; }
+	float sigma = sqrtf((float) varw), sigma0;	// `sigma = sd(stack)`, before the first clamp
+	float cl = -FLT_MAX, cu = FLT_MAX, clo = FLT_MAX, chi = 0.f;
 	const double rn = rcp_d(n), rn1 = rcp_d(n - 1);
-	for (int it = -1; ; it++) {
-		if (it >= 0) {
-			const float m0 = medf - 1.5f * sigma, m1 = medf + 1.5f * sigma;
-			const float ncl = clampw(cl, m0, m1), ncu = clampw(cu, m0, m1);
-			if (ncl < cl || ncu > cu) { REG_WHY(107); return 1; }	// clamp bounds only ever tighten with sane data
-			cl = ncl; cu = ncu;
-		}
-		float sd;
-		if (exact) sd = reg_sd_exact<T, RE>(v, g, n, cl, cu, nullptr);
-		else if (it < 0) {
-			varw = reg_var(s, n);
-			if (!(varw >= 0.0)) { REG_WHY(106); return 1; }
-			sd = sqrtf((float) varw);
-		} else {
-			// sums of the clamped samples about medf; a NaN slot clamps to cl and is taken out again below
-			double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
+	for (int it = 0; ; it++) {
+		const float m0 = medf - 1.5f * sigma, m1 = medf + 1.5f * sigma;
+		const float ncl = clampw(cl, m0, m1), ncu = clampw(cu, m0, m1);
+		if (ncl < cl || ncu > cu) { REG_WHY(107); return 1; }	// clamp bounds only ever tighten with sane data
+		cl = ncl; cu = ncu;
+		// sums of the clamped samples about medf; a NaN slot clamps to cl and is taken out again below
+		double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
 #pragma unroll
-			for (int j = 0; j < RE; j++) {
-				const double y = (double) (fminf(fmaxf(v[j], cl), cu) - medf);
-				if (j & 1) { b1 += y; b2 = fma(y, y, b2); } else { a1 += y; a2 = fma(y, y, a2); }
-			}
-			const double yc = (double) (cl - medf), nn = (double) s.nanl;
-			const double W1 = g.sum((a1 + b1) - nn * yc), W2 = g.sum((a2 + b2) - nn * yc * yc);
-			varw = (W2 - W1 * W1 * rn) * rn1;
-			meanw = (double) medf + W1 * rn;
-			if (!(varw >= 0.0)) { REG_WHY(108); return 1; }
-			sd = sqrtf((float) varw);
+		for (int j = 0; j < RE; j++) {
+			const double y = (double) (fminf(fmaxf(v[j], cl), cu) - medf);
+			if (j & 1) { b1 += y; b2 = fma(y, y, b2); } else { a1 += y; a2 = fma(y, y, a2); }
 		}
-		if (it < 0) { sigma = sd; continue; }	// `sigma = sd(stack)`, before the first clamp
+		const double yc = (double) (cl - medf), nn = (double) s.nanl;
+		const double W1 = g.sum((a1 + b1) - nn * yc), W2 = g.sum((a2 + b2) - nn * yc * yc);
+		varw = (W2 - W1 * W1 * rn) * rn1;
+		meanw = (double) medf + W1 * rn;
+		if (!(varw >= 0.0)) { REG_WHY(108); return 1; }
 		sigma0 = sigma;
-		sigma = 1.134f * sd;
+		sigma = 1.134f * sqrtf((float) varw);
 #if defined(SGPU_FAST_DEBUG) && !defined(__CUDA_ARCH__)
 		g_reg_inner++;
 #endif
 		const float d = fabsf(sigma - sigma0), thr = sigma0 * 0.0005f;
-		if (!exact && fabsf(d - thr) <= 2.f * REG_DELTA_WS * sigma0) return 2;
-		if (!(d > thr)) break;
 		if (it > 64) { REG_WHY(109); return 1; }
+		if (fabsf(d - thr) <= 2.f * REG_DELTA_WS * sigma0) {	// the reference may stop here or go on
+#if defined(SGPU_FAST_DEBUG) && !defined(__CUDA_ARCH__)
+			g_reg_exact++;
+#endif
+			float l, h;
+			if (!sd_interval(varw, meanw, n, REG_DELTA_WS, 1.134f, &l, &h)) { REG_WHY(105); return 1; }
+			clo = l < clo ? l : clo; chi = h > chi ? h : chi;
+			continue;
+		}
+		if (!(d > thr)) break;
 	}
-	if (exact) { *slo = *shi = sigma; return 0; }
-	return sd_interval(varw, meanw, n, REG_DELTA_WS, 1.134f, slo, shi) ? 0 : 1;
+	if (!sd_interval(varw, meanw, n, REG_DELTA_WS, 1.134f, slo, shi)) return 1;
+	*slo = clo < *slo ? clo : *slo; *shi = chi > *shi ? chi : *shi;
+	return 0;
 }
 
 // Mean with rejection of the N samples in the registers (no nulls among them: the kernel hands
@@ -451,13 +423,7 @@ SGPU_HD int reg_mean_and_reject(float (&v)[RE], const Group<T> &g, int N, const 
 			if (c.type == SGPU_SIGMA) {
 				if (!sd_interval(reg_var(s, n), reg_mean(s, n), n, REG_DELTA_SD, 1.f, &slo, &shi)) { REG_WHY(120); return FAST_FALLBACK; }
 			} else {
-				int rv = 2;
-				for (int exact = 0; exact < 2 && rv == 2; exact++) {
-#if defined(SGPU_FAST_DEBUG) && !defined(__CUDA_ARCH__)
-					g_reg_exact += exact;
-#endif
-					rv = reg_winsor_sigma<T, RE>(v, g, n, s, medf, exact, &slo, &shi);
-				}
+				const int rv = reg_winsor_sigma<T, RE>(v, g, n, s, medf, &slo, &shi);
 				if (rv) { REG_WHY(121); return FAST_FALLBACK; }
 			}
 			tl_lo = slo * c.s0; tl_hi = shi * c.s0; th_lo = slo * c.s1; th_hi = shi * c.s1;

@@ -226,6 +226,9 @@ SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S
 		Sums In = S;
 		float cl = -FLT_MAX, cu = FLT_MAX;
 		double varw, meanw;
+		// stopping points the reference MAY have taken: where its convergence test is too close to
+		// call the iteration goes on and the sigma it would have stopped with is remembered
+		float clo = FLT_MAX, chi = 0.f;
 		for (;;) {
 			const float m0 = medf - 1.5f * sigma, m1 = medf + 1.5f * sigma;
 			const float ncl = clampw(cl, m0, m1), ncu = clampw(cu, m0, m1);
@@ -243,12 +246,18 @@ SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S
 			sigma0 = sigma;
 			sigma = 1.134f * sqrtf((float) varw);
 			const float d = fabsf(sigma - sigma0), thr = sigma0 * 0.0005f;
-			if (fabsf(d - thr) <= 2.f * SGPU_DELTA_WS * sigma0) return;	// convergence test too close to call
-			if (!(d > thr)) break;
 			if (++it > 64) return;
+			if (fabsf(d - thr) <= 2.f * SGPU_DELTA_WS * sigma0) {
+				float l, h;
+				if (!sd_interval(varw, meanw, nn, SGPU_DELTA_WS, 1.134f, &l, &h)) return;
+				clo = l < clo ? l : clo; chi = h > chi ? h : chi;
+				continue;
+			}
+			if (!(d > thr)) break;
 		}
 		float slo, shi;
 		if (!sd_interval(varw, meanw, nn, SGPU_DELTA_WS, 1.134f, &slo, &shi)) return;
+		slo = clo < slo ? clo : slo; shi = chi > shi ? chi : shi;	// every sigma the reference may have ended on
 		int a2, b2;
 		if (clip_range(s, a, b, medf, slo, shi, c.s0, c.s1, &a2, &b2)) return;
 		const int K = (a2 - a) + (b - b2);

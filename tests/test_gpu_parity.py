@@ -15,14 +15,14 @@ NAMES = ["none", "percentile", "sigma", "mad", "sigmedian", "winsorized", "linea
 SIGS = {O.NO_REJEC: (3, 3), O.PERCENTILE: (0.2, 0.3), O.SIGMA: (3, 3), O.MAD: (3, 3), O.SIGMEDIAN: (3, 3),
         O.WINSORIZED: (3, 3), O.LINEARFIT: (5, 5), O.GESDT: (0.3, 0.05)}
 REL_TOL = 1e-6   # float stacked pixels (north_star)
-ENGINE = 0       # sgpu_stack_args.engine: 0 automatic, 1 exact engine, 2 sorted engine, 3 register engine
+ENGINE = 0       # sgpu_stack_args.engine: 0 automatic, 1 exact, 2 sorted, 3 register, 4 thread-sort engine
 
 
-@pytest.fixture(autouse=True, params=[0, 1, 2], ids=["auto", "exact", "sorted"])
+@pytest.fixture(autouse=True, params=[0, 1, 2, 4], ids=["auto", "exact", "sorted", "tsort"])
 def engine(request):
     """every parity test runs through the automatic choice (register engine, else sorted engine,
     each with its exact-engine hand-over list), the exact thread-per-pixel engine alone, and the
-    sorted engine wherever it applies (test_gpu_reg.py forces the register engine)"""
+    sorted and thread-sort engines wherever they apply (test_gpu_reg.py forces the register engine)"""
     global ENGINE
     ENGINE = request.param
     yield request.param
@@ -80,8 +80,8 @@ def run_gpu(fr, device_resident=True, **kw):
             return args.method(args)       # coefficients supplied: step 3 of main_stack only
         return sb.main_stack(args)
     rv = go()
-    if rv != 0 and ENGINE == 2 and "does not cover" in str(getattr(args, "error", "")):
-        args.engine = 0                    # configuration outside the sorted engine: automatic choice
+    if rv != 0 and ENGINE in (2, 4) and "does not cover" in str(getattr(args, "error", "")):
+        args.engine = 0                    # configuration outside the forced engine: automatic choice
         rv = go()
     assert rv == 0, getattr(args, "error", rv)
     r = args.result
