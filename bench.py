@@ -217,11 +217,8 @@ def run_ours(args, wl):
         mine = list(range(rank, n, world))
         off, mul, sc, bg = compute_estimators(sargs, mine)
         if world > 1:
-            pack = torch.from_numpy(np.stack([off, mul, sc, bg])).to(dev)
-            mask = torch.zeros_like(pack); mask[..., mine] = 1
-            pack = pack * mask
-            dist.all_reduce(pack)            # disjoint frame sets: a sum is an all-gather
-            off, mul, sc, bg = (x.cpu().numpy() for x in pack)
+            from siril_b200 import sharding
+            off, mul, sc, bg = sharding.merge_estimators(dist, [off, mul, sc, bg], mine, device=dev)
         finalize_factors(sargs, off, mul, sc)
         sargs.bgnoise = bg
         torch.cuda.synchronize()
@@ -269,6 +266,7 @@ def run_ours(args, wl):
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
     launches = ctx.launches - launches0
     handed = ctx.handovers
+    kernel_name = ctx.last_engine
     clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -313,10 +311,12 @@ def run_ours(args, wl):
         peak, peak_src = measured_peak_gbs()
         B = algorithmic_bytes(n, c, h, w, es)
         achieved = B / (kernel_ms_max * 1e-3) / 1e9
-        traffic = None
+        traffic = None    # DRAM bytes per launch from the committed ncu --set full capture (per px-frame x units)
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.workload)
+            t = json.load(open(tp)).get(args.workload)
+            if t and t.get("kernel") == kernel_name:
+                traffic = t["dram_bytes_per_px_frame"] * n * c * h * w
         cb = None
         if world == 1 or True:
             rows = min(h, max(256, 8 * (os.cpu_count() or 1)))
@@ -334,7 +334,7 @@ def run_ours(args, wl):
                        "stats_ms": stats_ms,
                        "handed_to_exact_engine_px": handed},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "stack_exact_kernel", "kernel_ms": kernel_ms_max,
+                         "traffic": traffic, "peak_source": peak_src, "kernel": kernel_name, "kernel_ms": kernel_ms_max,
                          "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0},
             "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }

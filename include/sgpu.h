@@ -79,6 +79,8 @@ uint64_t sgpu_launch_count(const sgpu_ctx *ctx);
 /* number of pixels the last sgpu_stack_block / sgpu_stack_host call of this context handed from the
  * register / sorted engine to the exact engine (diagnostic; synchronizes the context stream) */
 uint64_t sgpu_handover_count(sgpu_ctx *ctx);
+/* engine the last stack call of this context ran on: 1 exact, 2 sorted, 3 register, 4 thread-sort */
+int sgpu_last_engine(const sgpu_ctx *ctx);
 /* cooperative cancel: polled between row-block launches like processing_should_continue()
  * (median_and_mean.c:1563); return non-zero from the callback to get SGPU_CANCEL */
 int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*should_cancel)(void *), void *user);

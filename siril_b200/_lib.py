@@ -49,6 +49,7 @@ SIGNATURES = {
     "sgpu_last_error": (C.c_char_p, [P]),
     "sgpu_launch_count": (C.c_uint64, [P]),
     "sgpu_handover_count": (C.c_uint64, [P]),
+    "sgpu_last_engine": (C.c_int, [P]),
     "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_host_free": (None, [P, P]),
@@ -118,6 +119,11 @@ class Context:
     def handovers(self):
         """pixels the last stack call handed from the register / sorted engine to the exact engine"""
         return int(self.L.sgpu_handover_count(self.h))
+
+    @property
+    def last_engine(self):
+        return {1: "stack_exact_kernel", 2: "stack_sorted_kernel", 3: "stack_reg_kernel",
+                4: "stack_tsort_kernel"}.get(int(self.L.sgpu_last_engine(self.h)), "none")
 
     def close(self):
         if getattr(self, "h", None):

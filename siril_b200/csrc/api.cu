@@ -93,6 +93,7 @@ int sgpu_ctx_synchronize(sgpu_ctx *ctx) {
 
 const char *sgpu_last_error(const sgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 uint64_t sgpu_launch_count(const sgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int sgpu_last_engine(const sgpu_ctx *ctx) { return ctx ? ctx->last_engine : 0; }
 uint64_t sgpu_handover_count(sgpu_ctx *ctx) {
 	if (!ctx || !ctx->d_list || !ctx->list_used) return 0;
 	unsigned n = 0;
@@ -250,12 +251,13 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	// automatic (by measurement on B200, profiles/): the register engine beyond 128 frames where it
 	// applies, the sorted engine otherwise; the thread-sort engine only when asked for
 	if ((a->engine == 3 || (a->engine == 0 && blk->d.nb_frames > 128)) && sgpu_reg_supports(blk->d, a))
-		return sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+		return ctx->last_engine = 3, sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 4 && sgpu_tsort_supports(blk->d, a))
-		return sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+		return ctx->last_engine = 4, sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the thread-sort engine does not cover this configuration");
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
-		return sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+		return ctx->last_engine = 2, sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	ctx->last_engine = 1;
 	return sgpu_launch_exact(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 }
 

@@ -23,7 +23,7 @@ struct sgpu_ctx {
 	void *d_params = nullptr; size_t d_params_cap = 0;
 	void *h_params = nullptr;			// pinned mirror
 	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
-	void *d_list = nullptr; size_t d_list_cap = 0; bool list_used = false;		// sorted engine: pixels handed to the exact engine
+	void *d_list = nullptr; size_t d_list_cap = 0; bool list_used = false; int last_engine = 0;		// sorted engine: pixels handed to the exact engine
 };
 
 struct sgpu_block {
