@@ -238,7 +238,7 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	StackDevParams dp;
 	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
 	// engine: 0 automatic (register engine, else sorted engine, else exact), 1 exact thread-per-pixel,
-	// 2 sorted or fail, 3 register or fail, 4 thread-sort or fail
+	// 2 sorted or fail, 3 register or fail, 4 thread-sort or fail, 5 lane-sort or fail
 	if (a->engine == 3 && !sgpu_reg_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the register engine does not cover this configuration");
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
 	ctx->list_used = false;
@@ -246,7 +246,7 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	if (a->engine == 0) if (const char *e = getenv("SGPU_ENGINE")) {	// tuning aid: force an engine from the environment
 		forced = *a; forced.engine = atoi(e);
 		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 3 && sgpu_reg_supports(blk->d, a)) ||
-		    (forced.engine == 4 && sgpu_tsort_supports(blk->d, a)) || forced.engine == 1) a = &forced;
+		    (forced.engine == 4 && sgpu_tsort_supports(blk->d, a)) || (forced.engine == 5 && sgpu_lsort_supports(blk->d, a)) || forced.engine == 1) a = &forced;
 	}
 	// automatic (by measurement on B200, profiles/): the register engine beyond 128 frames where it
 	// applies, the sorted engine otherwise; the thread-sort engine only when asked for
@@ -255,6 +255,9 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	if (a->engine == 4 && sgpu_tsort_supports(blk->d, a))
 		return ctx->last_engine = 4, sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the thread-sort engine does not cover this configuration");
+	if (a->engine == 5 && sgpu_lsort_supports(blk->d, a))
+		return ctx->last_engine = 5, sgpu_launch_lsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	if (a->engine == 5) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the lane-sort engine does not cover this configuration");
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
 		return ctx->last_engine = 2, sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	ctx->last_engine = 1;

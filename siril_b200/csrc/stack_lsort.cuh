@@ -1,0 +1,250 @@
+// stack_lsort.cuh — kernel of the LANE-SORT engine: same coverage as the sorted engine
+// (stack_sorted.cuh) with a sort that needs an order of magnitude fewer shuffles and a rejection
+// phase that keeps every thread busy.
+//
+// One CTA of SUB warps owns SUB sub-tiles of 32 consecutive pixels of one layer (tile load: TMA, one
+// 3-D box per sub-tile and <= 256 frames, 128B swizzle; or coalesced row loads with x shifts /
+// 16-bit samples — stack_sorted.cuh's loaders).
+//  sort    a group of T = 2^LT lanes owns one pixel; lane t takes the samples of rows j*T + t
+//          (bank-conflict free) into RE registers (+inf beyond the stack and for nulls in mean
+//          mode).  Each lane first sorts its own run with a generated odd-even merge network
+//          (gen_sortnet.py; only the RS rows that can hold samples take part), then LT merge
+//          levels combine the runs LANE-MAJOR (lane t ends up with ranks t*RE .. t*RE+RE-1): per
+//          level one flip exchange (run j against the partner's run RE-1-j), L-1 lane half-cleaners
+//          and a register-only bitonic merge of the lane's run.  Shuffles per sample: LT(LT+1)/2
+//          instead of ~log2(N)^2/2.  The group leaves n and sum(x-K), sum((x-K)^2) beside the stack.
+//  reject  after all sort rounds, thread i of the CTA runs the per-pixel rejection / combine
+//          (sorted.cuh) on pixel i of the tile: SUB*32 threads, SUB*32 pixels.
+#pragma once
+#include "stack_sorted.cuh"
+
+namespace sgpu {
+
+template <int RS> struct LocalNet { template <int RE> static __device__ __forceinline__ void run(float (&v)[RE]); };
+#define LCE(a, b) { const float lo__ = fminf(v[a], v[b]); v[b] = fmaxf(v[a], v[b]); v[a] = lo__; }
+#define SGPU_LOCALNET(RS_) template <> template <int RE> __device__ __forceinline__ void LocalNet<RS_>::run(float (&v)[RE])
+
+// register-only bitonic merge of a bitonic run of RE (power of two) values, ascending
+template <int RE>
+__device__ __forceinline__ void local_bitonic_merge(float (&v)[RE]) {
+#pragma unroll
+	for (int m = RE >> 1; m > 0; m >>= 1) {
+#pragma unroll
+		for (int j = 0; j < RE; j++) if ((j & m) == 0) { const float a = v[j], b = v[j | m]; v[j] = fminf(a, b); v[j | m] = fmaxf(a, b); }
+	}
+}
+
+// merge the T sorted runs of a group lane-major: afterwards lane t holds ranks [t*RE, (t+1)*RE)
+template <int LT, int RE>
+__device__ __forceinline__ void group_merge(float (&v)[RE], int t, unsigned mask) {
+#pragma unroll
+	for (int L = 1; L <= LT; L++) {
+		{	// flip: element j of this run against element RE-1-j of the partner's
+			const int pm = (1 << L) - 1;
+			const bool keep_min = ((t >> (L - 1)) & 1) == 0;
+#pragma unroll
+			for (int j = 0; j < RE / 2; j++) {
+				const float a = v[j], b = v[RE - 1 - j];
+				const float xa = __shfl_xor_sync(mask, b, pm), xb = __shfl_xor_sync(mask, a, pm);
+				v[j] = keep_min ? fminf(a, xa) : fmaxf(a, xa);
+				v[RE - 1 - j] = keep_min ? fminf(b, xb) : fmaxf(b, xb);
+			}
+		}
+#pragma unroll
+		for (int s = 1 << (L - 2 >= 0 ? L - 2 : 0); L >= 2 && s > 0; s >>= 1) {	// half-cleaners between lanes
+			const bool keep_min = (t & s) == 0;
+#pragma unroll
+			for (int j = 0; j < RE; j++) {
+				const float x = __shfl_xor_sync(mask, v[j], s);
+				v[j] = keep_min ? fminf(v[j], x) : fmaxf(v[j], x);
+			}
+		}
+		local_bitonic_merge<RE>(v);
+	}
+}
+
+// sorted stack of one pixel in the tile: rank i lives in row i
+struct SubStack {
+	float *rows; int px;
+	__device__ __forceinline__ float operator()(int i) const { return rows[sw_idx(i, px)]; }
+	__device__ __forceinline__ void set(int i, float v) const { rows[sw_idx(i, px)] = v; }
+};
+
+// pixel (within a sub-tile) of group g of a warp in sort round r (T rounds cover the 32 pixels):
+// chosen so that the lanes of a warp hit different banks when they read rows j*T + t of the
+// 128B-swizzled tile (bank = (((px >> 2) ^ (row & 7)) << 2) | (px & 3))
+template <int LT>
+__device__ __forceinline__ int lsort_pixel(int r, int g) {
+	if (LT == 1) return ((r ^ (2 * (g >> 2))) << 2) | (g & 3);	// 16 px / round: 16-byte chunks r, r^2, r^4, r^6
+	if (LT == 2) return ((r + 4 * (g >> 2)) << 2) | (g & 3);	// 8 px / round: chunks r and r + 4
+	if (LT == 3) return (r << 2) | g;				// 4 px / round: chunk r
+	return r * (32 >> LT) + g;					// 2 or 1 px / round
+}
+
+template <int LT, int RE, int RS, int SUB, int NW>
+__global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
+	constexpr int T = 1 << LT, Q = 32 >> LT, PXC = SUB * TILE_PX;
+	extern __shared__ __align__(1024) unsigned char smem_raw[];
+	const int N = p.N;
+	float *rows = (float *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);	// [SUB][tile_rows][32]
+	const size_t sub_floats = (size_t) ((p.tile_rows + 7) & ~7) * TILE_PX;	// sub-tiles start on 1024-byte swizzle atoms
+	Sums *sums = (Sums *) (rows + SUB * sub_floats);
+	int *cnt = (int *) (sums + PXC), *bad = cnt + PXC;
+	unsigned long long *bar = (unsigned long long *) (bad + PXC);
+	const int layer = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * PXC;
+
+	if (p.use_tma) {
+		if (threadIdx.x == 0) mbar_init(bar, 1);
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			int nsub = 0;	// sub-tiles that start inside the image (the others are never looked at)
+			for (int sb = 0; sb < SUB; sb++) if (pix0 + (size_t) sb * TILE_PX < npix) nsub++;
+			mbar_expect_tx(bar, (unsigned) (nsub * (size_t) p.tile_rows * TILE_PX * sizeof(float)));
+			for (int sb = 0; sb < nsub; sb++)
+				for (int r0 = 0; r0 < p.tile_rows; r0 += p.box_rows)
+					tma_load_3d(rows + sb * sub_floats + (size_t) r0 * TILE_PX, &tmap, (int) (pix0 + sb * TILE_PX), layer, r0, bar);
+		}
+		mbar_wait(bar, 0);
+	} else {
+		for (int sb = 0; sb < SUB; sb++) {
+			if (p.is_u16) load_tile_any<u16, NW>(p, rows + sb * sub_floats, layer, pix0 + sb * TILE_PX, npix, warp, lane);
+			else load_tile_any<float, NW>(p, rows + sb * sub_floats, layer, pix0 + sb * TILE_PX, npix, warp, lane);
+		}
+		__syncthreads();
+	}
+	const int tma_mode = !p.use_tma ? 0 : (p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2));
+	const double *nc0 = p.scale + layer * N, *nc1 = (tma_mode == 1 ? p.offset : p.mul) + layer * N;
+
+	// ---- sort: warp w works on sub-tile w % SUB, rounds w / SUB, + NW / SUB, ... ----
+	{
+		const int t = lane & (T - 1), g = lane >> LT;
+		const unsigned gmask = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane & ~(T - 1)));
+		float *srows = rows + (warp % SUB) * sub_floats;	// 1024-byte aligned
+		const float nullv = p.is_mean ? 0.f : __int_as_float(0x7fc00000);	// samples equal to this are dropped (nothing equals NaN)
+		constexpr int NA = (T >= 8) ? 1 : 8 / T;	// distinct values of (j*T) & 7
+#pragma unroll 1
+		for (int r = warp / SUB; r < T; r += NW / SUB) {
+			const int px = lsort_pixel<LT>(r, g);
+			// byte address of (row j*T + t, px) = (la[k] + j*T*128) with k = ((j*T) & 7) / T: the 128B swizzle
+			// XORs the 16-byte chunk index with row & 7 = ((j*T) & 7) | (t & 7) [T <= 8], t & 7 [T > 8]
+			const char *la[NA];
+			{
+				const unsigned a0 = (unsigned) (t * 128) | ((unsigned) (((px >> 2) ^ t) & 7) << 4) | ((unsigned) (px & 3) << 2);
+#pragma unroll
+				for (int k = 0; k < NA; k++) la[k] = (const char *) srows + (a0 ^ ((unsigned) ((k * T) & 7) << 4));
+			}
+			float v[RE];
+			int n = 0;
+			float poison = 0.f;	// becomes NaN if a sample is not finite
+#pragma unroll
+			for (int j = 0; j < RE; j++) {
+				float x = SGPU_INF;
+				if (j < RS) {
+					const int i = j * T + t;
+					if (i < N) {
+						x = *(const float *) (la[(((j * T) & 7) / T) % NA] + j * T * 128);
+						if (tma_mode == 1) x = normalize_sample<float, 1>(x, nc0[i], nc1[i]);
+						else if (tma_mode == 2) x = normalize_sample<float, 2>(x, nc0[i], nc1[i]);
+						poison = fmaf(x, 0.f, poison);
+						const bool ok = x != nullv;
+						n += ok;
+						x = ok ? x : SGPU_INF;
+					}
+				}
+				v[j] = x;
+			}
+			Sums S; S.K = 0.0; S.S1 = 0.0; S.S2 = 0.0;
+			if (p.need_sums) {	// sum(x - K), sum((x - K)^2) over the valid samples, K: a sample of the group's first lane
+				float Kf = __shfl_sync(gmask, v[0], 0, T);
+				Kf = (Kf < SGPU_INF) ? Kf : 0.f;
+				const double K = (double) Kf;
+				double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
+#pragma unroll
+				for (int j = 0; j < RS; j++) {
+					const float xs = (v[j] < SGPU_INF) ? v[j] : Kf;	// dropped samples and padding count as K: y == 0
+					const double y = (double) xs - K;
+					if (j & 1) { b1 += y; b2 = fma(y, y, b2); } else { a1 += y; a2 = fma(y, y, a2); }
+				}
+				a1 += b1; a2 += b2;
+#pragma unroll
+				for (int m = 1; m < T; m <<= 1) { a1 += __shfl_xor_sync(gmask, a1, m); a2 += __shfl_xor_sync(gmask, a2, m); }
+				S.K = K; S.S1 = a1; S.S2 = a2;
+			}
+			int weird = !(poison == 0.f);
+#pragma unroll
+			for (int m = 1; m < T; m <<= 1) { n += __shfl_xor_sync(gmask, n, m); weird |= __shfl_xor_sync(gmask, weird, m); }
+			LocalNet<RS>::template run<RE>(v);
+			group_merge<LT, RE>(v, t, gmask);
+			__syncwarp();	// every lane of the warp has read its rows of this round's pixels
+			const int pxc = (warp % SUB) * TILE_PX + px;
+			if (t == 0) { cnt[pxc] = n; bad[pxc] = weird; if (p.need_sums) sums[pxc] = S; }
+			// rank t*RE + j goes to row t*RE + j, whose swizzle term is j & 7 (RE is a multiple of 8)
+			char *sa = (char *) srows + ((unsigned) (t * RE * 128) | ((unsigned) (px >> 2) << 4) | ((unsigned) (px & 3) << 2));
+			const int lim = N - t * RE;
+#pragma unroll
+			for (int j = 0; j < RE; j++) if (j < lim) *(float *) ((char *) ((uintptr_t) sa ^ ((unsigned) (j & 7) << 4)) + j * 128) = v[j];
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x >= PXC) return;
+
+	// ---- reject / combine: thread i of the CTA owns pixel i of the tile ----
+	const int sb = threadIdx.x >> 5;
+	const size_t pix = pix0 + threadIdx.x;
+	int rej[2] = { 0, 0 };
+	if (pix < npix) {
+		SubStack st{ rows + sb * sub_floats, lane };
+		const int n = cnt[threadIdx.x];
+		int status = bad[threadIdx.x] ? FAST_FALLBACK : FAST_DONE;
+		double result = 0.0;
+		if (status == FAST_DONE) {
+			if (p.is_mean) {
+				const int x = (int) (pix % p.W);
+				const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
+				const Sums *S0 = (p.need_sums && n > 0) ? &sums[threadIdx.x] : nullptr;
+				if (p.is_u16) {
+					auto orig = [&](int ff) { return (float) load_norm<u16>(p, ff, layer, pix, x); };
+					result = fast_mean_and_reject<true>(st, n, N, p.rc, w, orig, S0, rej, &status);
+				} else {
+					auto orig = [&](int ff) { return load_norm<float>(p, ff, layer, pix, x); };
+					result = fast_mean_and_reject<false>(st, n, N, p.rc, w, orig, S0, rej, &status);
+				}
+			} else {	// all N samples, zeros included (median_and_mean.c:1711-1715)
+				result = p.is_u16 ? median_sorted<true>(st, 0, N) : median_sorted<false>(st, 0, N);
+			}
+		}
+		if (status == FAST_DONE) {
+			if (p.is_u16) store_result<u16>(p, (size_t) layer * npix + pix, result, rej);
+			else store_result<float>(p, (size_t) layer * npix + pix, result, rej);
+		} else {
+			rej[0] = rej[1] = 0;
+			p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pix;
+		}
+	}
+	if (p.is_mean && p.rc.type != SGPU_NO_REJEC) {
+		__syncwarp();
+		unsigned lo = rej[0], hi = rej[1];
+		lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
+		if (lane == 0 && (lo | hi)) {
+			atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
+			atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+		}
+	}
+}
+
+}  // namespace sgpu
+
+template <int LT, int RE, int RS, int SUB, int NW>
+int sgpu_launch_lsort_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm);
+
+#define SGPU_LSORT_VARIANT(LT, RE, RS, SUB, NW) \
+	template <> int sgpu_launch_lsort_variant<LT, RE, RS, SUB, NW>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
+		auto kern = sgpu::stack_lsort_kernel<LT, RE, RS, SUB, NW>; \
+		const CUtensorMap tm = tmap ? *tmap : CUtensorMap{}; \
+		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm)); \
+		kern<<<grid, NW * 32, shm, ctx->stream>>>(p, tm); \
+		ctx->launches++; \
+		SGPU_CUDA(ctx, cudaGetLastError()); \
+		return SGPU_OK; \
+	}
