@@ -248,16 +248,16 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 3 && sgpu_reg_supports(blk->d, a)) ||
 		    (forced.engine == 4 && sgpu_tsort_supports(blk->d, a)) || (forced.engine == 5 && sgpu_lsort_supports(blk->d, a)) || forced.engine == 1) a = &forced;
 	}
-	// automatic (by measurement on B200, profiles/): the register engine beyond 128 frames where it
-	// applies, the sorted engine otherwise; the thread-sort engine only when asked for
-	if ((a->engine == 3 || (a->engine == 0 && blk->d.nb_frames > 128)) && sgpu_reg_supports(blk->d, a))
+	// automatic (by measurement on B200, profiles/): the lane-sort engine wherever it applies (up to
+	// 1024 frames), else the sorted engine, else the exact engine; the others only when asked for
+	if ((a->engine == 0 || a->engine == 5) && sgpu_lsort_supports(blk->d, a))
+		return ctx->last_engine = 5, sgpu_launch_lsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	if (a->engine == 5) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the lane-sort engine does not cover this configuration");
+	if (a->engine == 3 && sgpu_reg_supports(blk->d, a))
 		return ctx->last_engine = 3, sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 4 && sgpu_tsort_supports(blk->d, a))
 		return ctx->last_engine = 4, sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the thread-sort engine does not cover this configuration");
-	if (a->engine == 5 && sgpu_lsort_supports(blk->d, a))
-		return ctx->last_engine = 5, sgpu_launch_lsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
-	if (a->engine == 5) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the lane-sort engine does not cover this configuration");
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
 		return ctx->last_engine = 2, sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	ctx->last_engine = 1;

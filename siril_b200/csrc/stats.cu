@@ -337,8 +337,8 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	// pass B (bgnoise) queued behind it
 	if (nx >= 3) {
 		const size_t shm = (size_t) nx * 5 + 16;
-		if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rows of %ld pixels do not fit in shared memory", nx);
-		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(noise_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
+		if (shm + 4096 > ctx->smem_optin) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rows of %ld pixels do not fit in shared memory", nx);	// + the kernel's static arrays
+		if (shm + 4096 > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(noise_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
 		noise_rows_kernel<T><<<(unsigned) std::min<long>(ny, 148 * 8), NT, shm, ctx->stream>>>(d, nx, ny, d_rows);
 		ctx->launches++;
 		SGPU_CUDA(ctx, cudaGetLastError());

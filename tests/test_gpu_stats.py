@@ -43,7 +43,7 @@ def check(got, exp):
 
 @pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
 @pytest.mark.parametrize("lite", [False, True], ids=["ikss", "lite"])
-@pytest.mark.parametrize("shape", [(64, 96), (257, 1031), (40, 5), (1200, 1600)])
+@pytest.mark.parametrize("shape", [(64, 96), (257, 1031), (40, 5), (1200, 1600), (24, 9576)])   # 9576: rows that need the shared-memory opt-in
 def test_image_stats(orc, dtype, lite, shape):
     import siril_b200 as sb
     from siril_b200.stacking import image_stats
