@@ -14,24 +14,24 @@ bool sgpu_lsort_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
 }
 
 // 2^lt lanes per pixel, re register slots per lane of which the first rs can hold samples
-// (the variant serves N <= rs * 2^lt), sub sub-tiles of 32 px and nw warps per CTA
+// (the variant serves rf * 2^lt < N <= rs * 2^lt: rows below rf are always full), sub sub-tiles of 32 px and nw warps per CTA
 struct LsortVariant { int lt, re, rs, sub, nw; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
-#define LV(LT, RE, RS, SUB, NW) { LT, RE, RS, SUB, NW, sgpu_launch_lsort_variant<LT, RE, RS, SUB, NW> }
+#define LV(LT, RE, RS, RF, SUB, NW) { LT, RE, RS, SUB, NW, sgpu_launch_lsort_variant<LT, RE, RS, RF, SUB, NW> }
 static const LsortVariant VARIANTS[] = {
-	LV(1, 8, 8, 4, 8),	// N <= 16
-	LV(2, 8, 8, 4, 8),	// 32
-	LV(2, 16, 13, 4, 8),	// 52
-	LV(2, 16, 16, 4, 8),	// 64
-	LV(2, 32, 20, 4, 8),	// 80
-	LV(2, 32, 25, 4, 8),	// 100
-	LV(2, 32, 32, 4, 8),	// 128
-	LV(3, 32, 20, 2, 8),	// 160
-	LV(3, 32, 25, 2, 8),	// 200
-	LV(3, 32, 32, 2, 8),	// 256
-	LV(4, 32, 19, 1, 8),	// 304
-	LV(4, 32, 25, 1, 8),	// 400
-	LV(4, 32, 32, 1, 8),	// 512
-	LV(5, 32, 32, 1, 8),	// 1024
+	LV(1, 8, 8, 0, 4, 8),	// N <= 16
+	LV(2, 8, 8, 4, 4, 8),	// 32
+	LV(2, 16, 13, 8, 4, 8),	// 52
+	LV(2, 16, 16, 13, 4, 8),	// 64
+	LV(2, 32, 20, 16, 4, 8),	// 80
+	LV(2, 32, 25, 20, 4, 8),	// 100
+	LV(2, 32, 32, 25, 4, 8),	// 128
+	LV(3, 32, 20, 16, 2, 8),	// 160
+	LV(3, 32, 25, 20, 2, 8),	// 200
+	LV(3, 32, 32, 25, 2, 8),	// 256
+	LV(4, 32, 19, 16, 1, 8),	// 304
+	LV(4, 32, 25, 19, 1, 8),	// 400
+	LV(4, 32, 32, 25, 1, 8),	// 512
+	LV(5, 32, 32, 16, 1, 8),	// 1024
 };
 
 int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
@@ -63,7 +63,7 @@ int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 		else { p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; }
 	}
 	const int pxc = var->sub * TILE_PX;
-	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * ((p.tile_rows + 7) & ~7) * sizeof(float) + (size_t) pxc * (sizeof(Sums) + 2 * sizeof(int)) + 16;
+	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * ((p.tile_rows + 7) & ~7) * sizeof(float) + (size_t) pxc * (sizeof(Sums) + 2 * sizeof(int)) + 16 + (size_t) d.nb_frames * 16;
 	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the lane-sort engine");
 	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
 	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);

@@ -65,9 +65,11 @@ __device__ __forceinline__ void group_merge(float (&v)[RE], int t, unsigned mask
 
 // sorted stack of one pixel in the tile: rank i lives in row i
 struct SubStack {
-	float *rows; int px;
-	__device__ __forceinline__ float operator()(int i) const { return rows[sw_idx(i, px)]; }
-	__device__ __forceinline__ void set(int i, float v) const { rows[sw_idx(i, px)] = v; }
+	char *base; int c;	// base: sub-tile + (px & 3) * 4 bytes; c = px >> 2
+	__device__ __forceinline__ SubStack(float *rows, int px) : base((char *) rows + ((px & 3) << 2)), c(px >> 2) { }
+	__device__ __forceinline__ float *at(int i) const { return (float *) (base + ((((i << 3) | ((i ^ c) & 7))) << 4)); }
+	__device__ __forceinline__ float operator()(int i) const { return *at(i); }
+	__device__ __forceinline__ void set(int i, float v) const { *at(i) = v; }
 };
 
 // pixel (within a sub-tile) of group g of a warp in sort round r (T rounds cover the 32 pixels):
@@ -81,7 +83,7 @@ __device__ __forceinline__ int lsort_pixel(int r, int g) {
 	return r * (32 >> LT) + g;					// 2 or 1 px / round
 }
 
-template <int LT, int RE, int RS, int SUB, int NW>
+template <int LT, int RE, int RS, int RF, int SUB, int NW>
 __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int T = 1 << LT, Q = 32 >> LT, PXC = SUB * TILE_PX;
 	extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 	Sums *sums = (Sums *) (rows + SUB * sub_floats);
 	int *cnt = (int *) (sums + PXC), *bad = cnt + PXC;
 	unsigned long long *bar = (unsigned long long *) (bad + PXC);
+	double2 *coef = (double2 *) (bar + 2);	// [N] {scale, offset | mul} when the tile holds raw samples
 	const int layer = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * PXC;
 
@@ -105,6 +108,12 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 				for (int r0 = 0; r0 < p.tile_rows; r0 += p.box_rows)
 					tma_load_3d(rows + sb * sub_floats + (size_t) r0 * TILE_PX, &tmap, (int) (pix0 + sb * TILE_PX), layer, r0, bar);
 		}
+		if (p.normalize != SGPU_NO_NORM) {	// per-frame coefficients, staged while the tile is in flight
+			const bool add = p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING;
+			const double *c0 = p.scale + layer * N, *c1 = (add ? p.offset : p.mul) + layer * N;
+			for (int i = threadIdx.x; i < N; i += NW * 32) coef[i] = make_double2(c0[i], c1[i]);
+			__syncthreads();
+		}
 		mbar_wait(bar, 0);
 	} else {
 		for (int sb = 0; sb < SUB; sb++) {
@@ -114,7 +123,6 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 		__syncthreads();
 	}
 	const int tma_mode = !p.use_tma ? 0 : (p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2));
-	const double *nc0 = p.scale + layer * N, *nc1 = (tma_mode == 1 ? p.offset : p.mul) + layer * N;
 
 	// ---- sort: warp w works on sub-tile w % SUB, rounds w / SUB, + NW / SUB, ... ----
 	{
@@ -142,10 +150,12 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 				float x = SGPU_INF;
 				if (j < RS) {
 					const int i = j * T + t;
-					if (i < N) {
+					if (j < RF || i < N) {	// rows below RF are full for every stack depth this variant serves
 						x = *(const float *) (la[(((j * T) & 7) / T) % NA] + j * T * 128);
-						if (tma_mode == 1) x = normalize_sample<float, 1>(x, nc0[i], nc1[i]);
-						else if (tma_mode == 2) x = normalize_sample<float, 2>(x, nc0[i], nc1[i]);
+						if (tma_mode) {
+							const double2 c = coef[i];
+							x = tma_mode == 1 ? normalize_sample<float, 1>(x, c.x, c.y) : normalize_sample<float, 2>(x, c.x, c.y);
+						}
 						poison = fmaf(x, 0.f, poison);
 						const bool ok = x != nullv;
 						n += ok;
@@ -194,7 +204,7 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 	const size_t pix = pix0 + threadIdx.x;
 	int rej[2] = { 0, 0 };
 	if (pix < npix) {
-		SubStack st{ rows + sb * sub_floats, lane };
+		SubStack st(rows + sb * sub_floats, lane);
 		const int n = cnt[threadIdx.x];
 		int status = bad[threadIdx.x] ? FAST_FALLBACK : FAST_DONE;
 		double result = 0.0;
@@ -235,12 +245,12 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 
 }  // namespace sgpu
 
-template <int LT, int RE, int RS, int SUB, int NW>
+template <int LT, int RE, int RS, int RF, int SUB, int NW>
 int sgpu_launch_lsort_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm);
 
-#define SGPU_LSORT_VARIANT(LT, RE, RS, SUB, NW) \
-	template <> int sgpu_launch_lsort_variant<LT, RE, RS, SUB, NW>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
-		auto kern = sgpu::stack_lsort_kernel<LT, RE, RS, SUB, NW>; \
+#define SGPU_LSORT_VARIANT(LT, RE, RS, RF, SUB, NW) \
+	template <> int sgpu_launch_lsort_variant<LT, RE, RS, RF, SUB, NW>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
+		auto kern = sgpu::stack_lsort_kernel<LT, RE, RS, RF, SUB, NW>; \
 		const CUtensorMap tm = tmap ? *tmap : CUtensorMap{}; \
 		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm)); \
 		kern<<<grid, NW * 32, shm, ctx->stream>>>(p, tm); \

@@ -12,7 +12,7 @@ SGPU_LOCALNET(16) {
 #include "gen/sortnet_16.inc"
 }
 }  // namespace sgpu
-SGPU_LSORT_VARIANT(1, 8, 8, 4, 8)
-SGPU_LSORT_VARIANT(2, 8, 8, 4, 8)
-SGPU_LSORT_VARIANT(2, 16, 13, 4, 8)
-SGPU_LSORT_VARIANT(2, 16, 16, 4, 8)
+SGPU_LSORT_VARIANT(1, 8, 8, 0, 4, 8)
+SGPU_LSORT_VARIANT(2, 8, 8, 4, 4, 8)
+SGPU_LSORT_VARIANT(2, 16, 13, 8, 4, 8)
+SGPU_LSORT_VARIANT(2, 16, 16, 13, 4, 8)
