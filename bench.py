@@ -190,6 +190,8 @@ def run_ours(args, wl):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: one JSON line
         dist.init_process_group("nccl", device_id=dev)
     L = _lib.lib()
     stream = torch.cuda.current_stream(dev)
@@ -355,11 +357,14 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's rows per GPU")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--rej", default="", help="profiling only: override the workload's rejection (none, sigma, winsorized, ...)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
     if args.height:
         wl = wl[:2] + (args.height,) + wl[3:-1] + (wl[-1] + f" [PROFILING SUBSET: {args.height} rows]",)
+    if args.rej:
+        wl = wl[:6] + (REJ_NAMES.index(args.rej),) + wl[7:-1] + (wl[-1] + f" [PROFILING: rejection {args.rej}]",)
     if args.impl == "reference":
         return run_reference(args, wl)
     return run_ours(args, wl)

@@ -24,6 +24,9 @@ static const LsortVariant VARIANTS[] = {
 	LV(2, 16, 16, 13, 4, 8),	// 64
 	LV(2, 32, 20, 16, 4, 8),	// 80
 	LV(2, 32, 25, 20, 4, 8),	// 100
+	LV(2, 32, 25, 20, 2, 4),	//   alternates of the same network (SGPU_LSORT_ALT = 1, 2, 3): tuning aid
+	LV(2, 32, 25, 20, 4, 4),
+	LV(2, 32, 25, 20, 2, 8),
 	LV(2, 32, 32, 25, 4, 8),	// 128
 	LV(3, 32, 20, 16, 2, 8),	// 160
 	LV(3, 32, 25, 20, 2, 8),	// 200
@@ -50,6 +53,10 @@ int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 	p.need_sums = a->is_mean && a->type_of_rejection != SGPU_LINEARFIT;
 	const LsortVariant *var = nullptr;
 	for (const LsortVariant &v : VARIANTS) if ((v.rs << v.lt) >= d.nb_frames) { var = &v; break; }
+	if (const char *e = getenv("SGPU_LSORT_ALT")) {	// alternates follow their primary in the table
+		const LsortVariant *alt = var + atoi(e);
+		if (var && alt < VARIANTS + sizeof VARIANTS / sizeof VARIANTS[0] && alt->lt == var->lt && alt->rs == var->rs && alt->re == var->re) var = alt;
+	}
 	if (!var) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "no lane-sort variant for %d frames", d.nb_frames);
 	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes
 	CUtensorMap tmap;

@@ -284,6 +284,10 @@ def image_stats(ctx, plane, lite=False):
     return st
 
 
+STATS_WORKERS = 8      # concurrent per-plane statistics (contexts / streams) in compute_estimators
+_stats_pool = {}       # device index -> worker contexts
+
+
 def compute_estimators(args: StackingArgs, frame_indices=None):
     """_compute_estimators_for_image over the given frames (all by default): returns
     (offset, mul, scale, bgnoise) arrays [C][N] holding ESTIMATORS (normalization.c:98-141)."""
@@ -291,12 +295,53 @@ def compute_estimators(args: StackingArgs, frame_indices=None):
     ctx = _context(args)
     n, c, h, w, dt = _shape_dtype(args.frames)
     off = np.zeros((c, n)); mul = np.ones((c, n)); sc = np.ones((c, n)); bg = np.zeros((c, n))
-    for f in (range(n) if frame_indices is None else frame_indices):
-        for layer in range(c):
-            st = image_stats(ctx, args.frames[f][layer], args.lite_norm)
-            o, m, s = C.c_double(), C.c_double(), C.c_double()
-            L.sgpu_estimators_from_stats(args.normalize, int(args.lite_norm), C.byref(st), C.byref(o), C.byref(m), C.byref(s))
-            off[layer, f], mul[layer, f], sc[layer, f], bg[layer, f] = o.value, m.value, s.value, st.bgnoise
+    todo = [(f, layer) for f in (range(n) if frame_indices is None else frame_indices) for layer in range(c)]
+
+    def one(wctx, f, layer):
+        st = image_stats(wctx, args.frames[f][layer], args.lite_norm)
+        o, m, s = C.c_double(), C.c_double(), C.c_double()
+        L.sgpu_estimators_from_stats(args.normalize, int(args.lite_norm), C.byref(st), C.byref(o), C.byref(m), C.byref(s))
+        off[layer, f], mul[layer, f], sc[layer, f], bg[layer, f] = o.value, m.value, s.value, st.bgnoise
+
+    workers = min(STATS_WORKERS, len(todo)) if _is_torch_cuda(args.frames) else 1
+    if workers <= 1:
+        for f, layer in todo:
+            one(ctx, f, layer)
+        return off, mul, sc, bg
+    # frame-parallel like the reference (compute_normalization runs its frame loop under OpenMP,
+    # normalization.c:239-265): one private context (stream + scratch) per worker thread, so the
+    # host round trips of one plane's passes overlap the kernels of the others.  Every plane's
+    # statistics are independent and deterministic, so the result does not depend on the schedule.
+    import queue
+    import threading
+    ctx.synchronize()
+    dev = args.frames.device.index or 0
+    pool = _stats_pool.setdefault(dev, [])
+    while len(pool) < workers:
+        pool.append(_lib.Context(dev, None))
+    q = queue.Queue()
+    for item in todo:
+        q.put(item)
+    errors = []
+
+    def run(wctx):
+        try:
+            while True:
+                try:
+                    f, layer = q.get_nowait()
+                except queue.Empty:
+                    return
+                one(wctx, f, layer)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=run, args=(pool[i],)) for i in range(workers)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
     return off, mul, sc, bg
 
 
