@@ -321,16 +321,25 @@ SGPU_HD __forceinline__ bool reg_clip(float (&v)[RE], const Group<T> &g, float m
 	int lo = 0, hi = 0, amb = 0;
 	double r1 = 0.0, r2 = 0.0;
 	const float nth = -th_lo;
+	// screen without branches first: most passes of most pixels have no candidate at all
+	bool any = false;
 #pragma unroll
 	for (int j = 0; j < RE; j++) {
-		const float d = medf - v[j];	// `median - pixel`; `pixel - median` is its exact negation
-		if (d > tl_lo || d < nth) {
-			if (d > tl_hi) lo++;
-			else if (-d > th_hi) hi++;
-			else amb = 1;
-			const double y = (double) v[j] - (double) K;
-			r1 += y; r2 = fma(y, y, r2);
-			v[j] = reg_nan();
+		const float d = medf - v[j];
+		any |= (d > tl_lo) | (d < nth);
+	}
+	if (g.any(any)) {
+#pragma unroll
+		for (int j = 0; j < RE; j++) {
+			const float d = medf - v[j];	// `median - pixel`; `pixel - median` is its exact negation
+			if (d > tl_lo || d < nth) {
+				if (d > tl_hi) lo++;
+				else if (-d > th_hi) hi++;
+				else amb = 1;
+				const double y = (double) v[j] - (double) K;
+				r1 += y; r2 = fma(y, y, r2);
+				v[j] = reg_nan();
+			}
 		}
 	}
 	*nlo = lo; *nhi = hi; *rs1 = r1; *rs2 = r2;
@@ -391,7 +400,7 @@ SGPU_HD int reg_winsor_sigma(const float (&v)[RE], const Group<T> &g, int n, con
 
 // Mean with rejection of the N samples in the registers (no nulls among them: the kernel hands
 // pixels with zeros over).  Types: NO_REJEC, PERCENTILE, SIGMA, WINSORIZED.
-template <int T, int RE, int RF, class St>
+template <int T, int RE, int RF, bool WINSOR, class St>
 SGPU_HD int reg_mean_and_reject(float (&v)[RE], const Group<T> &g, int N, const RejCfg &c, St &st, int rej[2], double *result) {
 	RegState s;
 	int n = N;
@@ -420,7 +429,8 @@ SGPU_HD int reg_mean_and_reject(float (&v)[RE], const Group<T> &g, int N, const 
 			tl_lo = tl_hi = medf * c.s0; th_lo = th_hi = medf * c.s1;
 		} else {
 			float slo, shi;
-			if (c.type == SGPU_SIGMA) {
+			if (!WINSOR || c.type == SGPU_SIGMA) {
+				if (c.type != SGPU_SIGMA) { REG_WHY(128); return FAST_FALLBACK; }	// a kernel built without the winsorized iteration
 				if (!sd_interval(reg_var(s, n), reg_mean(s, n), n, REG_DELTA_SD, 1.f, &slo, &shi)) { REG_WHY(120); return FAST_FALLBACK; }
 			} else {
 				const int rv = reg_winsor_sigma<T, RE>(v, g, n, s, medf, &slo, &shi);

@@ -10,8 +10,9 @@ int sgpu_make_tile_tmap(sgpu_ctx *ctx, CUtensorMap *tm, void *base, size_t npix,
 
 bool sgpu_reg_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
 	if (d.dtype != SGPU_F32 || d.nb_frames < 32 || d.nb_frames > 512 || (size_t) d.height * d.width >= (1u << 30)) return false;
+	if (a->shiftx || ((size_t) d.height * d.width) % 4 != 0) return false;	// x shifts / planes that TMA cannot address: other engines
 	if (!a->is_mean) return true;
-	if (a->weights) return false;	// the weighted combine re-reads the original stack: sorted / exact engines
+	if (a->weights) return false;	// the weighted combine re-reads the original stack: other engines
 	switch (a->type_of_rejection) {
 	case SGPU_NO_REJEC: case SGPU_PERCENTILE: case SGPU_SIGMA: case SGPU_WINSORIZED: return true;
 	default: return false;
@@ -20,14 +21,14 @@ bool sgpu_reg_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
 
 // every compiled variant: 2^lt lanes per pixel, re register slots per lane, the first rf rows
 // always full (the variant serves rf * 2^lt < N <= re * 2^lt)
-struct RegVariant { int lt, re, rf; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
+struct RegVariant { int lt, re, rf; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); int (*launch_w)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
 static const RegVariant VARIANTS[] = {
-	{ 2, 25, 8, sgpu_launch_reg_variant<2, 25, 8, 6> },	// 32 < N <= 100
-	{ 2, 38, 25, sgpu_launch_reg_variant<2, 38, 25, 6> },	// .. 152
-	{ 2, 64, 38, sgpu_launch_reg_variant<2, 64, 38, 4> },	// .. 256
-	{ 3, 38, 32, sgpu_launch_reg_variant<3, 38, 32, 3> },	// 256 < N <= 304
-	{ 3, 50, 38, sgpu_launch_reg_variant<3, 50, 38, 3> },	// .. 400
-	{ 3, 64, 50, sgpu_launch_reg_variant<3, 64, 50, 2> },	// .. 512
+	{ 2, 25, 8, sgpu_launch_reg_variant<2, 25, 8, 6, false>, sgpu_launch_reg_variant<2, 25, 8, 6, true> },	// 32 < N <= 100
+	{ 2, 38, 25, sgpu_launch_reg_variant<2, 38, 25, 6, false>, sgpu_launch_reg_variant<2, 38, 25, 6, true> },	// .. 152
+	{ 2, 64, 38, sgpu_launch_reg_variant<2, 64, 38, 4, false>, sgpu_launch_reg_variant<2, 64, 38, 4, true> },	// .. 256
+	{ 3, 38, 32, sgpu_launch_reg_variant<3, 38, 32, 3, false>, sgpu_launch_reg_variant<3, 38, 32, 3, true> },	// 256 < N <= 304
+	{ 3, 50, 38, sgpu_launch_reg_variant<3, 50, 38, 3, false>, sgpu_launch_reg_variant<3, 50, 38, 3, true> },	// .. 400
+	{ 3, 64, 50, sgpu_launch_reg_variant<3, 64, 50, 2, false>, sgpu_launch_reg_variant<3, 64, 50, 2, true> },	// .. 512
 };
 
 int sgpu_launch_reg(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
@@ -61,7 +62,11 @@ int sgpu_launch_reg(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, co
 	const size_t shm = 1024 + (size_t) TILE_PX * p.tile_rows * sizeof(float) + (size_t) TILE_PX * 2 * REG_WCAP * sizeof(float) + coef_bytes + 16;
 	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the register engine");
 	dim3 grid((unsigned) ((npix + TILE_PX - 1) / TILE_PX), (unsigned) d.nb_layers);
-	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);
+	if (!p.use_tma) {	// no tensor map (unaligned block, TMA switched off): the lane-sort engine has a plain loader
+		if (sgpu_lsort_supports(d, a)) return sgpu_launch_lsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the register engine needs the TMA tile load");
+	}
+	rv = (a->is_mean && a->type_of_rejection == SGPU_WINSORIZED ? var->launch_w : var->launch)(ctx, p, &tmap, grid, shm);
 	if (rv) return rv;
 	return sgpu_launch_exact_list(ctx, blk, p);
 }

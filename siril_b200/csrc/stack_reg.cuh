@@ -27,18 +27,22 @@ __device__ __forceinline__ int reg_pixel(int warp, int g) {
 	return 0;
 }
 
+// lane-private list entry e lives in row e*T + t of the pixel's column.  Byte address =
+// row*128 + (((px >> 2) ^ (row & 7)) << 4) + (px & 3)*4 with row & 7 = ((e*T) & 7) | t (T <= 8):
+// la = t*128 + (((px >> 2) ^ t) & 7) << 4 | (px & 3) << 2 is fixed per lane, the rest depends on e only
 template <int T>
 struct TileSt {
-	float *rows, *wb; int px, t;
-	__device__ __forceinline__ void put(int e, float x) { rows[sw_idx(e * T + t, px)] = x; }
-	__device__ __forceinline__ float get(int e) const { return rows[sw_idx(e * T + t, px)]; }
+	char *la; float *wb;
+	__device__ __forceinline__ float *at(int e) const { return (float *) ((char *) ((uintptr_t) la ^ (uintptr_t) (((e * T) & 7) << 4)) + e * (T * 128)); }
+	__device__ __forceinline__ void put(int e, float x) { *at(e) = x; }
+	__device__ __forceinline__ float get(int e) const { return *at(e); }
 	__device__ __forceinline__ float &w(int i) { return wb[i]; }
 	__device__ __forceinline__ float w(int i) const { return wb[i]; }
 	__device__ __forceinline__ float &sw(int i) { return wb[REG_WCAP + i]; }
 	__device__ __forceinline__ float sw(int i) const { return wb[REG_WCAP + i]; }
 };
 
-template <int LT, int RE, int RF, int MINB>
+template <int LT, int RE, int RF, int MINB, bool WINSOR>
 __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int T = 1 << LT, Q = 32 >> LT;
 	extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -51,7 +55,7 @@ __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackPa
 	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * TILE_PX;
 	const int tma_mode = !p.use_tma ? 0 : (p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2));
 
-	if (p.use_tma) {
+	{	// TMA only (frames with per-frame x shifts go to the lane-sort engine)
 		if (threadIdx.x == 0) mbar_init(bar, 1);
 		__syncthreads();
 		if (threadIdx.x == 0) {
@@ -65,15 +69,13 @@ __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackPa
 			__syncthreads();
 		}
 		mbar_wait(bar, 0);
-	} else {
-		load_tile_any<float, T>(p, rows, layer, pix0, npix, warp, lane);
-		__syncthreads();
 	}
 
 	const int t = lane & (T - 1), gi = lane >> LT;
 	const int px = reg_pixel<LT>(warp, gi);
 	Group<T> g; g.t = t; g.mask = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane & ~(T - 1)));
-	TileSt<T> st; st.rows = rows; st.wb = wbuf + px * 2 * REG_WCAP; st.px = px; st.t = t;
+	TileSt<T> st; st.wb = wbuf + px * 2 * REG_WCAP;
+	st.la = (char *) rows + ((unsigned) (t * 128) | ((unsigned) (((px >> 2) ^ t) & 7) << 4) | ((unsigned) (px & 3) << 2));
 
 	// ---- gather: samples j*T + t -> registers ----
 	float v[RE];
@@ -83,9 +85,8 @@ __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackPa
 		const int i = j * T + t;
 		float x = reg_nan();
 		if (j < RF || i < N) {
-			x = rows[sw_idx(i, px)];
-			if (tma_mode == 1) { const double2 c = coef[i]; x = normalize_sample<float, 1>(x, c.x, c.y); }
-			else if (tma_mode == 2) { const double2 c = coef[i]; x = normalize_sample<float, 2>(x, c.x, c.y); }
+			x = st.get(j);
+			if (tma_mode) { const double2 c = coef[i]; x = tma_mode == 1 ? normalize_sample<float, 1>(x, c.x, c.y) : normalize_sample<float, 2>(x, c.x, c.y); }
 			nullish |= (x == 0.f);
 		}
 		v[j] = x;
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackPa
 	if (pix < npix) {
 		if (p.is_mean) {
 			if (g.any(nullish)) status = FAST_FALLBACK;	// null samples are dropped first (rejection_float.c:128-135): exact engine
-			else status = reg_mean_and_reject<T, RE, RF>(v, g, N, p.rc, st, rej, &result);
+			else status = reg_mean_and_reject<T, RE, RF, WINSOR>(v, g, N, p.rc, st, rej, &result);
 		} else status = reg_median<T, RE, RF>(v, g, N, st, &result);
 		if (t == 0) {
 			if (status == FAST_DONE) store_result<float>(p, (size_t) layer * npix + pix, result, rej);
@@ -120,12 +121,12 @@ __global__ void __launch_bounds__(32 << LT, MINB) stack_reg_kernel(const StackPa
 
 }  // namespace sgpu
 
-template <int LT, int RE, int RF, int MINB>
+template <int LT, int RE, int RF, int MINB, bool WINSOR>
 int sgpu_launch_reg_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm);
 
-#define SGPU_REG_VARIANT(LT, RE, RF, MINB) \
-	template <> int sgpu_launch_reg_variant<LT, RE, RF, MINB>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
-		auto kern = sgpu::stack_reg_kernel<LT, RE, RF, MINB>; \
+#define SGPU_REG_VARIANT(LT, RE, RF, MINB, WINSOR) \
+	template <> int sgpu_launch_reg_variant<LT, RE, RF, MINB, WINSOR>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
+		auto kern = sgpu::stack_reg_kernel<LT, RE, RF, MINB, WINSOR>; \
 		const CUtensorMap tm = tmap ? *tmap : CUtensorMap{}; \
 		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm)); \
 		kern<<<grid, 32 << LT, shm, ctx->stream>>>(p, tm); \

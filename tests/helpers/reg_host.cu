@@ -32,7 +32,7 @@ extern "C" int reg_host_stack(const float *stack, int N, int is_mean, int rejtyp
 	RejCfg c{ rejtype, s0, s1, nullptr, N, 0.f, 0.f };
 	rej[0] = rej[1] = 0;
 	if (!is_mean) return reg_median<1, HRE, 0>(vr, g, N, st, result);
-	return reg_mean_and_reject<1, HRE, 0>(vr, g, N, c, st, rej, result);
+	return reg_mean_and_reject<1, HRE, 0, true>(vr, g, N, c, st, rej, result);
 }
 
 extern "C" int reg_host_reason(void) { return sgpu::g_reg_reason; }
