@@ -81,6 +81,9 @@ uint64_t sgpu_launch_count(const sgpu_ctx *ctx);
 uint64_t sgpu_handover_count(sgpu_ctx *ctx);
 /* engine the last stack call of this context ran on: 1 exact, 2 sorted, 3 register, 4 thread-sort, 5 lane-sort */
 int sgpu_last_engine(const sgpu_ctx *ctx);
+/* sgpu_image_stats: medians of this context that fell outside the shared-memory histogram window and
+ * were recomputed on the full 65536-bin histogram (diagnostic; results are identical either way) */
+uint64_t sgpu_stats_window_misses(const sgpu_ctx *ctx);
 /* cooperative cancel: polled between row-block launches like processing_should_continue()
  * (median_and_mean.c:1563); return non-zero from the callback to get SGPU_CANCEL */
 int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*should_cancel)(void *), void *user);

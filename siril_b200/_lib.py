@@ -50,6 +50,7 @@ SIGNATURES = {
     "sgpu_launch_count": (C.c_uint64, [P]),
     "sgpu_handover_count": (C.c_uint64, [P]),
     "sgpu_last_engine": (C.c_int, [P]),
+    "sgpu_stats_window_misses": (C.c_uint64, [P]),
     "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_host_free": (None, [P, P]),
@@ -119,6 +120,11 @@ class Context:
     def handovers(self):
         """pixels the last stack call handed from the register / sorted engine to the exact engine"""
         return int(self.L.sgpu_handover_count(self.h))
+
+    @property
+    def stats_window_misses(self):
+        """medians of image_stats that took the full-histogram path (window missed the median)"""
+        return int(self.L.sgpu_stats_window_misses(self.h))
 
     @property
     def last_engine(self):

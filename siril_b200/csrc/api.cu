@@ -56,6 +56,7 @@ int sgpu_ctx_create(int device, sgpu_ctx **out) {
 	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return SGPU_GENERIC_ERROR; }
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->smem_optin = prop.sharedMemPerBlockOptin;
+	{ const char *e = getenv("SGPU_STATS_FULL_HIST"); ctx->stats_full_hist = e && *e && *e != '0'; }
 	if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SGPU_GENERIC_ERROR; }
 	ctx->stream = ctx->own_stream;
@@ -94,6 +95,7 @@ int sgpu_ctx_synchronize(sgpu_ctx *ctx) {
 const char *sgpu_last_error(const sgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 uint64_t sgpu_launch_count(const sgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int sgpu_last_engine(const sgpu_ctx *ctx) { return ctx ? ctx->last_engine : 0; }
+uint64_t sgpu_stats_window_misses(const sgpu_ctx *ctx) { return ctx ? ctx->stats_window_misses : 0; }
 uint64_t sgpu_handover_count(sgpu_ctx *ctx) {
 	if (!ctx || !ctx->d_list || !ctx->list_used) return 0;
 	unsigned n = 0;

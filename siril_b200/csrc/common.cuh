@@ -17,6 +17,8 @@ struct sgpu_ctx {
 	uint64_t launches = 0;
 	int sm_count = 148;
 	size_t smem_optin = 0;
+	bool stats_full_hist = false;			// SGPU_STATS_FULL_HIST=1: skip the windowed histograms (stats.cu)
+	uint64_t stats_window_misses = 0;		// medians that fell outside the window and took the full histogram
 	int (*should_cancel)(void *) = nullptr;
 	void *cancel_user = nullptr;
 	// small device-side parameter arena (coefficients, weights, shifts, critical values)

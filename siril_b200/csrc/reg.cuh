@@ -261,11 +261,23 @@ SGPU_HD bool reg_window(const float (&v)[RE], const Group<T> &g, int n, float me
 	const int off = g.exscan(cnt);
 	for (int e = 0; e < cnt; e++) st.w(off + e) = st.get(e);
 	g.sync();
-	for (int i = g.t; i < Cin; i += T) {
-		const float x = st.w(i);
-		int r = 0;
-		for (int q = 0; q < Cin; q++) { const float y = st.w(q); r += (y < x) || (y == x && q < i); }
-		st.sw(r) = x;
+	{	// every lane ranks its first two window entries in one sweep
+		const int i0 = g.t, i1 = g.t + T;
+		const float x0 = i0 < Cin ? st.w(i0) : 0.f, x1 = i1 < Cin ? st.w(i1) : 0.f;
+		int r0 = 0, r1 = 0;
+		for (int q = 0; q < Cin; q++) {
+			const float y = st.w(q);
+			r0 += (y < x0) || (y == x0 && q < i0);
+			r1 += (y < x1) || (y == x1 && q < i1);
+		}
+		if (i0 < Cin) st.sw(r0) = x0;
+		if (i1 < Cin) st.sw(r1) = x1;
+		for (int i = g.t + 2 * T; i < Cin; i += T) {	// host build (T == 1) and wider windows
+			const float x = st.w(i);
+			int r = 0;
+			for (int q = 0; q < Cin; q++) { const float y = st.w(q); r += (y < x) || (y == x && q < i); }
+			st.sw(r) = x;
+		}
 	}
 	g.sync();
 	return true;

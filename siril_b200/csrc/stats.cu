@@ -113,15 +113,68 @@ __global__ void hist_float_kernel(const T *d, size_t n, Sel s, float mn, float s
 	}
 }
 
+// The same binning with the counters of bins [w0, w0 + HWIN) in shared memory (no global
+// atomics in the sweep): samples below the window are only counted, samples above it ignored.
+// The host places the window where the median is expected and falls back to the full
+// histogram when the median is not inside.
+static constexpr unsigned HWIN = 32768;	// bins per window: 128 KB of shared memory, one CTA per SM
+static constexpr int HNB = 148, HNT = 1024;
+
+__device__ __forceinline__ void win_count(unsigned bin, unsigned w0, unsigned *sh, unsigned &below) {
+	const unsigned b = bin - w0;
+	if (bin < w0) below++;
+	else if (b < HWIN) atomicAdd(&sh[b], 1u);
+}
+
+__device__ __forceinline__ void win_flush(const unsigned *sh, unsigned below, unsigned *hist, unsigned long long *d_below) {
+	__syncthreads();
+	for (unsigned i = threadIdx.x; i < HWIN; i += blockDim.x) { const unsigned c = sh[i]; if (c) atomicAdd(&hist[i], c); }
+	below = __reduce_add_sync(0xffffffffu, below);
+	if ((threadIdx.x & 31) == 0 && below) atomicAdd(d_below, (unsigned long long) below);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(HNT, 1) hist_float_win_kernel(const T *d, size_t n, Sel s, float mn, float scale, unsigned w0,
+		unsigned *hist, unsigned long long *d_below) {
+	extern __shared__ unsigned sh[];
+	for (unsigned i = threadIdx.x; i < HWIN; i += blockDim.x) sh[i] = 0;
+	__syncthreads();
+	unsigned below = 0;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		float v, x;
+		if (!sel_value(d, i, s, v, x)) continue;
+		win_count((unsigned) (u16) (scale * (v - mn)), w0, sh, below);
+	}
+	win_flush(sh, below, hist, d_below);
+}
+
 // exact histogram of WORD samples, or of |x - med| (siril_stats_ushort_mad, statistics.c:133-154)
+__device__ __forceinline__ bool u16_bin(u16 raw, int absdev, int med, unsigned &bin) {
+	if (raw == 0) return false;
+	int v = raw;
+	if (absdev) { v -= med; v = v < 0 ? -v : v; v &= 0xffff; }
+	bin = (unsigned) v;
+	return true;
+}
+
 __global__ void hist_u16_kernel(const u16 *d, size_t n, int absdev, int med, unsigned *hist) {
 	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
-		const u16 raw = d[i];
-		if (raw == 0) continue;
-		int v = raw;
-		if (absdev) { v -= med; v = v < 0 ? -v : v; v &= 0xffff; }
-		atomicAdd(&hist[v], 1u);
+		unsigned bin;
+		if (u16_bin(d[i], absdev, med, bin)) atomicAdd(&hist[bin], 1u);
 	}
+}
+
+__global__ void __launch_bounds__(HNT, 1) hist_u16_win_kernel(const u16 *d, size_t n, int absdev, int med, unsigned w0,
+		unsigned *hist, unsigned long long *d_below) {
+	extern __shared__ unsigned sh[];
+	for (unsigned i = threadIdx.x; i < HWIN; i += blockDim.x) sh[i] = 0;
+	__syncthreads();
+	unsigned below = 0;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		unsigned bin;
+		if (u16_bin(d[i], absdev, med, bin)) win_count(bin, w0, sh, below);
+	}
+	win_flush(sh, below, hist, d_below);
 }
 
 struct BwPartial { double up, down; };
@@ -223,29 +276,37 @@ struct Sweep {
 	unsigned *d_hist; void *d_part; void *h_part;
 };
 
-// rt_algo.cc:112-138 on a finished histogram (minPrct = maxPrct = 0.5, outputs aliased)
-float finish_hist_median_float(const unsigned *histo, size_t n, float mn, float mx, float scale) {
-	size_t k = 0, count = 0;
+// rt_algo.cc:112-138 on a finished histogram (minPrct = maxPrct = 0.5, outputs aliased).
+// `histo` holds bins [k0, k1) and `count0` samples lie below bin k0; returns false when the
+// walk would stop outside [k0, k1) (the caller then builds the full histogram)
+bool finish_hist_median_float(const unsigned *histo, size_t k0, size_t k1, size_t count0, size_t n, float mn, float mx, float scale, float &median) {
+	size_t k = k0, count = count0;
 	const float thresh = 0.5f * n;
-	while (count < thresh) count += histo[k++];
+	if (k0 > 0 && !(count < thresh)) return false;
+	while (count < thresh) { if (k >= k1) return false; count += histo[k++ - k0]; }
 	float v;
 	if (k > 0) {
-		const size_t count_ = count - histo[k - 1];
+		const size_t count_ = count - histo[k - 1 - k0];
 		const float c0 = count - thresh;
 		const float c1 = thresh - count_;
 		v = (c1 * k + c0 * (k - 1)) / (c0 + c1);
 	} else v = k;
 	v /= scale; v += mn;
 	{ const float t = v < mx ? v : mx; v = mn < t ? t : mn; }
-	return v;
+	median = v;
+	return true;
 }
 
-// sorting.c:624-641 on a finished 65536-bin histogram
-double finish_hist_median_u16(const unsigned *h, size_t n) {
-	unsigned i = 0, j = 0, k = (unsigned) (n / 2), sum = 0;
-	if (n % 2 == 0) { for (; sum <= k - 1; j++) sum += h[j]; i = j; }
-	for (; sum <= k; i++) sum += h[i];
-	return (n % 2 == 0) ? (double) (i + j - 2) / 2.0 : (double) (i - 1);
+// sorting.c:624-641 on a finished histogram, same window convention
+bool finish_hist_median_u16(const unsigned *h, size_t k0, size_t k1, size_t count0, size_t n, double &median) {
+	size_t i = k0, j = k0;
+	const size_t k = n / 2;
+	size_t sum = count0;
+	if (k0 > 0 && !(sum <= (n % 2 == 0 ? k - 1 : k))) return false;
+	if (n % 2 == 0) { for (; sum <= k - 1; j++) { if (j >= k1) return false; sum += h[j - k0]; } i = j; }
+	for (; sum <= k; i++) { if (i >= k1) return false; sum += h[i - k0]; }
+	median = (n % 2 == 0) ? (double) (i + j - 2) / 2.0 : (double) (i - 1);
+	return true;
 }
 
 template <typename T>
@@ -262,21 +323,56 @@ int minmax_sel(Sweep &w, const Sel &s, float &mn, float &mx, size_t &cnt) {
 	return SGPU_OK;
 }
 
-// histogram_median_float of the selected / transformed samples (sorting.c:644-649)
+// launch-side of the windowed histograms: zero [HWIN bins | below], sweep, read back
+template <typename Launch>
+int run_window(Sweep &w, Launch launch, std::vector<unsigned> &h, size_t &below) {
+	sgpu_ctx *ctx = w.ctx;
+	SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, (HWIN + 2) * sizeof(unsigned), ctx->stream));
+	launch(w.d_hist, (unsigned long long *) (w.d_hist + HWIN));
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	h.resize(HWIN + 2);
+	SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, (HWIN + 2) * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	unsigned long long b; memcpy(&b, h.data() + HWIN, sizeof b);
+	below = (size_t) b;
+	return SGPU_OK;
+}
+
+inline unsigned window_start(double center_bin) {
+	const double lo = center_bin - HWIN / 2;
+	return lo <= 0 ? 0u : (lo >= 65536 - HWIN ? 65536u - HWIN : (unsigned) lo);
+}
+
+// histogram_median_float of the selected / transformed samples (sorting.c:644-649); `guess` is
+// where the median is expected (only the speed depends on it)
 template <typename T>
-int hist_median_float(Sweep &w, const Sel &s, float mn, float mx, size_t cnt, float &median) {
+int hist_median_float(Sweep &w, const Sel &s, float mn, float mx, size_t cnt, float guess, float &median) {
 	sgpu_ctx *ctx = w.ctx;
 	if (fabsf(mx - mn) == 0.f) { median = mn; return SGPU_OK; }		// rt_algo.cc:78-81
 	const unsigned hs = (unsigned) std::min<size_t>(65536, cnt);
 	const float scale = (hs - 1) / (mx - mn);
+	std::vector<unsigned> h;
+	if (ctx->smem_optin >= HWIN * sizeof(unsigned) && !ctx->stats_full_hist) {
+		const unsigned w0 = window_start((double) scale * ((double) guess - (double) mn));
+		size_t below;
+		SGPU_CUDA(ctx, cudaFuncSetAttribute(hist_float_win_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (HWIN * sizeof(unsigned))));
+		int rv = run_window(w, [&](unsigned *hist, unsigned long long *d_below) {
+			hist_float_win_kernel<T><<<HNB, HNT, HWIN * sizeof(unsigned), ctx->stream>>>((const T *) w.d, w.n, s, mn, scale, w0, hist, d_below);
+		}, h, below);
+		if (rv) return rv;
+		if (finish_hist_median_float(h.data(), w0, w0 + HWIN, below, cnt, mn, mx, scale, median)) return SGPU_OK;
+		ctx->stats_window_misses++;
+	}
 	SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
 	hist_float_kernel<T><<<NB, NT, 0, ctx->stream>>>((const T *) w.d, w.n, s, mn, scale, w.d_hist);
 	ctx->launches++;
 	SGPU_CUDA(ctx, cudaGetLastError());
-	std::vector<unsigned> h(65536);
+	h.resize(65536);
 	SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	median = finish_hist_median_float(h.data(), cnt, mn, mx, scale);
+	if (!finish_hist_median_float(h.data(), 0, 65536, 0, cnt, mn, mx, scale, median))
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "histogram median: counts do not reach half of the samples");
 	return SGPU_OK;
 }
 
@@ -291,13 +387,13 @@ int ikss(Sweep &w, float inv, float median, float mad, double &location, double 
 	int rv = minmax_sel<T>(w, s, mn, mx, kept); if (rv) return rv;
 	if (kept == 0) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "IKSS: no sample within 6 MAD of the median");
 	float loc;
-	rv = hist_median_float<T>(w, s, mn, mx, kept, loc); if (rv) return rv;
+	rv = hist_median_float<T>(w, s, mn, mx, kept, median, loc); if (rv) return rv;
 	location = loc;
 	Sel sa{ 1, xlow, xhigh, 1, (float) location, inv };
 	float amn, amx; size_t c2;
 	rv = minmax_sel<T>(w, sa, amn, amx, c2); if (rv) return rv;
 	float mad2;
-	rv = hist_median_float<T>(w, sa, amn, amx, kept, mad2); if (rv) return rv;
+	rv = hist_median_float<T>(w, sa, amn, amx, kept, mad, mad2); if (rv) return rv;
 	if (mad2 == 0.0f) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "MAD is null. Statistics cannot be computed.");
 	double bw = 0.0;
 	if (mad2 > 0.f) {
@@ -376,25 +472,42 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	if (sizeof(T) == 4) {
 		Sel s{ 0, 0.f, 0.f, 0, 0.f, 1.f };
 		float med;
-		rv = hist_median_float<T>(w, s, nzmn, nzmx, ngood, med); if (rv) return rv;
+		rv = hist_median_float<T>(w, s, nzmn, nzmx, ngood, (float) mean, med); if (rv) return rv;
 		median = med;
 		Sel sa{ 0, 0.f, 0.f, 1, med, 1.f };
 		float amn, amx, madf; size_t c;
 		rv = minmax_sel<T>(w, sa, amn, amx, c); if (rv) return rv;
-		rv = hist_median_float<T>(w, sa, amn, amx, ngood, madf); if (rv) return rv;
+		rv = hist_median_float<T>(w, sa, amn, amx, ngood, (float) (0.6745 * sigma), madf); if (rv) return rv;
 		mad = madf;
 		if (!lite) { rv = ikss<T>(w, 1.f, med, madf, location, scale); if (rv) return rv; }
 	} else {
-		std::vector<unsigned> h(65536);
+		std::vector<unsigned> h;
 		for (int pass = 0; pass < 2; pass++) {
 			const int imed = pass ? (int) (median + (median >= 0.0 ? 0.5 : -0.5)) : 0;		// round_to_int
-			SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
-			hist_u16_kernel<<<NB, NT, 0, ctx->stream>>>((const u16 *) d, n, pass, imed, w.d_hist);
-			ctx->launches++;
-			SGPU_CUDA(ctx, cudaGetLastError());
-			SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
-			SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-			const double m = finish_hist_median_u16(h.data(), ngood);
+			double m = 0.0;
+			bool done = false;
+			if (ctx->smem_optin >= HWIN * sizeof(unsigned) && !ctx->stats_full_hist) {
+				const unsigned w0 = window_start(pass ? 0.6745 * sigma : mean);
+				size_t below;
+				SGPU_CUDA(ctx, cudaFuncSetAttribute(hist_u16_win_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (HWIN * sizeof(unsigned))));
+				rv = run_window(w, [&](unsigned *hist, unsigned long long *d_below) {
+					hist_u16_win_kernel<<<HNB, HNT, HWIN * sizeof(unsigned), ctx->stream>>>((const u16 *) d, n, pass, imed, w0, hist, d_below);
+				}, h, below);
+				if (rv) return rv;
+				done = finish_hist_median_u16(h.data(), w0, w0 + HWIN, below, ngood, m);
+				if (!done) ctx->stats_window_misses++;
+			}
+			if (!done) {
+				SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
+				hist_u16_kernel<<<NB, NT, 0, ctx->stream>>>((const u16 *) d, n, pass, imed, w.d_hist);
+				ctx->launches++;
+				SGPU_CUDA(ctx, cudaGetLastError());
+				h.resize(65536);
+				SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+				SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+				if (!finish_hist_median_u16(h.data(), 0, 65536, 0, ngood, m))
+					return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "histogram median: counts do not reach half of the samples");
+			}
 			if (pass == 0) median = m; else mad = (double) (float) m;
 		}
 		if (!lite) {									// statistics.c:409-438

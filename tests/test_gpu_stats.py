@@ -60,6 +60,55 @@ def test_image_stats(orc, dtype, lite, shape):
     assert got_dev == got_host     # deterministic reductions: host-staged and resident agree bit for bit
 
 
+def odd_image(rng, kind, H, W, dtype):
+    """distributions whose median is far from where the shared-memory histogram window is placed"""
+    if kind == "bimodal":            # 45% near 0.02, 55% near 0.9: the mean sits in the empty middle
+        img = np.where(rng.random((H, W)) < 0.45, 0.02, 0.9) + 0.004 * rng.standard_normal((H, W))
+    elif kind == "uniform":
+        img = rng.uniform(0.001, 1.0, (H, W))
+    elif kind == "spike":            # > half of the samples share one value, a few huge outliers
+        img = np.full((H, W), 0.25) + (rng.random((H, W)) < 0.3) * rng.uniform(0, 0.01, (H, W))
+        img[rng.random((H, W)) < 0.001] = 1.0
+    elif kind == "tail":             # exponential: median well below the mean
+        img = 0.001 + 0.05 * rng.exponential(1.0, (H, W))
+    img = np.clip(img, 1e-4, 1.0)
+    img[rng.random((H, W)) < 0.01] = 0
+    if dtype == np.uint16:
+        return np.round(img * 65535).astype(np.uint16)
+    return img.astype(np.float32)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+@pytest.mark.parametrize("lite", [False, True], ids=["ikss", "lite"])
+@pytest.mark.parametrize("kind", ["bimodal", "uniform", "spike", "tail"])
+def test_image_stats_window(orc, dtype, lite, kind, monkeypatch):
+    """windowed and full histograms give the same medians, whether or not the window holds the median"""
+    import siril_b200 as sb
+    from siril_b200.stacking import image_stats
+    rng = np.random.default_rng(len(kind) * 31 + int(lite))
+    img = odd_image(rng, kind, 300, 410, dtype)
+    ctx = sb.Context(0, torch.cuda.current_stream().cuda_stream)
+    try:
+        exp = orc.image_stats(img, lite)
+    except Exception:
+        exp = None                   # the reference gives up on this image (null MAD): so must we
+    if exp is None:
+        with pytest.raises(sb.SgpuError):
+            image_stats(ctx, img, lite)
+    else:
+        check(image_stats(ctx, img, lite).asdict(), exp)
+    if kind == "bimodal":
+        assert ctx.stats_window_misses > 0       # the fallback path really ran
+    monkeypatch.setenv("SGPU_STATS_FULL_HIST", "1")
+    full = sb.Context(0, torch.cuda.current_stream().cuda_stream)
+    if exp is None:
+        with pytest.raises(sb.SgpuError):
+            image_stats(full, img, lite)
+    else:
+        check(image_stats(full, img, lite).asdict(), exp)
+    assert full.stats_window_misses == 0
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
 @pytest.mark.parametrize("nrm", [O.ADDITIVE, O.MULTIPLICATIVE, O.ADDITIVE_SCALING, O.MULTIPLICATIVE_SCALING], ids=["add", "mul", "addscale", "mulscale"])
 def test_do_normalization_and_weights(orc, dtype, nrm):
