@@ -22,18 +22,23 @@ static const LsortVariant VARIANTS[] = {
 	LV(2, 8, 8, 4, 4, 8),	// 32
 	LV(2, 16, 13, 8, 4, 8),	// 52
 	LV(2, 16, 16, 13, 4, 8),	// 64
-	LV(2, 32, 20, 16, 4, 8),	// 80
+	LV(2, 20, 20, 16, 4, 8),	// 80
+	LV(2, 24, 24, 20, 4, 8),	// 96
 	LV(2, 32, 25, 20, 4, 8),	// 100
 	LV(2, 32, 25, 20, 2, 4),	//   alternates of the same network (SGPU_LSORT_ALT = 1, 2, 3): tuning aid
 	LV(2, 32, 25, 20, 4, 4),
 	LV(2, 32, 25, 20, 2, 8),
 	LV(2, 32, 32, 25, 4, 8),	// 128
-	LV(3, 32, 20, 16, 2, 8),	// 160
+	LV(3, 20, 20, 16, 2, 8),	// 160
+	LV(3, 24, 24, 20, 2, 8),	// 192
 	LV(3, 32, 25, 20, 2, 8),	// 200
 	LV(3, 32, 32, 25, 2, 8),	// 256
-	LV(4, 32, 19, 16, 1, 8),	// 304
+	LV(4, 20, 20, 16, 1, 8),	// 320
+	LV(4, 24, 24, 20, 1, 8),	// 384
 	LV(4, 32, 25, 19, 1, 8),	// 400
 	LV(4, 32, 32, 25, 1, 8),	// 512
+	LV(5, 20, 20, 16, 1, 8),	// 640
+	LV(5, 24, 24, 20, 1, 8),	// 768
 	LV(5, 32, 32, 16, 1, 8),	// 1024
 };
 

@@ -24,15 +24,29 @@ template <int RS> struct LocalNet { template <int RE> static __device__ __forcei
 #define LCE(a, b) { const float lo__ = fminf(v[a], v[b]); v[b] = fmaxf(v[a], v[b]); v[a] = lo__; }
 #define SGPU_LOCALNET(RS_) template <> template <int RE> __device__ __forceinline__ void LocalNet<RS_>::run(float (&v)[RE])
 
-// register-only bitonic merge of a bitonic run of RE (power of two) values, ascending
-template <int RE>
-__device__ __forceinline__ void local_bitonic_merge(float (&v)[RE]) {
+// register-only merge of a bitonic run of RE values, ascending.  A half-cleaner (i against
+// i + LEN/2) splits a bitonic run of any EVEN length into two bitonic halves with every value of
+// the first <= every value of the second; an odd tail of 3 or 5 values is sorted outright.  So RE
+// may be 2^k, 3 * 2^k or 5 * 2^k (20 and 24 slots serve stacks that would waste a third of 32).
+#define LCE2(a, b) { const float lo__ = fminf(v[a], v[b]); v[b] = fmaxf(v[a], v[b]); v[a] = lo__; }
+template <int LEN, int OFF, int RE>
+__device__ __forceinline__ void merge_bitonic_run(float (&v)[RE]) {
+	if constexpr (LEN <= 1) return;
+	else if constexpr (LEN % 2 == 0) {
 #pragma unroll
-	for (int m = RE >> 1; m > 0; m >>= 1) {
-#pragma unroll
-		for (int j = 0; j < RE; j++) if ((j & m) == 0) { const float a = v[j], b = v[j | m]; v[j] = fminf(a, b); v[j | m] = fmaxf(a, b); }
+		for (int i = 0; i < LEN / 2; i++) LCE2(OFF + i, OFF + i + LEN / 2)
+		merge_bitonic_run<LEN / 2, OFF, RE>(v);
+		merge_bitonic_run<LEN / 2, OFF + LEN / 2, RE>(v);
+	} else if constexpr (LEN == 3) {
+		LCE2(OFF, OFF + 1) LCE2(OFF + 1, OFF + 2) LCE2(OFF, OFF + 1)
+	} else {
+		static_assert(LEN == 5, "run length must be 2^k, 3 * 2^k or 5 * 2^k");
+		LCE2(OFF, OFF + 1) LCE2(OFF + 3, OFF + 4) LCE2(OFF + 2, OFF + 4) LCE2(OFF + 2, OFF + 3) LCE2(OFF + 1, OFF + 4)
+		LCE2(OFF, OFF + 3) LCE2(OFF, OFF + 2) LCE2(OFF + 1, OFF + 3) LCE2(OFF + 1, OFF + 2)
 	}
 }
+template <int RE>
+__device__ __forceinline__ void local_bitonic_merge(float (&v)[RE]) { merge_bitonic_run<RE, 0, RE>(v); }
 
 // merge the T sorted runs of a group lane-major: afterwards lane t holds ranks [t*RE, (t+1)*RE)
 template <int LT, int RE>
@@ -189,8 +203,10 @@ __global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(c
 			__syncwarp();	// every lane of the warp has read its rows of this round's pixels
 			const int pxc = (warp % SUB) * TILE_PX + px;
 			if (t == 0) { cnt[pxc] = n; bad[pxc] = weird; if (p.need_sums) sums[pxc] = S; }
-			// rank t*RE + j goes to row t*RE + j, whose swizzle term is j & 7 (RE is a multiple of 8)
-			char *sa = (char *) srows + ((unsigned) (t * RE * 128) | ((unsigned) (px >> 2) << 4) | ((unsigned) (px & 3) << 2));
+			// rank t*RE + j goes to row t*RE + j, whose swizzle term is (j + t*RE) & 7 = (j & 7) ^ ((t*RE) & 7):
+			// RE is a multiple of 4, so t*RE & 7 is 0 or 4 and the addition is an XOR
+			static_assert(RE % 4 == 0, "register slots per lane must be a multiple of 4");
+			char *sa = (char *) srows + ((unsigned) (t * RE * 128) | ((unsigned) (((px >> 2) ^ ((t * RE) & 7)) & 7) << 4) | ((unsigned) (px & 3) << 2));
 			const int lim = N - t * RE;
 #pragma unroll
 			for (int j = 0; j < RE; j++) if (j < lim) *(float *) ((char *) ((uintptr_t) sa ^ ((unsigned) (j & 7) << 4)) + j * 128) = v[j];

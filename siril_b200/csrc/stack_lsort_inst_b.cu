@@ -12,7 +12,6 @@ SGPU_LOCALNET(32) {
 #include "gen/sortnet_32.inc"
 }
 }  // namespace sgpu
-SGPU_LSORT_VARIANT(2, 32, 20, 16, 4, 8)
 SGPU_LSORT_VARIANT(2, 32, 25, 20, 4, 8)
 SGPU_LSORT_VARIANT(2, 32, 32, 25, 4, 8)
 SGPU_LSORT_VARIANT(2, 32, 25, 20, 2, 4)

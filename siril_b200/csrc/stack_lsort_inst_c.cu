@@ -12,6 +12,5 @@ SGPU_LOCALNET(32) {
 #include "gen/sortnet_32.inc"
 }
 }  // namespace sgpu
-SGPU_LSORT_VARIANT(3, 32, 20, 16, 2, 8)
 SGPU_LSORT_VARIANT(3, 32, 25, 20, 2, 8)
 SGPU_LSORT_VARIANT(3, 32, 32, 25, 2, 8)

@@ -12,7 +12,6 @@ SGPU_LOCALNET(32) {
 #include "gen/sortnet_32.inc"
 }
 }  // namespace sgpu
-SGPU_LSORT_VARIANT(4, 32, 19, 16, 1, 8)
 SGPU_LSORT_VARIANT(4, 32, 25, 19, 1, 8)
 SGPU_LSORT_VARIANT(4, 32, 32, 25, 1, 8)
 SGPU_LSORT_VARIANT(5, 32, 32, 16, 1, 8)

@@ -20,8 +20,42 @@ typedef uint16_t u16;
 static constexpr int NB = 592;		// CTAs per sweep: 4 per SM on 148 SMs
 static constexpr int NT = 256;
 
-__device__ __forceinline__ float ldf(const float *p, size_t i, float) { return p[i]; }
-__device__ __forceinline__ float ldf(const u16 *p, size_t i, float inv) { return (float) p[i] * inv; }
+__device__ __forceinline__ float cvf(float raw, float) { return raw; }
+__device__ __forceinline__ float cvf(u16 raw, float inv) { return (float) raw * inv; }
+
+// Grid-stride sweep of a plane with 16-byte loads, four in flight per thread (a scalar loop keeps
+// < 1 MB in flight on the whole GPU and runs at ~1 TB/s): f(raw) is called once per sample; the
+// unaligned head and the tail go through scalar loads.
+template <typename T, typename F>
+__device__ __forceinline__ void sweep(const T *d, size_t n, F f) {
+	constexpr int V = 16 / sizeof(T);
+	union Vec { uint4 u; T e[V]; };
+	const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t) gridDim.x * blockDim.x;
+	size_t head = ((16 - ((uintptr_t) d & 15)) & 15) / sizeof(T);
+	if (head > n) head = n;
+	const size_t nv = (n - head) / V;
+	const uint4 *dv = (const uint4 *) (d + head);
+	size_t i = tid;
+	for (; i + 3 * nth < nv; i += 4 * nth) {
+		Vec a, b, c, e;
+		a.u = dv[i]; b.u = dv[i + nth]; c.u = dv[i + 2 * nth]; e.u = dv[i + 3 * nth];
+		#pragma unroll
+		for (int k = 0; k < V; k++) f(a.e[k]);
+		#pragma unroll
+		for (int k = 0; k < V; k++) f(b.e[k]);
+		#pragma unroll
+		for (int k = 0; k < V; k++) f(c.e[k]);
+		#pragma unroll
+		for (int k = 0; k < V; k++) f(e.e[k]);
+	}
+	for (; i < nv; i += nth) {
+		Vec a; a.u = dv[i];
+		#pragma unroll
+		for (int k = 0; k < V; k++) f(a.e[k]);
+	}
+	for (size_t k = tid; k < head; k += nth) f(d[k]);
+	for (size_t k = head + nv * V + tid; k < n; k += nth) f(d[k]);
+}
 
 // block-wide reduction in a fixed order (xor tree inside each warp, then warps 0..n-1 in turn);
 // every thread returns the result
@@ -48,17 +82,16 @@ __global__ void basic_kernel(const T *d, size_t n, BasicPartial *out) {
 	__shared__ double shd[32]; __shared__ float shf[32]; __shared__ unsigned long long shu[32];
 	double sum = 0, sum2 = 0; unsigned long long ng = 0, is = 0, is2 = 0;
 	float mn = FLT_MAX, mx = -FLT_MAX, nzmn = FLT_MAX, nzmx = -FLT_MAX;
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
-		const T raw = d[i];
+	sweep(d, n, [&](T raw) {
 		const float v = (float) raw;
-		if (sizeof(T) == 4 && v != v) continue;
+		if (sizeof(T) == 4 && v != v) return;
 		mn = fminf(mn, v); mx = fmaxf(mx, v);
 		if (raw != (T) 0) {
 			ng++; nzmn = fminf(nzmn, v); nzmx = fmaxf(nzmx, v);
 			if (sizeof(T) == 4) { const double x = (double) v; sum += x; sum2 += x * x; }
 			else { const unsigned long long x = (unsigned long long) raw; is += x; is2 += x * x; }
 		}
-	}
+	});
 	auto addd = [](double a, double b) { return a + b; };
 	auto addu = [](unsigned long long a, unsigned long long b) { return a + b; };
 	auto fmn = [](float a, float b) { return fminf(a, b); };
@@ -75,10 +108,9 @@ __global__ void basic_kernel(const T *d, size_t n, BasicPartial *out) {
 struct Sel { int ranged; float lo, hi; int absdev; float c; float inv; };
 
 template <typename T>
-__device__ __forceinline__ bool sel_value(const T *d, size_t i, const Sel &s, float &val, float &x) {
-	const T raw = d[i];
+__device__ __forceinline__ bool sel_value(T raw, const Sel &s, float &val, float &x) {
 	if (raw == (T) 0) return false;
-	x = ldf(d, i, s.inv);
+	x = cvf(raw, s.inv);
 	if (x != x) return false;
 	if (s.ranged && !(x >= s.lo && x <= s.hi)) return false;
 	val = s.absdev ? fabsf(x - s.c) : x;
@@ -91,11 +123,11 @@ template <typename T>
 __global__ void minmax_sel_kernel(const T *d, size_t n, Sel s, MMPartial *out) {
 	__shared__ float shf[32]; __shared__ unsigned long long shu[32];
 	float mn = FLT_MAX, mx = -FLT_MAX; unsigned long long cnt = 0;
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](T raw) {
 		float v, x;
-		if (!sel_value(d, i, s, v, x)) continue;
+		if (!sel_value(raw, s, v, x)) return;
 		mn = fminf(mn, v); mx = fmaxf(mx, v); cnt++;
-	}
+	});
 	mn = block_reduce(mn, [](float a, float b) { return fminf(a, b); }, shf);
 	mx = block_reduce(mx, [](float a, float b) { return fmaxf(a, b); }, shf);
 	cnt = block_reduce(cnt, [](unsigned long long a, unsigned long long b) { return a + b; }, shu);
@@ -105,12 +137,12 @@ __global__ void minmax_sel_kernel(const T *d, size_t n, Sel s, MMPartial *out) {
 // histogram of (uint16_t)(scale * (val - mn)) — findMinMaxPercentile's binning (rt_algo.cc:99)
 template <typename T>
 __global__ void hist_float_kernel(const T *d, size_t n, Sel s, float mn, float scale, unsigned *hist) {
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](T raw) {
 		float v, x;
-		if (!sel_value(d, i, s, v, x)) continue;
+		if (!sel_value(raw, s, v, x)) return;
 		const unsigned bin = (unsigned) (u16) (scale * (v - mn));
 		atomicAdd(&hist[bin], 1u);
-	}
+	});
 }
 
 // The same binning with the counters of bins [w0, w0 + HWIN) in shared memory (no global
@@ -140,11 +172,11 @@ __global__ void __launch_bounds__(HNT, 1) hist_float_win_kernel(const T *d, size
 	for (unsigned i = threadIdx.x; i < HWIN; i += blockDim.x) sh[i] = 0;
 	__syncthreads();
 	unsigned below = 0;
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](T raw) {
 		float v, x;
-		if (!sel_value(d, i, s, v, x)) continue;
+		if (!sel_value(raw, s, v, x)) return;
 		win_count((unsigned) (u16) (scale * (v - mn)), w0, sh, below);
-	}
+	});
 	win_flush(sh, below, hist, d_below);
 }
 
@@ -158,10 +190,10 @@ __device__ __forceinline__ bool u16_bin(u16 raw, int absdev, int med, unsigned &
 }
 
 __global__ void hist_u16_kernel(const u16 *d, size_t n, int absdev, int med, unsigned *hist) {
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](u16 raw) {
 		unsigned bin;
-		if (u16_bin(d[i], absdev, med, bin)) atomicAdd(&hist[bin], 1u);
-	}
+		if (u16_bin(raw, absdev, med, bin)) atomicAdd(&hist[bin], 1u);
+	});
 }
 
 __global__ void __launch_bounds__(HNT, 1) hist_u16_win_kernel(const u16 *d, size_t n, int absdev, int med, unsigned w0,
@@ -170,10 +202,10 @@ __global__ void __launch_bounds__(HNT, 1) hist_u16_win_kernel(const u16 *d, size
 	for (unsigned i = threadIdx.x; i < HWIN; i += blockDim.x) sh[i] = 0;
 	__syncthreads();
 	unsigned below = 0;
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](u16 raw) {
 		unsigned bin;
-		if (u16_bin(d[i], absdev, med, bin)) win_count(bin, w0, sh, below);
-	}
+		if (u16_bin(raw, absdev, med, bin)) win_count(bin, w0, sh, below);
+	});
 	win_flush(sh, below, hist, d_below);
 }
 
@@ -183,9 +215,9 @@ template <typename T>
 __global__ void bwmv_kernel(const T *d, size_t n, Sel s, float median, float factor, BwPartial *out) {
 	__shared__ double shd[32];
 	double up = 0, down = 0;
-	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+	sweep(d, n, [&](T raw) {
 		float v, x;
-		if (!sel_value(d, i, s, v, x)) continue;
+		if (!sel_value(raw, s, v, x)) return;
 		const float im = x - median;
 		const float yi = im * factor;
 		const float yi2 = fabsf(yi) < 1.f ? yi * yi : 1.f;
@@ -193,7 +225,7 @@ __global__ void bwmv_kernel(const T *d, size_t n, Sel s, float median, float fac
 		const float t = im * (q * q);
 		up += (double) (t * t);
 		down += (double) (q * (1 - 5 * yi2));
-	}
+	});
 	auto addd = [](double a, double b) { return a + b; };
 	up = block_reduce(up, addd, shd); down = block_reduce(down, addd, shd);
 	if (threadIdx.x == 0) out[blockIdx.x] = BwPartial{ up, down };
@@ -202,63 +234,79 @@ __global__ void bwmv_kernel(const T *d, size_t n, Sel s, float median, float fac
 // FnNoise1_float / FnNoise1_ushort (quantize.c:1343-1488 / :1202-1341), one CTA per row:
 // first differences of consecutive valid pixels, then <= 3 passes of 5-sigma clipping of the
 // differences around their mean; row value = sigma, or -1 when the row yields < 2 differences.
+// Each warp compacts a contiguous segment of the row with coalesced loads (ballot + popc keep the
+// pixel order); clipped differences are overwritten with a marker.
+struct NoiseAcc { double s, s2; unsigned long long k; };
+static constexpr unsigned NOISE_CLIPPED = 0xffc0c11bu;	// NaN payload no arithmetic produces: marks a clipped difference
+
 template <typename T>
-__global__ void noise_rows_kernel(const T *d, long nx, long ny, double *rowsd) {
+__global__ void __launch_bounds__(NT) noise_rows_kernel(const T *d, long nx, long ny, double *rowsd) {
 	extern __shared__ unsigned char sm[];
-	float *vals = (float *) sm;				// nx floats: valid pixels, then differences
-	unsigned char *keep = (unsigned char *) (vals + nx);
-	__shared__ int cnts[NT + 1];
-	__shared__ double shd[32]; __shared__ unsigned long long shu[32];
-	auto addd = [](double a, double b) { return a + b; };
-	auto addu = [](unsigned long long a, unsigned long long b) { return a + b; };
+	float *vals = (float *) sm;				// nx floats: valid pixels in order
+	float *dif = vals + nx;					// nx floats: the staged row, then the first differences
+	__shared__ int wc[NT / 32];
+	__shared__ NoiseAcc acc[NT / 32];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const long seg = (((nx + NT / 32 - 1) / (NT / 32)) + 31) & ~31L;
+	const long s0 = warp * seg, s1 = s0 + seg < nx ? s0 + seg : nx;
 	for (long row = blockIdx.x; row < ny; row += gridDim.x) {
 		const T *rp = d + row * nx;
-		const int chunk = (int) ((nx + NT - 1) / NT);
-		const long b0 = (long) threadIdx.x * chunk, b1 = b0 + chunk < nx ? b0 + chunk : nx;
+		// stage the row (independent coalesced loads), then compact from shared memory
+		#pragma unroll 8
+		for (long i = threadIdx.x; i < nx; i += NT) dif[i] = (float) rp[i];
+		__syncthreads();
 		int c = 0;
-		for (long i = b0; i < b1; i++) { const float v = (float) rp[i]; if (rp[i] != (T) 0 && v == v) c++; }
-		cnts[threadIdx.x + 1] = c;
-		if (threadIdx.x == 0) cnts[0] = 0;
+		for (long i0 = s0; i0 < s1; i0 += 32) {
+			const long i = i0 + lane;
+			bool ok = false;
+			if (i < s1) { const float v = dif[i]; ok = v != 0.f && v == v; }
+			c += __popc(__ballot_sync(0xffffffffu, ok));
+		}
+		if (lane == 0) wc[warp] = c;
 		__syncthreads();
-		if (threadIdx.x == 0) for (int k = 1; k <= NT; k++) cnts[k] += cnts[k - 1];
-		__syncthreads();
-		int o = cnts[threadIdx.x];
-		const int M = cnts[NT];
-		for (long i = b0; i < b1; i++) { const float v = (float) rp[i]; if (rp[i] != (T) 0 && v == v) vals[o++] = v; }
+		int o = 0, M = 0;
+		for (int k = 0; k < NT / 32; k++) { if (k < warp) o += wc[k]; M += wc[k]; }
+		for (long i0 = s0; i0 < s1; i0 += 32) {
+			const long i = i0 + lane;
+			bool ok = false; float v = 0.f;
+			if (i < s1) { v = dif[i]; ok = v != 0.f && v == v; }
+			const unsigned bal = __ballot_sync(0xffffffffu, ok);
+			if (ok) vals[o + __popc(bal & ((1u << lane) - 1u))] = v;
+			o += __popc(bal);
+		}
 		__syncthreads();
 		const int nd = M - 1;					// number of differences
-		// differences in place, in batches: read the pairs, barrier, write (no read/write hazard)
-		for (int base = 0; base < nd; base += NT * 8) {
-			float tmp[8];
-			#pragma unroll
-			for (int k = 0; k < 8; k++) { const int i = base + k * NT + threadIdx.x; tmp[k] = i < nd ? vals[i] - vals[i + 1] : 0.f; }
-			__syncthreads();
-			#pragma unroll
-			for (int k = 0; k < 8; k++) { const int i = base + k * NT + threadIdx.x; if (i < nd) { vals[i] = tmp[k]; keep[i] = 1; } }
-			__syncthreads();
-		}
 		if (nd < 2) { if (threadIdx.x == 0) rowsd[row] = -1.0; __syncthreads(); continue; }
+		for (int i = threadIdx.x; i < nd; i += NT) dif[i] = vals[i] - vals[i + 1];
+		__syncthreads();
 		double mean = 0, stdev = 0;
 		unsigned long long nv = nd;
 		for (int iter = 0; iter <= 3; iter++) {
 			double s = 0, s2 = 0; unsigned long long kk = 0;
 			for (int i = threadIdx.x; i < nd; i += NT) {
-				if (!keep[i]) continue;
+				const float dv = dif[i];
+				if (__float_as_uint(dv) == NOISE_CLIPPED) continue;
 				if (iter > 0) {
-					const float dv = vals[i];
 					const double dev = (sizeof(T) == 4) ? fabs((double) (dv - (float) mean)) : fabs((double) dv - mean);
-					if (!(dev < 5. * stdev)) { keep[i] = 0; continue; }
+					if (!(dev < 5. * stdev)) { dif[i] = __uint_as_float(NOISE_CLIPPED); continue; }
 				}
-				const double x = (double) vals[i]; s += x; s2 += x * x; kk++;
+				const double x = (double) dv; s += x; s2 += x * x; kk++;
 			}
-			s = block_reduce(s, addd, shd); s2 = block_reduce(s2, addd, shd); kk = block_reduce(kk, addu, shu);
+			for (int off = 16; off; off >>= 1) {
+				s += __shfl_xor_sync(0xffffffffu, s, off); s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+				kk += __shfl_xor_sync(0xffffffffu, kk, off);
+			}
+			if (lane == 0) acc[warp] = NoiseAcc{ s, s2, kk };
+			__syncthreads();
+			s = acc[0].s; s2 = acc[0].s2; kk = acc[0].k;
+			for (int k = 1; k < NT / 32; k++) { s += acc[k].s; s2 += acc[k].s2; kk += acc[k].k; }
+			__syncthreads();
 			if (iter > 0 && kk == nv) break;		// nothing clipped: keep previous mean/stdev
 			nv = kk;
 			if (nv > 1) { mean = s / (double) nv; stdev = sqrt((s2 / (double) nv) - (mean * mean)); }
 			else if (nv == 1) { mean = s; stdev = 0.0; }
 			else { mean = 0.; stdev = 0.; }
 			if (iter == 0 && !(stdev > 0.)) break;
-			__syncthreads();
 		}
 		if (threadIdx.x == 0) rowsd[row] = stdev;
 		__syncthreads();
@@ -432,7 +480,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(BasicPartial), cudaMemcpyDeviceToHost, ctx->stream));
 	// pass B (bgnoise) queued behind it
 	if (nx >= 3) {
-		const size_t shm = (size_t) nx * 5 + 16;
+		const size_t shm = (size_t) nx * 8 + 16;
 		if (shm + 4096 > ctx->smem_optin) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rows of %ld pixels do not fit in shared memory", nx);	// + the kernel's static arrays
 		if (shm + 4096 > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(noise_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
 		noise_rows_kernel<T><<<(unsigned) std::min<long>(ny, 148 * 8), NT, shm, ctx->stream>>>(d, nx, ny, d_rows);

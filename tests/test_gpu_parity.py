@@ -231,7 +231,8 @@ def test_config_c1_shape(orc):
 @pytest.mark.parametrize("case", [
     (100, np.float32, O.WINSORIZED), (100, np.float32, O.SIGMA), (200, np.float32, None), (300, np.float32, O.GESDT),
     (300, np.float32, O.SIGMA), (500, np.uint16, O.LINEARFIT), (130, np.uint16, O.GESDT), (257, np.uint16, O.SIGMA),
-    (65, np.float32, O.PERCENTILE), (600, np.float32, O.SIGMA), (1100, np.uint16, None)],
+    (65, np.float32, O.PERCENTILE), (600, np.float32, O.SIGMA), (1100, np.uint16, None),
+    (90, np.float32, O.SIGMA), (180, np.float32, O.WINSORIZED), (350, np.float32, O.SIGMA), (700, np.uint16, O.SIGMA), (330, np.float32, None)],
     ids=lambda c: f"{c[0]}-{np.dtype(c[1]).name}-{'median' if c[2] is None else NAMES[c[2]]}")
 def test_deep_stacks(orc, case):
     """stack depths of the benchmark configs (BASELINE.json C2..C5) on a small image: every
