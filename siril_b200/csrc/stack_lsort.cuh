@@ -98,7 +98,7 @@ __device__ __forceinline__ int lsort_pixel(int r, int g) {
 }
 
 template <int LT, int RE, int RS, int RF, int SUB, int NW>
-__global__ void __launch_bounds__(NW * 32, 768 / (NW * 32)) stack_lsort_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
+__global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) / (NW * 32)) stack_lsort_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int T = 1 << LT, Q = 32 >> LT, PXC = SUB * TILE_PX;
 	extern __shared__ __align__(1024) unsigned char smem_raw[];
 	const int N = p.N;
