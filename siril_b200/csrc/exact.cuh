@@ -31,6 +31,7 @@ struct Col {
 
 struct RejCfg {
 	int type; float s0, s1; const float *crit; int nb_frames; float m_x, m_dx2;
+	const float *xf;	// optional table 1.f / (i + 1) (median_and_mean.c:1493) for the linear-fit running means; nullptr: computed in place
 };
 
 // ---- rounding helpers (src/core/proto.h:208-237, 324-346) ----

@@ -275,30 +275,71 @@ SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S
 // replayed in float exactly as the reference does: its quicksort leaves the canonical ascending
 // order, which is what `s` already holds (and compaction keeps it), so nothing here depends on
 // anything but the values.  `xf` is the reference's table 1.f / (i + 1) (median_and_mean.c:1493).
+// ranks [i0, i0 + 8) of the stack (0.f beyond n): the loads are independent of the float chains
+// below, so a block is in flight while the previous one is consumed
+template <class Acc>
+SGPU_HD __forceinline__ void acc_load8(const Acc &s, int i0, int n, float (&x)[8]) {
+#pragma unroll
+	for (int k = 0; k < 8; k++) x[k] = (i0 + k < n) ? s(i0 + k) : 0.f;
+}
+SGPU_HD __forceinline__ void xf_load8(const float *xf, int i0, float (&r)[8]) {
+#pragma unroll
+	for (int k = 0; k < 8; k++) r[k] = xf ? xf[i0 + k] : 1.f / (float) (i0 + k + 1);
+}
+
 template <class Acc>
 SGPU_HD void fast_linearfit(Acc &s, int n, const RejCfg &c, int rej[2], FastRes &o) {
 	int N = n, r = 0, changed;
+	const float *xf = c.xf;		// holds >= nb_frames rounded up to 8 entries when given
 	do {
-		float m_y = s(0);
-		for (int i = 1; i < N; i++) m_y += (s(i) - m_y) * (1.f / (i + 1));
+		float x[8], rc[8];
+		float m_y = 0.f;
+		for (int i0 = 0; i0 < N; i0 += 8) {
+			acc_load8(s, i0, N, x); xf_load8(xf, i0, rc);
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const int i = i0 + k;
+				if (i == 0) m_y = x[0];
+				else if (i < N) m_y += (x[k] - m_y) * rc[k];
+			}
+		}
 		float m_dxdy = 0.f, dx = -c.m_x;
-		for (int i = 0; i < N; i++, dx += 1.f) {
-			const float dy = s(i) - m_y;
-			m_dxdy += (dx * dy - m_dxdy) * (1.f / (i + 1));
+		for (int i0 = 0; i0 < N; i0 += 8) {
+			acc_load8(s, i0, N, x); xf_load8(xf, i0, rc);
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				if (i0 + k < N) {
+					const float dy = x[k] - m_y;
+					m_dxdy += (dx * dy - m_dxdy) * rc[k];
+					dx += 1.f;
+				}
+			}
 		}
 		const float a = m_dxdy * c.m_dx2;	// slope
 		const float b = m_y - c.m_x * a;	// intercept
 		float sigma = 0.f;
-		for (int f = 0; f < N; f++) sigma += fabsf(s(f) - (a * f + b));
+		for (int i0 = 0; i0 < N; i0 += 8) {
+			acc_load8(s, i0, N, x);
+#pragma unroll
+			for (int k = 0; k < 8; k++) if (i0 + k < N) sigma += fabsf(x[k] - (a * (i0 + k) + b));
+		}
 		sigma /= (float) N;
 		int out = 0;
-		for (int f = 0; f < N; f++) {
-			const float v = s(f); int flag = 0;
-			if (N - r > 4) {
-				if (a * f + b - v > sigma * c.s0) { rej[0]++; flag = -1; r++; }
-				else if (v - a * f - b > sigma * c.s1) { rej[1]++; flag = 1; r++; }
+		const float tl = sigma * c.s0, th = sigma * c.s1;
+		for (int i0 = 0; i0 < N; i0 += 8) {
+			acc_load8(s, i0, N, x);
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const int f = i0 + k;
+				if (f < N) {
+					const float v = x[k]; int flag = 0;
+					if (N - r > 4) {
+						if (a * f + b - v > tl) { rej[0]++; flag = -1; r++; }
+						else if (v - a * f - b > th) { rej[1]++; flag = 1; r++; }
+					}
+					if (!flag) { if (f != out) s.set(out, v); out++; }
+				}
 			}
-			if (!flag) { if (f != out) s.set(out, v); out++; }
 		}
 		changed = N != out; N = out;
 	} while (changed && N > 3);

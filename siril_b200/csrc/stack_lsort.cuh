@@ -85,6 +85,13 @@ struct SubStack {
 	__device__ __forceinline__ float operator()(int i) const { return *at(i); }
 	__device__ __forceinline__ void set(int i, float v) const { *at(i) = v; }
 };
+// ranks [i0, i0 + 8), i0 a multiple of 8: one base address, eight fixed offsets (the swizzle term of
+// row i0 + k is (k ^ c) & 7)
+__device__ __forceinline__ void acc_load8(const SubStack &s, int i0, int n, float (&x)[8]) {
+	const char *q = s.base + (size_t) i0 * 128;
+#pragma unroll
+	for (int k = 0; k < 8; k++) x[k] = (i0 + k < n) ? *(const float *) (q + k * 128 + (((k ^ s.c) & 7) << 4)) : 0.f;
+}
 
 // pixel (within a sub-tile) of group g of a warp in sort round r (T rounds cover the 32 pixels):
 // chosen so that the lanes of a warp hit different banks when they read rows j*T + t of the
@@ -213,6 +220,13 @@ __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) /
 		}
 	}
 	__syncthreads();
+	RejCfg rc = p.rc;
+	if (p.is_mean && rc.type == SGPU_LINEARFIT) {	// table 1.f / (i + 1) of the running means, over the (now dead) coefficients
+		float *xf = (float *) coef;
+		for (int i = threadIdx.x; i < ((N + 7) & ~7); i += NW * 32) xf[i] = 1.f / (float) (i + 1);
+		rc.xf = xf;
+		__syncthreads();
+	}
 	if (threadIdx.x >= PXC) return;
 
 	// ---- reject / combine: thread i of the CTA owns pixel i of the tile ----
@@ -231,10 +245,10 @@ __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) /
 				const Sums *S0 = (p.need_sums && n > 0) ? &sums[threadIdx.x] : nullptr;
 				if (p.is_u16) {
 					auto orig = [&](int ff) { return (float) load_norm<u16>(p, ff, layer, pix, x); };
-					result = fast_mean_and_reject<true>(st, n, N, p.rc, w, orig, S0, rej, &status);
+					result = fast_mean_and_reject<true>(st, n, N, rc, w, orig, S0, rej, &status);
 				} else {
 					auto orig = [&](int ff) { return load_norm<float>(p, ff, layer, pix, x); };
-					result = fast_mean_and_reject<false>(st, n, N, p.rc, w, orig, S0, rej, &status);
+					result = fast_mean_and_reject<false>(st, n, N, rc, w, orig, S0, rej, &status);
 				}
 			} else {	// all N samples, zeros included (median_and_mean.c:1711-1715)
 				result = p.is_u16 ? median_sorted<true>(st, 0, N) : median_sorted<false>(st, 0, N);
