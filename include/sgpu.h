@@ -150,6 +150,26 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 int sgpu_minmax_nonzero(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]);
 int sgpu_rescale_0_1(sgpu_ctx *ctx, float *d_img, size_t n, float mini, float maxi);
 
+/* ---- sum / max / min stackers (replace sum_stacking_image_hook + _finalize_hook, sum.c:107-372,
+ * and minmax_stacking_image_hook, stackminmax.c:103-184) ------------------------------------- */
+#define SGPU_SIMPLE_SUM 0	/* stack_summing_generic (sum.c:418) */
+#define SGPU_SIMPLE_MAX 1	/* stack_addmax (stackminmax.c:301) */
+#define SGPU_SIMPLE_MIN 2	/* stack_addmin (stackminmax.c:305) */
+/* One pass over the frames of a resident block.  shiftx / shifty: the integer registration shifts
+ * (host arrays of nb_frames, or NULL); the block's rows must have been uploaded with the same
+ * shifty (sgpu_block_upload_frame), row0 is the image row of block row 0 and frame_height the full
+ * frame height: a pixel outside a shifted frame is skipped, as in the reference, not read as zero.
+ * d_acc (device, [nb_layers][height][width]): SUM -> double (float samples) or uint64_t (WORD
+ * samples) sums, and *max_out (host, may be NULL) their maximum over the block, never below 0;
+ * MAX / MIN -> the result in the sample type.  SUM with max_out synchronizes the stream. */
+int sgpu_simple_block(sgpu_ctx *ctx, sgpu_block *blk, int op, const int *shiftx, const int *shifty,
+		int row0, int frame_height, void *d_acc, double *max_out);
+/* sum.c:307-343 with the maximum over the WHOLE image (reduce it over row shards first): float
+ * output = (float)(sum / max); WORD output = sum, scaled by 65535 / max when max > 65535.
+ * Fails like the reference when max is 0 (sum.c:266, :275). */
+int sgpu_sum_convert(sgpu_ctx *ctx, const void *d_acc, int acc_is_float, size_t n, double max,
+		int output_32bits, void *d_out);
+
 /* ---- normalization inputs (replaces compute_normalization, normalization.c:217) --------------- */
 /* imstats fields in the reference's order (core/siril.h:407-413) */
 typedef struct {

@@ -56,6 +56,11 @@ RANGES = {
     "quant_diffmeansigma": ("src/algos/quantize.c", 327, 422, None),
     "quant_noise1":      ("src/algos/quantize.c", 1202, 1501, None),
     "norm_factors":      ("src/stacking/normalization.c", 144, 181, None),
+    # --- sum / min / max stackers (ref_simple.c) ---
+    "sum_pixel_loop":    ("src/stacking/sum.c", 186, 231, None),
+    "sum_find_max":      ("src/stacking/sum.c", 257, 279, None),
+    "sum_convert":       ("src/stacking/sum.c", 308, 344, None),
+    "minmax_pixel_loop": ("src/stacking/stackminmax.c", 160, 182, None),
 }
 
 HASHES_FILE = os.path.join(HERE, "ref_ranges.sha256")
@@ -139,9 +144,11 @@ def build():
             objs.append(obj)
         drv = os.path.join(odir, "ref_driver.o")
         run(["gcc"] + BASE + extra + inc + ["-c", os.path.join(HERE, "ref_driver.c"), "-o", drv])
+        smp = os.path.join(odir, "ref_simple.o")
+        run(["gcc"] + BASE + extra + inc + ["-c", os.path.join(HERE, "ref_simple.c"), "-o", smp])
         omp = os.path.join(odir, "ref_omp.o")
         run(["gcc"] + BASE + ["-fopenmp", "-c", os.path.join(HERE, "ref_omp.c"), "-o", omp])
-        run(["g++", "-shared", "-fopenmp", "-o", os.path.join(OUT, so)] + objs + [drv, omp, "-lm"])
+        run(["g++", "-shared", "-fopenmp", "-o", os.path.join(OUT, so)] + objs + [drv, smp, omp, "-lm"])
 
 
 def main():

@@ -115,6 +115,12 @@ class Oracle:
         f.argtypes = [C.c_long, C.c_long, C.c_long, C.c_long, C.c_int, C.c_void_p, C.c_int,
                       C.POINTER(C.c_long), C.POINTER(C.c_int)]
         self._planner = f
+        for nm in ("stack_sum", "stack_minmax"):
+            f = getattr(L, self.px + nm)
+            f.restype = C.c_int
+            f.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        self._sum = getattr(L, self.px + "stack_sum")
+        self._minmax = getattr(L, self.px + "stack_minmax")
         f = getattr(L, self.px + "norm_to_0_1")
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_long, C.c_long, C.c_long]
@@ -208,6 +214,23 @@ class Oracle:
         return dict(out=out, rej_low=rl, rej_high=rh, irej=irej.reshape(3, 2))
 
     # -- normalization -------------------------------------------------------------------
+    def stack_simple(self, frames, op, shiftx=None, shifty=None, output_32bits=None):
+        """sum.c / stackminmax.c on frames [N][C][H][W]; op in ('sum', 'max', 'min').
+        Returns the [C][H][W] result, or None when the reference reports an error (all-zero sum)."""
+        frames = np.ascontiguousarray(frames)
+        N, Cn, H, W = frames.shape
+        is_float = frames.dtype == np.float32
+        sx = None if shiftx is None else np.ascontiguousarray(shiftx, dtype=np.int32)
+        sy = None if shifty is None else np.ascontiguousarray(shifty, dtype=np.int32)
+        if op == "sum":
+            o32 = is_float if output_32bits is None else bool(output_32bits)
+            out = np.zeros((Cn, H, W), dtype=np.float32 if o32 else np.uint16)
+            rv = self._sum(int(is_float), _ptr(frames), N, Cn, H, W, _ptr(sx), _ptr(sy), int(o32), _ptr(out))
+        else:
+            out = np.zeros((Cn, H, W), dtype=frames.dtype)
+            rv = self._minmax(int(is_float), _ptr(frames), N, Cn, H, W, _ptr(sx), _ptr(sy), int(op == "max"), _ptr(out))
+        return None if rv else out
+
     def image_stats(self, plane, lite=False):
         plane = np.ascontiguousarray(plane)
         ny, nx = plane.shape

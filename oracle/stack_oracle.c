@@ -956,3 +956,90 @@ int orc_planner(long max_rows, long W, long H, long C, int nb_threads, long *blo
 	} while (ch < C);
 	return 0;
 }
+
+/* ---- sum / min / max stackers (src/stacking/sum.c, src/stacking/stackminmax.c) ------------------
+ * Frames [N][C][H][W], output [C][H][W]; shiftx/shifty are the integer registration shifts the
+ * reference rounds from the homography (sum.c:160-173): output pixel (x, y) takes source pixel
+ * (x - shiftx, y - shifty) of each frame when that lies inside the frame (sum.c:186-193,
+ * stackminmax.c:160-167). */
+
+/* sum.c:193-205 (accumulate: double for float input, 64-bit integer for WORD), :256-278 (maximum
+ * over all layers; an all-zero sum is an error), :307-343 (output: float = sum / max; WORD = sum,
+ * or sum * 65535 / max when the maximum does not fit) */
+int orc_stack_sum(int is_float, const void *frames, int N, int C, int H, int W,
+		const int *shiftx, const int *shifty, int output_32bits, void *out) {
+	const size_t np = (size_t) H * W, nb = np * C;
+	double *fsum = is_float ? calloc(nb, sizeof(double)) : NULL;
+	uint64_t *sum = is_float ? NULL : calloc(nb, sizeof(uint64_t));
+	for (int f = 0; f < N; f++) {
+		const int sx = shiftx ? shiftx[f] : 0, sy = shifty ? shifty[f] : 0;
+		for (int y = 0; y < H; y++) {
+			const int ny = y - sy;
+			if (ny < 0 || ny >= H) continue;
+			for (int x = 0; x < W; x++) {
+				const int nx = x - sx;
+				if (nx < 0 || nx >= W) continue;
+				for (int l = 0; l < C; l++) {
+					const size_t src = ((size_t) f * C + l) * np + (size_t) ny * W + nx, dst = l * np + (size_t) y * W + x;
+					if (is_float) fsum[dst] += (double) ((const float *) frames)[src];
+					else sum[dst] += ((const u16 *) frames)[src];
+				}
+			}
+		}
+	}
+	int rv = 0;
+	if (is_float) {
+		double fmax = 0.0;
+		for (size_t i = 0; i < nb; i++) if (fsum[i] > fmax) fmax = fsum[i];
+		if (!fmax) rv = 1;
+		else if (output_32bits) {
+			const double ratio = 1.0 / fmax;
+			for (size_t i = 0; i < nb; i++) ((float *) out)[i] = (float) (fsum[i] * ratio);
+		} else rv = 1;	/* sum.c has no float -> WORD branch (a float sequence always stacks to 32 bits) */
+	} else {
+		uint64_t max = 0;
+		for (size_t i = 0; i < nb; i++) if (sum[i] > max) max = sum[i];
+		if (!max) rv = 1;
+		else if (output_32bits) {
+			const double ratio = 1.0 / (double) max;
+			for (size_t i = 0; i < nb; i++) ((float *) out)[i] = (float) ((double) sum[i] * ratio);
+		} else {
+			double ratio = 1.0;
+			if (max > 65535) ratio = 65535.0 / (double) max;
+			for (size_t i = 0; i < nb; i++)
+				((u16 *) out)[i] = ratio == 1.0 ? rnd_word((double) sum[i]) : rnd_word((double) sum[i] * ratio);
+		}
+	}
+	free(fsum); free(sum);
+	return rv;
+}
+
+/* stackminmax.c:49-84 (start from 0 / 1.0f / USHRT_MAX), :168-181 (strict comparisons) */
+int orc_stack_minmax(int is_float, const void *frames, int N, int C, int H, int W,
+		const int *shiftx, const int *shifty, int ismax, void *out) {
+	const size_t np = (size_t) H * W, nb = np * C;
+	if (is_float) for (size_t i = 0; i < nb; i++) ((float *) out)[i] = ismax ? 0.0f : 1.0f;
+	else for (size_t i = 0; i < nb; i++) ((u16 *) out)[i] = ismax ? 0 : 65535;
+	for (int f = 0; f < N; f++) {
+		const int sx = shiftx ? shiftx[f] : 0, sy = shifty ? shifty[f] : 0;
+		for (int y = 0; y < H; y++) {
+			const int ny = y - sy;
+			if (ny < 0 || ny >= H) continue;
+			for (int x = 0; x < W; x++) {
+				const int nx = x - sx;
+				if (nx < 0 || nx >= W) continue;
+				for (int l = 0; l < C; l++) {
+					const size_t src = ((size_t) f * C + l) * np + (size_t) ny * W + nx, dst = l * np + (size_t) y * W + x;
+					if (is_float) {
+						const float cur = ((const float *) frames)[src], acc = ((float *) out)[dst];
+						if ((ismax && cur > acc) || (!ismax && cur < acc)) ((float *) out)[dst] = cur;
+					} else {
+						const u16 cur = ((const u16 *) frames)[src], acc = ((u16 *) out)[dst];
+						if ((ismax && cur > acc) || (!ismax && cur < acc)) ((u16 *) out)[dst] = cur;
+					}
+				}
+			}
+		}
+	}
+	return 0;
+}

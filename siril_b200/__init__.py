@@ -7,6 +7,7 @@ do_normalization), used by the tests and the benchmark.  There is no CPU fallbac
 works anywhere, computing needs the CUDA library and a GPU and fails loudly otherwise.
 """
 from .enums import *  # noqa: F401,F403
-from .stacking import (StackingArgs, NormCoeff, main_stack, stack_mean_with_rejection, stack_median,  # noqa: F401
+from .stacking import (StackingArgs, NormCoeff, main_stack, stack_mean_with_rejection, stack_median,
+                       stack_summing_generic, stack_addmax, stack_addmin,  # noqa: F401
                        do_normalization, StackResult, gesdt_critical_values)
 from ._lib import lib, SgpuError, Context  # noqa: F401

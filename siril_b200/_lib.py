@@ -6,6 +6,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SGPU_LIB") or os.path.join(HERE, "libsgpu.so")
 
 
+SIMPLE_SUM, SIMPLE_MAX, SIMPLE_MIN = 0, 1, 2      # include/sgpu.h SGPU_SIMPLE_*
+
+
 class SgpuError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"sgpu error {code}: {msg}")
@@ -50,6 +53,8 @@ SIGNATURES = {
     "sgpu_launch_count": (C.c_uint64, [P]),
     "sgpu_handover_count": (C.c_uint64, [P]),
     "sgpu_last_engine": (C.c_int, [P]),
+    "sgpu_simple_block": (C.c_int, [P, P, C.c_int, P, P, C.c_int, C.c_int, P, C.POINTER(C.c_double)]),
+    "sgpu_sum_convert": (C.c_int, [P, P, C.c_int, C.c_size_t, C.c_double, C.c_int, P]),
     "sgpu_stats_window_misses": (C.c_uint64, [P]),
     "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),

@@ -266,6 +266,86 @@ def stack_median(args: StackingArgs) -> int:
     return stack_mean_or_median(args, False)
 
 
+def _stack_simple(args: StackingArgs, op: int) -> int:
+    """the sum / max / min stackers (sum.c:375-441, stackminmax.c:186-306) on the GPU: frames as for
+    stack_mean_or_median; shiftx / shifty are the rounded registration shifts (sum.c:160-173)"""
+    import torch
+    L = _lib.lib()
+    host = not _is_torch_cuda(args.frames)
+    frames = args.frames
+    if host:        # host frames go up through torch (plumbing); the result comes back as numpy
+        arr = np.ascontiguousarray(np.stack([np.asarray(f) for f in frames]))
+        if arr.dtype not in (np.float32, np.uint16):
+            raise TypeError(f"unsupported frame dtype {arr.dtype}")
+        t = torch.from_numpy(arr.view(np.int16) if arr.dtype == np.uint16 else arr).cuda()
+        frames = t.view(torch.uint16) if arr.dtype == np.uint16 else t
+        torch.cuda.current_stream().synchronize()
+    ctx = _context(args)
+    n, c, h, w, dt = _shape_dtype(frames)
+    is_float = dt == DATA_FLOAT
+    out32 = bool(args.use_32bit_output)
+    if op == _lib.SIMPLE_SUM and is_float and not out32:
+        raise ValueError("a 32-bit sequence is summed to a 32-bit image (sum.c:399-400)")
+    frames = frames.contiguous()
+    dev = frames.device
+    desc = _lib.BlockDesc(n, c, w, h, dt)
+    sx = None if args.shiftx is None else np.ascontiguousarray(args.shiftx, dtype=np.int32)
+    sy = None if args.shifty is None else np.ascontiguousarray(args.shifty, dtype=np.int32)
+    blk = C.c_void_p()
+    if sy is not None and np.any(sy != 0):
+        ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
+        es = frames.element_size()
+        for f in range(n):
+            ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0, int(sy[f])))
+    else:
+        ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
+    ptr = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    try:
+        if op == _lib.SIMPLE_SUM:
+            acc = torch.empty((c, h, w), dtype=torch.float64 if is_float else torch.int64, device=dev)
+            mx = C.c_double(0.0)
+            rv = L.sgpu_simple_block(ctx.h, blk, op, ptr(sx), ptr(sy), 0, h, C.c_void_p(acc.data_ptr()), C.byref(mx))
+            out = torch.empty((c, h, w), dtype=torch.float32 if out32 else torch.uint16, device=dev)
+            if rv == 0:
+                rv = L.sgpu_sum_convert(ctx.h, C.c_void_p(acc.data_ptr()), int(is_float), acc.numel(), mx.value,
+                                        int(out32), C.c_void_p(out.data_ptr()))
+        else:
+            out = torch.empty((c, h, w), dtype=frames.dtype, device=dev)
+            rv = L.sgpu_simple_block(ctx.h, blk, op, ptr(sx), ptr(sy), 0, h, C.c_void_p(out.data_ptr()), None)
+        ctx.synchronize()
+        if rv:
+            args.retval = rv
+            args.error = (L.sgpu_last_error(ctx.h) or b"").decode()
+            return rv
+    finally:
+        ctx.synchronize()
+        L.sgpu_block_destroy(blk)
+    res = StackResult()
+    if host:
+        o = out.cpu()
+        res.data = (o.view(torch.int16).numpy().view(np.uint16) if o.dtype == torch.uint16 else o.numpy())
+    else:
+        res.data = out
+    args.result = res
+    args.retval = ST_OK
+    return ST_OK
+
+
+def stack_summing_generic(args: StackingArgs) -> int:
+    """stack_summing_generic (sum.c:375-441): sum of the frames, scaled by its maximum"""
+    return _stack_simple(args, _lib.SIMPLE_SUM)
+
+
+def stack_addmax(args: StackingArgs) -> int:
+    """stack_addmax (stackminmax.c:301-303): per-pixel maximum (starts from 0)"""
+    return _stack_simple(args, _lib.SIMPLE_MAX)
+
+
+def stack_addmin(args: StackingArgs) -> int:
+    """stack_addmin (stackminmax.c:305-306): per-pixel minimum (starts from 1.0 / 65535)"""
+    return _stack_simple(args, _lib.SIMPLE_MIN)
+
+
 def image_stats(ctx, plane, lite=False):
     """statistics(..., STATS_NORM | STATS_LITENORM) of one plane (torch CUDA tensor or numpy)."""
     L = _lib.lib()
