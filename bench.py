@@ -214,6 +214,8 @@ def run_ours(args, wl):
     stats_ms = None
     if nrm != NO_NORM:
         from siril_b200.stacking import compute_estimators, finalize_factors
+        if world > 1:       # the first collective pays the communicator set-up: keep it out of stats_ms
+            dist.all_reduce(torch.zeros(1, device=dev))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         mine = list(range(rank, n, world))
