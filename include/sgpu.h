@@ -178,7 +178,11 @@ typedef struct {
 } sgpu_imstats;
 
 /* statistics_internal_float / _ushort with STATS_NORM (lite: STATS_LITENORM) on one plane of
- * nx*ny samples; `plane` is a device pointer when on_device != 0, else host memory (uploaded). */
+ * nx*ny samples; `plane` is a device pointer when on_device != 0, else host memory (uploaded).
+ * lite == SGPU_STATS_NOISE_ONLY stops after STATS_BASIC | STATS_BGNOISE (min, max, ngoodpix, mean,
+ * sigma, bgnoise): the noise estimate the reference logs for a stacked result (bgnoise_image_hook,
+ * command.c:6901); median / mad / location / scale are left 0. */
+#define SGPU_STATS_NOISE_ONLY 2
 int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny,
 		int lite, sgpu_imstats *out);
 

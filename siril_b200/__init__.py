@@ -9,5 +9,5 @@ works anywhere, computing needs the CUDA library and a GPU and fails loudly othe
 from .enums import *  # noqa: F401,F403
 from .stacking import (StackingArgs, NormCoeff, main_stack, stack_mean_with_rejection, stack_median,
                        stack_summing_generic, stack_addmax, stack_addmin,  # noqa: F401
-                       do_normalization, StackResult, gesdt_critical_values)
+                       do_normalization, StackResult, gesdt_critical_values, result_bgnoise)
 from ._lib import lib, SgpuError, Context  # noqa: F401

@@ -515,6 +515,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	out->total = (double) n; out->ngoodpix = (double) ngood; out->mean = mean; out->sigma = sigma;
 	out->min = mn; out->max = mx; out->normValue = normValue; out->bgnoise = bgnoise;
 	if (ngood == 0) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "image has no non-null pixel");	// statistics_float.c:399-403
+	if (lite == SGPU_STATS_NOISE_ONLY) return SGPU_OK;	// STATS_BASIC | STATS_BGNOISE: what the noise estimate of a stacked result needs
 
 	double median, mad, location = 0, scale = 0;
 	if (sizeof(T) == 4) {

@@ -368,6 +368,14 @@ STATS_WORKERS = 8      # concurrent per-plane statistics (contexts / streams) in
 _stats_pool = {}       # device index -> worker contexts
 
 
+def result_bgnoise(args: StackingArgs):
+    """background noise of every layer of the stacked result (FnNoise1 through K3's kernels): what
+    the reference reports after stacking (bgnoise_image_hook, command.c:6901-6910)"""
+    ctx = _context(args)
+    data = args.result.data
+    return [image_stats(ctx, data[layer], lite=2).bgnoise for layer in range(data.shape[0])]
+
+
 def compute_estimators(args: StackingArgs, frame_indices=None):
     """_compute_estimators_for_image over the given frames (all by default): returns
     (offset, mul, scale, bgnoise) arrays [C][N] holding ESTIMATORS (normalization.c:98-141)."""

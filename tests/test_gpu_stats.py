@@ -156,3 +156,26 @@ def test_do_normalization_and_weights(orc, dtype, nrm):
     assert np.array_equal(args.result.irej, o["irej"])
     rel = np.abs(out - o["out"]) / np.maximum(np.abs(o["out"]), 1e-30)
     assert rel.max() <= 1e-6
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+def test_result_bgnoise(orc, dtype):
+    """noise estimate of the stacked result (STATS_BASIC | STATS_BGNOISE only)"""
+    import siril_b200 as sb
+    rng = np.random.default_rng(23)
+    fr = np.stack([np.stack([make_image(rng, 60, 90, dtype, zeros=0.002) for _ in range(3)]) for _ in range(9)])
+    dev = torch.from_numpy(fr.view(np.int16) if dtype == np.uint16 else fr).cuda()
+    if dtype == np.uint16:
+        dev = dev.view(torch.uint16)
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=dev, type_of_rejection=sb.SIGMA, sig=(3, 3))
+    assert args.method(args) == 0
+    got = sb.result_bgnoise(args)
+    res = args.result.data.cpu().numpy()
+    for layer in range(3):
+        exp = orc.image_stats(res[layer], True)
+        assert got[layer] == pytest.approx(exp["bgnoise"], rel=1e-12)
+    st = sb.stacking.image_stats(args.ctx, args.result.data[0], lite=2).asdict()
+    exp = orc.image_stats(res[0], True)
+    for k in ("total", "ngoodpix", "min", "max"):
+        assert st[k] == exp[k]
+    assert st["median"] == 0 and st["mad"] == 0
