@@ -216,9 +216,11 @@ def run_ours(args, wl):
         from siril_b200.stacking import compute_estimators, finalize_factors
         if world > 1:       # the first collective pays the communicator set-up: keep it out of stats_ms
             dist.all_reduce(torch.zeros(1, device=dev))
+        mine = list(range(rank, n, world))
+        from siril_b200.stacking import STATS_WORKERS
+        compute_estimators(sargs, mine[:STATS_WORKERS])     # warm-up: worker contexts, scratch, kernel attributes
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        mine = list(range(rank, n, world))
         off, mul, sc, bg = compute_estimators(sargs, mine)
         if world > 1:
             from siril_b200 import sharding

@@ -373,17 +373,28 @@ int minmax_sel(Sweep &w, const Sel &s, float &mn, float &mx, size_t &cnt) {
 
 // launch-side of the windowed histograms: zero [HWIN bins | below], sweep, read back
 template <typename Launch>
-int run_window(Sweep &w, Launch launch, std::vector<unsigned> &h, size_t &below) {
+int run_window(Sweep &w, Launch launch, const unsigned *&h, size_t &below) {
 	sgpu_ctx *ctx = w.ctx;
 	SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, (HWIN + 2) * sizeof(unsigned), ctx->stream));
 	launch(w.d_hist, (unsigned long long *) (w.d_hist + HWIN));
 	ctx->launches++;
 	SGPU_CUDA(ctx, cudaGetLastError());
-	h.resize(HWIN + 2);
-	SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, (HWIN + 2) * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+	unsigned *hh = (unsigned *) ctx->h_params;	// pinned: the read-back is a 5 us DMA, not a staged copy
+	SGPU_CUDA(ctx, cudaMemcpyAsync(hh, w.d_hist, (HWIN + 2) * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	unsigned long long b; memcpy(&b, h.data() + HWIN, sizeof b);
+	unsigned long long b; memcpy(&b, hh + HWIN, sizeof b);
 	below = (size_t) b;
+	h = hh;
+	return SGPU_OK;
+}
+
+// full 65536-bin histogram read back into the pinned arena
+inline int read_full_hist(Sweep &w, const unsigned *&h) {
+	sgpu_ctx *ctx = w.ctx;
+	unsigned *hh = (unsigned *) ctx->h_params;
+	SGPU_CUDA(ctx, cudaMemcpyAsync(hh, w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	h = hh;
 	return SGPU_OK;
 }
 
@@ -400,7 +411,7 @@ int hist_median_float(Sweep &w, const Sel &s, float mn, float mx, size_t cnt, fl
 	if (fabsf(mx - mn) == 0.f) { median = mn; return SGPU_OK; }		// rt_algo.cc:78-81
 	const unsigned hs = (unsigned) std::min<size_t>(65536, cnt);
 	const float scale = (hs - 1) / (mx - mn);
-	std::vector<unsigned> h;
+	const unsigned *h = nullptr;
 	if (ctx->smem_optin >= HWIN * sizeof(unsigned) && !ctx->stats_full_hist) {
 		const unsigned w0 = window_start((double) scale * ((double) guess - (double) mn));
 		size_t below;
@@ -409,17 +420,15 @@ int hist_median_float(Sweep &w, const Sel &s, float mn, float mx, size_t cnt, fl
 			hist_float_win_kernel<T><<<HNB, HNT, HWIN * sizeof(unsigned), ctx->stream>>>((const T *) w.d, w.n, s, mn, scale, w0, hist, d_below);
 		}, h, below);
 		if (rv) return rv;
-		if (finish_hist_median_float(h.data(), w0, w0 + HWIN, below, cnt, mn, mx, scale, median)) return SGPU_OK;
+		if (finish_hist_median_float(h, w0, w0 + HWIN, below, cnt, mn, mx, scale, median)) return SGPU_OK;
 		ctx->stats_window_misses++;
 	}
 	SGPU_CUDA(ctx, cudaMemsetAsync(w.d_hist, 0, 65536 * sizeof(unsigned), ctx->stream));
 	hist_float_kernel<T><<<NB, NT, 0, ctx->stream>>>((const T *) w.d, w.n, s, mn, scale, w.d_hist);
 	ctx->launches++;
 	SGPU_CUDA(ctx, cudaGetLastError());
-	h.resize(65536);
-	SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
-	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	if (!finish_hist_median_float(h.data(), 0, 65536, 0, cnt, mn, mx, scale, median))
+	{ int rv = read_full_hist(w, h); if (rv) return rv; }
+	if (!finish_hist_median_float(h, 0, 65536, 0, cnt, mn, mx, scale, median))
 		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "histogram median: counts do not reach half of the samples");
 	return SGPU_OK;
 }
@@ -469,8 +478,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	Sweep w{ ctx, d, sizeof(T) == 4 ? SGPU_F32 : SGPU_U16, n, (unsigned *) ctx->d_scratch,
 		 (char *) ctx->d_scratch + 65536 * sizeof(unsigned), nullptr };
 	double *d_rows = (double *) ((char *) w.d_part + part_bytes);
-	std::vector<unsigned char> hp(part_bytes);
-	w.h_part = hp.data();
+	w.h_part = (char *) ctx->h_params + 512 * 1024;	// pinned arena: [0, 256 KB) histograms, [512 KB, ...) partials and row noise
 	memset(out, 0, sizeof(*out));
 
 	// pass A
@@ -487,8 +495,15 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 		ctx->launches++;
 		SGPU_CUDA(ctx, cudaGetLastError());
 	}
-	std::vector<double> rows(nx >= 3 ? ny : 0);
-	if (nx >= 3) SGPU_CUDA(ctx, cudaMemcpyAsync(rows.data(), d_rows, (size_t) ny * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	std::vector<double> rows_big;
+	const double *rows = nullptr;
+	const long nrows = nx >= 3 ? ny : 0;
+	if (nrows) {
+		double *dst = (double *) ((char *) ctx->h_params + 576 * 1024);
+		if ((size_t) nrows * sizeof(double) > ctx->d_params_cap - 576 * 1024) { rows_big.resize(nrows); dst = rows_big.data(); }
+		SGPU_CUDA(ctx, cudaMemcpyAsync(dst, d_rows, (size_t) nrows * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+		rows = dst;
+	}
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
 	const BasicPartial *bp = (const BasicPartial *) w.h_part;
@@ -507,7 +522,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	double bgnoise = 0.0;							// quantize.c:1470-1484
 	{
 		std::vector<double> v;
-		for (double r : rows) if (r >= 0.0) v.push_back(r);
+		for (long i = 0; i < nrows; i++) if (rows[i] >= 0.0) v.push_back(rows[i]);
 		if (v.size() == 1) bgnoise = v[0];
 		else if (v.size() > 1) { std::sort(v.begin(), v.end()); bgnoise = (v[(v.size() - 1) / 2] + v[v.size() / 2]) / 2.; }
 		bgnoise *= .70710678;
@@ -530,7 +545,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 		mad = madf;
 		if (!lite) { rv = ikss<T>(w, 1.f, med, madf, location, scale); if (rv) return rv; }
 	} else {
-		std::vector<unsigned> h;
+		const unsigned *h = nullptr;
 		for (int pass = 0; pass < 2; pass++) {
 			const int imed = pass ? (int) (median + (median >= 0.0 ? 0.5 : -0.5)) : 0;		// round_to_int
 			double m = 0.0;
@@ -543,7 +558,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 					hist_u16_win_kernel<<<HNB, HNT, HWIN * sizeof(unsigned), ctx->stream>>>((const u16 *) d, n, pass, imed, w0, hist, d_below);
 				}, h, below);
 				if (rv) return rv;
-				done = finish_hist_median_u16(h.data(), w0, w0 + HWIN, below, ngood, m);
+				done = finish_hist_median_u16(h, w0, w0 + HWIN, below, ngood, m);
 				if (!done) ctx->stats_window_misses++;
 			}
 			if (!done) {
@@ -551,10 +566,8 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 				hist_u16_kernel<<<NB, NT, 0, ctx->stream>>>((const u16 *) d, n, pass, imed, w.d_hist);
 				ctx->launches++;
 				SGPU_CUDA(ctx, cudaGetLastError());
-				h.resize(65536);
-				SGPU_CUDA(ctx, cudaMemcpyAsync(h.data(), w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
-				SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-				if (!finish_hist_median_u16(h.data(), 0, 65536, 0, ngood, m))
+				rv = read_full_hist(w, h); if (rv) return rv;
+				if (!finish_hist_median_u16(h, 0, 65536, 0, ngood, m))
 					return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "histogram median: counts do not reach half of the samples");
 			}
 			if (pass == 0) median = m; else mad = (double) (float) m;

@@ -7,6 +7,7 @@ Names, argument meaning and error behaviour follow the reference:
   do_normalization                         src/stacking/normalization.c:46-78
 All computation happens in libsgpu.so (CUDA); this file only marshals arguments.
 """
+import os
 import ctypes as C
 from dataclasses import dataclass, field
 from typing import Any, Callable, Optional
@@ -364,7 +365,7 @@ def image_stats(ctx, plane, lite=False):
     return st
 
 
-STATS_WORKERS = 8      # concurrent per-plane statistics (contexts / streams) in compute_estimators
+STATS_WORKERS = int(os.environ.get("SGPU_STATS_WORKERS", "4"))     # concurrent per-plane statistics (contexts / streams) in compute_estimators
 _stats_pool = {}       # device index -> worker contexts
 
 
