@@ -114,6 +114,37 @@ void *sgpu_block_device_ptr(sgpu_block *blk);
 int sgpu_block_upload_frame(sgpu_block *blk, int frame, const void *host_frame, int frame_height,
 		int row0, int shifty);
 
+/* ---- raw FITS data units ----------------------------------------------------
+ * Replaces, for uncompressed primary-HDU images, the read leg of stack_read_block_data
+ * (median_and_mean.c:382-545 -> seq_opened_read_region -> internal_read_partial_fits,
+ * image_format_fits.c:927-1015): the host moves the file's bytes (pread -> pinned staging -> H2D, two
+ * chunks in flight) and the device does what cfitsio + convert_data_ushort (:390-416) /
+ * convert_floats (:648-672) do on the CPU: big-endian decode, +32768 for 16-bit data, BYTE
+ * widening, the DATAMAX > 10 rescale by INV_USHRT_MAX_SINGLE, y shift and zero fill. */
+typedef struct {
+	int bitpix;		/* 8, 16, 32, -32, -64 as in the header */
+	long naxes[3];		/* NAXIS1..3 (1 when absent) */
+	double bzero, bscale;	/* 0 / 1 when absent */
+	double datamax; int has_datamax;	/* DATAMAX (image_format_fits.c:995-1008) */
+	long data_offset;	/* byte offset of the primary data unit */
+	int device_readable;	/* 1: BYTE, SHORT/USHORT or FLOAT without physical scaling */
+} sgpu_fits_info;
+/* parse the primary header (80-byte cards, 2880-byte blocks, up to END); SGPU_SEQUENCE_ERROR when
+ * the file is missing, not FITS or shorter than its header says */
+int sgpu_fits_probe(const char *path, sgpu_fits_info *info);
+/* data_unit: host memory holding the whole big-endian data unit [layer][frame_height][width] of one
+ * frame (an mmap of the file, or pinned memory from sgpu_host_alloc: then the H2D copy reads it in
+ * place).  bitpix 8 / 16 -> SGPU_U16 blocks, -32 -> SGPU_F32 blocks.  rescale_ushrt: 1 for float data whose
+ * DATAMAX is above 10 (image_format_fits.c:1009-1011), 0 otherwise, -1 when the header has no DATAMAX:
+ * the reference then decides per read from three or four samples of the region (:997-1003), and so
+ * does this call, per layer, on the rows it uploads.  Geometry as sgpu_block_upload_frame.
+ * Asynchronous on the context stream, except for waiting on its own staging buffers. */
+int sgpu_block_upload_fits(sgpu_block *blk, int frame, const void *data_unit, int bitpix,
+		int frame_height, int row0, int shifty, int rescale_ushrt);
+/* the same, reading the rows this block needs from an open file descriptor with pread */
+int sgpu_block_upload_fits_fd(sgpu_block *blk, int frame, int fd, long data_offset, int bitpix,
+		int frame_height, int row0, int shifty, int rescale_ushrt);
+
 /* ---- stacking (replaces the block loop of stack_mean_or_median, median_and_mean.c:1552-1760) -- */
 typedef struct {
 	int is_mean;			/* 1: stack_mean_with_rejection, 0: stack_median */

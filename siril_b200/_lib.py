@@ -37,6 +37,12 @@ class ImStats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class FitsInfo(C.Structure):
+    _fields_ = [("bitpix", C.c_int), ("naxes", C.c_long * 3), ("bzero", C.c_double), ("bscale", C.c_double),
+                ("datamax", C.c_double), ("has_datamax", C.c_int), ("data_offset", C.c_long),
+                ("device_readable", C.c_int)]
+
+
 class ImageBlock(C.Structure):
     _fields_ = [("channel", C.c_long), ("start_row", C.c_long), ("end_row", C.c_long), ("height", C.c_long)]
 
@@ -64,6 +70,10 @@ SIGNATURES = {
     "sgpu_block_destroy": (None, [P]),
     "sgpu_block_device_ptr": (P, [P]),
     "sgpu_block_upload_frame": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int]),
+    "sgpu_fits_probe": (C.c_int, [C.c_char_p, C.POINTER(FitsInfo)]),
+    "sgpu_block_upload_fits": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "sgpu_block_upload_fits_fd": (C.c_int, [P, C.c_int, C.c_int, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_int]),
     "sgpu_stack_block": (C.c_int, [P, P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_stack_host": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P), P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),

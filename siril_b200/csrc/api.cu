@@ -75,6 +75,7 @@ void sgpu_ctx_destroy(sgpu_ctx *ctx) {
 	if (ctx->h_params) cudaFreeHost(ctx->h_params);
 	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
 	if (ctx->d_list) cudaFree(ctx->d_list);
+	sgpu_free_stage(ctx);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
 	delete ctx;

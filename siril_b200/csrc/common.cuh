@@ -26,6 +26,9 @@ struct sgpu_ctx {
 	void *h_params = nullptr;			// pinned mirror
 	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
 	void *d_list = nullptr; size_t d_list_cap = 0; bool list_used = false; int last_engine = 0;		// sorted engine: pixels handed to the exact engine
+	// raw FITS reader (fitsread.cu): two pinned + two device staging chunks, recycled by events
+	void *h_stage[2] = { nullptr, nullptr }, *d_stage[2] = { nullptr, nullptr };
+	cudaEvent_t stage_ev[2] = { nullptr, nullptr }; int stage_idx = 0;
 };
 
 struct sgpu_block {
@@ -43,6 +46,7 @@ int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...);
 int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what);
 int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes);
 int sgpu_ensure_list(sgpu_ctx *ctx, size_t bytes);
+void sgpu_free_stage(sgpu_ctx *ctx);
 
 #define SGPU_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return sgpu_cuda_fail((ctx), e__, #call); } while (0)
 

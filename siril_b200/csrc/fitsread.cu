@@ -1,0 +1,269 @@
+// fitsread.cu — raw FITS data units into a resident frame block.
+//
+// Replaces, for uncompressed primary-HDU images, the read leg of stack_read_block_data
+// (median_and_mean.c:382-545): seq_opened_read_region -> internal_read_partial_fits
+// (image_format_fits.c:927-1015), i.e. cfitsio's fits_read_subset (big-endian decode, BZERO) followed
+// by convert_data_ushort (:390-416) / convert_floats (:648-672).  The host only moves bytes: file
+// rows go pread -> pinned staging -> H2D, two chunks in flight, and the decode (byte swap, +32768,
+// BYTE widening, the DATAMAX > 10 rescale, y shift, zero fill) is a kernel that writes straight into
+// the block.  Rows of a FITS data unit are already in the order Siril keeps in memory (bottom-up),
+// so frame row r of layer l is at byte ((l * frame_height + r) * width) * |BITPIX| / 8.
+#include <cerrno>
+#include <cmath>
+#include <cstdlib>
+#include <fcntl.h>
+#include <unistd.h>
+#include <sys/stat.h>
+#include "common.cuh"
+
+#define SGPU_STAGE_CHUNK ((size_t) 32 << 20)	// bytes of raw rows per staging buffer
+#define INV_USHRT_MAX_SINGLE .000015259022f	// core/siril.h:94
+
+// ---- device decode -------------------------------------------------------------------------------
+// 16-bit: big-endian int16 + 32768 as WORD.  USHORT_IMG (BZERO 32768 applied by cfitsio) and
+// SHORT_IMG (convert_data_ushort: 32768 + (int) data16[i]) are the same map: swap, flip the top bit.
+__device__ __forceinline__ uint32_t dec16x2(uint32_t w) { return __byte_perm(w, 0, 0x2301) ^ 0x80008000u; }
+__device__ __forceinline__ uint32_t bswap32(uint32_t w) { return __byte_perm(w, 0, 0x0123); }
+__device__ __forceinline__ uint32_t dec32(uint32_t w, bool rescale) {
+	w = bswap32(w);
+	return rescale ? __float_as_uint(__uint_as_float(w) * INV_USHRT_MAX_SINGLE) : w;	// convert_floats, default case
+}
+
+// raw and dst have the same address modulo 16 (the staging offset is chosen so): scalar head up to the
+// first 16-byte boundary, 16-byte body, scalar tail.  ES = 2 or 4 bytes per sample on both sides.
+template <int ES>
+__global__ void __launch_bounds__(256) fits_decode_kernel(const unsigned char *__restrict__ raw, unsigned char *__restrict__ dst,
+		size_t bytes, int rescale) {
+	const size_t head = min(bytes, (size_t) ((16 - ((uintptr_t) dst & 15)) & 15));
+	const size_t nvec = (bytes - head) >> 4;
+	const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t) gridDim.x * blockDim.x;
+	const uint4 *rv = (const uint4 *) (raw + head);
+	uint4 *dv = (uint4 *) (dst + head);
+	for (size_t i = tid; i < nvec; i += nth) {
+		uint4 v = __ldg(rv + i);
+		if (ES == 2) { v.x = dec16x2(v.x); v.y = dec16x2(v.y); v.z = dec16x2(v.z); v.w = dec16x2(v.w); }
+		else { v.x = dec32(v.x, rescale); v.y = dec32(v.y, rescale); v.z = dec32(v.z, rescale); v.w = dec32(v.w, rescale); }
+		dv[i] = v;
+	}
+	// head and tail samples (fewer than 16 bytes each)
+	const size_t tail0 = head + (nvec << 4);
+	const size_t nscal = (head + (bytes - tail0)) / ES;
+	for (size_t i = tid; i < nscal; i += nth) {
+		const size_t off = i * ES < head ? i * ES : tail0 + (i * ES - head);
+		if (ES == 2) {
+			const uint16_t w = *(const uint16_t *) (raw + off);
+			*(uint16_t *) (dst + off) = (uint16_t) (((w >> 8) | (w << 8)) ^ 0x8000u);
+		} else *(uint32_t *) (dst + off) = dec32(*(const uint32_t *) (raw + off), rescale);
+	}
+}
+
+// BYTE_IMG: to[i] = (WORD) data8[i] (convert_data_ushort :396-400); rare, kept scalar
+__global__ void __launch_bounds__(256) fits_decode_byte_kernel(const unsigned char *__restrict__ raw, uint16_t *__restrict__ dst, size_t n) {
+	const size_t nth = (size_t) gridDim.x * blockDim.x;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += nth) dst[i] = raw[i];
+}
+
+// ---- staging -------------------------------------------------------------------------------------
+static int ensure_stage(sgpu_ctx *ctx) {
+	if (ctx->h_stage[0]) return SGPU_OK;
+	for (int k = 0; k < 2; k++) {
+		SGPU_CUDA(ctx, cudaMallocHost(&ctx->h_stage[k], SGPU_STAGE_CHUNK + 16));
+		SGPU_CUDA(ctx, cudaMalloc(&ctx->d_stage[k], SGPU_STAGE_CHUNK + 16));
+		SGPU_CUDA(ctx, cudaEventCreateWithFlags(&ctx->stage_ev[k], cudaEventDisableTiming));
+	}
+	return SGPU_OK;
+}
+
+void sgpu_free_stage(sgpu_ctx *ctx) {
+	for (int k = 0; k < 2; k++) {
+		if (ctx->h_stage[k]) cudaFreeHost(ctx->h_stage[k]);
+		if (ctx->d_stage[k]) cudaFree(ctx->d_stage[k]);
+		if (ctx->stage_ev[k]) cudaEventDestroy(ctx->stage_ev[k]);
+		ctx->h_stage[k] = ctx->d_stage[k] = nullptr; ctx->stage_ev[k] = nullptr;
+	}
+}
+
+struct RawSource {	// where the raw bytes of the data unit come from
+	const unsigned char *mem = nullptr;	// host memory holding the data unit, or
+	int fd = -1; off_t base = 0;		// an open file and the offset of the data unit
+	bool pinned = false;			// mem is page-locked: H2D straight from it
+};
+
+static int fill_from(sgpu_ctx *ctx, const RawSource &src, size_t off, void *dst, size_t bytes) {
+	if (src.mem) { memcpy(dst, src.mem + off, bytes); return SGPU_OK; }
+	size_t done = 0;
+	while (done < bytes) {
+		const ssize_t r = pread(src.fd, (char *) dst + done, bytes - done, src.base + (off_t) (off + done));
+		if (r < 0 && errno == EINTR) continue;
+		if (r <= 0) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "short read of FITS data (%zu of %zu bytes at %zu)", done, bytes, off);
+		done += (size_t) r;
+	}
+	return SGPU_OK;
+}
+
+static int decode_launch(sgpu_ctx *ctx, const unsigned char *d_raw, unsigned char *dst, size_t raw_bytes, int bitpix, int rescale) {
+	const size_t work = bitpix == 8 ? raw_bytes : raw_bytes / 16 + 32;
+	size_t grid = (work + 255) / 256;
+	const size_t cap = (size_t) ctx->sm_count * 8;
+	if (grid > cap) grid = cap;
+	if (grid < 1) grid = 1;
+	if (bitpix == 8) fits_decode_byte_kernel<<<(unsigned) grid, 256, 0, ctx->stream>>>(d_raw, (uint16_t *) dst, raw_bytes);
+	else if (bitpix == 16) fits_decode_kernel<2><<<(unsigned) grid, 256, 0, ctx->stream>>>(d_raw, dst, raw_bytes, 0);
+	else fits_decode_kernel<4><<<(unsigned) grid, 256, 0, ctx->stream>>>(d_raw, dst, raw_bytes, rescale);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	return SGPU_OK;
+}
+
+// one frame: for every layer the valid row range is contiguous in the data unit and in the block
+static int upload_raw(sgpu_block *b, int frame, const RawSource &src, int bitpix, int frame_height, int row0, int shifty, int rescale_arg) {
+	sgpu_ctx *ctx = b->ctx;
+	const sgpu_block_desc &d = b->d;
+	if (frame < 0 || frame >= d.nb_frames) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d out of range", frame);
+	const int want = (bitpix == -32) ? SGPU_F32 : SGPU_U16;
+	if (bitpix != 8 && bitpix != 16 && bitpix != -32)
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "FITS image format %d is not supported by the device reader", bitpix);
+	if (d.dtype != want) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "BITPIX %d does not match the block's sample type", bitpix);
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	int rv = ensure_stage(ctx); if (rv) return rv;
+	const size_t es = b->elem(), res = (size_t) abs(bitpix) / 8;	// block / raw bytes per sample
+	const size_t rowb = (size_t) d.width * es, rrow = (size_t) d.width * res;
+	long lo = (long) shifty - row0; if (lo < 0) lo = 0;			// as sgpu_block_upload_frame
+	long hi = (long) frame_height + shifty - row0; if (hi > d.height) hi = d.height;
+	for (int l = 0; l < d.nb_layers; l++) {
+		unsigned char *dst = (unsigned char *) b->dev + (((size_t) frame * d.nb_layers + l) * b->plane()) * es;
+		if (hi <= lo) { SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) d.height * rowb, ctx->stream)); continue; }
+		if (lo > 0) SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) lo * rowb, ctx->stream));
+		if (hi < d.height) SGPU_CUDA(ctx, cudaMemsetAsync(dst + (size_t) hi * rowb, 0, (size_t) (d.height - hi) * rowb, ctx->stream));
+		unsigned char *out = dst + (size_t) lo * rowb;
+		size_t roff = ((size_t) l * frame_height + (size_t) (row0 + lo - shifty)) * rrow;	// into the data unit
+		size_t left = (size_t) (hi - lo) * rrow;
+		int rescale = rescale_arg > 0;
+		if (rescale_arg < 0 && bitpix == -32) {
+			// no DATAMAX key: the reference looks at three or four samples of the region it has just read
+			// "and hopes for the best" (image_format_fits.c:997-1003), separately for every read
+			const size_t nbdata = (size_t) (hi - lo) * d.width;
+			if (nbdata > 3) {
+				double data_max = 0.;
+				for (size_t i = 0; i < nbdata; i += nbdata / 3) {
+					unsigned char q[4];
+					rv = fill_from(ctx, src, roff + i * 4, q, 4); if (rv) return rv;
+					const uint32_t w = ((uint32_t) q[0] << 24) | ((uint32_t) q[1] << 16) | ((uint32_t) q[2] << 8) | q[3];
+					float x; memcpy(&x, &w, 4);
+					data_max = (data_max > x) ? data_max : x;	// the reference's max() macro, NaN included
+				}
+				rescale = data_max > 10.0;
+			}
+		}
+		while (left) {
+			// the staging copy sits at the same address modulo 16 as its destination (16-byte decode)
+			const size_t pad = bitpix == 8 ? 0 : ((uintptr_t) out & 15);
+			const size_t n = left < SGPU_STAGE_CHUNK ? left : SGPU_STAGE_CHUNK;	// a multiple of 16 except the last
+			const int k = ctx->stage_idx; ctx->stage_idx ^= 1;
+			SGPU_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));	// buffer k's previous chunk has been decoded
+			unsigned char *d_raw = (unsigned char *) ctx->d_stage[k] + pad;
+			if (src.pinned) {
+				SGPU_CUDA(ctx, cudaMemcpyAsync(d_raw, src.mem + roff, n, cudaMemcpyHostToDevice, ctx->stream));
+			} else {
+				unsigned char *h_raw = (unsigned char *) ctx->h_stage[k] + pad;
+				rv = fill_from(ctx, src, roff, h_raw, n); if (rv) return rv;
+				SGPU_CUDA(ctx, cudaMemcpyAsync(d_raw, h_raw, n, cudaMemcpyHostToDevice, ctx->stream));
+			}
+			rv = decode_launch(ctx, d_raw, out, n, bitpix, rescale); if (rv) return rv;
+			SGPU_CUDA(ctx, cudaEventRecord(ctx->stage_ev[k], ctx->stream));
+			out += n / res * es; roff += n; left -= n;
+		}
+	}
+	return SGPU_OK;
+}
+
+// ---- primary header ------------------------------------------------------------------------------
+static bool card_value(const char *card, const char *key, double *v) {
+	const size_t kl = strlen(key);
+	if (strncmp(card, key, kl) != 0) return false;
+	for (size_t i = kl; i < 8; i++) if (card[i] != ' ') return false;
+	if (card[8] != '=') return false;
+	char buf[72]; memcpy(buf, card + 10, 70); buf[70] = 0;
+	char *sl = strchr(buf, '/'); if (sl) *sl = 0;
+	for (char *p = buf; *p; p++) if (*p == 'D' || *p == 'd') *p = 'E';	// Fortran exponents
+	char *end = nullptr;
+	const double x = strtod(buf, &end);
+	if (end == buf) return false;
+	*v = x;
+	return true;
+}
+
+extern "C" {
+
+int sgpu_fits_probe(const char *path, sgpu_fits_info *info) {
+	if (!path || !info) return SGPU_GENERIC_ERROR;
+	memset(info, 0, sizeof *info);
+	info->bscale = 1.0;
+	const int fd = open(path, O_RDONLY);
+	if (fd < 0) return SGPU_SEQUENCE_ERROR;
+	char blk[2880];
+	long off = 0;
+	int naxis = -1, rv = SGPU_SEQUENCE_ERROR;
+	bool first = true, done = false;
+	info->naxes[0] = info->naxes[1] = info->naxes[2] = 1;
+	while (!done) {
+		size_t got = 0;
+		while (got < sizeof blk) {
+			const ssize_t r = pread(fd, blk + got, sizeof blk - got, off + (long) got);
+			if (r < 0 && errno == EINTR) continue;
+			if (r <= 0) break;
+			got += (size_t) r;
+		}
+		if (got < sizeof blk) break;
+		if (first && strncmp(blk, "SIMPLE  =", 9) != 0) break;
+		first = false;
+		off += (long) sizeof blk;
+		for (int c = 0; c < 36; c++) {
+			const char *card = blk + 80 * c;
+			double v;
+			if (strncmp(card, "END     ", 8) == 0) { done = true; break; }
+			if (card_value(card, "BITPIX", &v)) info->bitpix = (int) v;
+			else if (card_value(card, "NAXIS", &v)) naxis = (int) v;
+			else if (card_value(card, "NAXIS1", &v)) info->naxes[0] = (long) v;
+			else if (card_value(card, "NAXIS2", &v)) info->naxes[1] = (long) v;
+			else if (card_value(card, "NAXIS3", &v)) info->naxes[2] = (long) v;
+			else if (card_value(card, "BZERO", &v)) info->bzero = v;
+			else if (card_value(card, "BSCALE", &v)) info->bscale = v;
+			else if (card_value(card, "DATAMAX", &v)) { info->datamax = v; info->has_datamax = 1; }
+		}
+	}
+	struct stat st;
+	if (done && naxis >= 2 && naxis <= 3 && info->bitpix != 0 && fstat(fd, &st) == 0) {
+		info->data_offset = off;
+		const long need = info->naxes[0] * info->naxes[1] * info->naxes[2] * (labs((long) info->bitpix) / 8);
+		if (info->naxes[0] > 0 && info->naxes[1] > 0 && info->naxes[2] > 0 && st.st_size >= off + need) rv = SGPU_OK;
+	}
+	close(fd);
+	if (rv) return rv;
+	// what the device reader decodes without cfitsio: BYTE, SHORT (BZERO 0), USHORT (BZERO 32768) and
+	// FLOAT without physical scaling (fits_uses_physical_scaling, image_format_fits.c:521-553)
+	const bool plain = info->bscale == 1.0;
+	info->device_readable = plain && ((info->bitpix == 8 && info->bzero == 0.0) ||
+			(info->bitpix == 16 && (info->bzero == 0.0 || info->bzero == 32768.0)) ||
+			(info->bitpix == -32 && info->bzero == 0.0));
+	return SGPU_OK;
+}
+
+int sgpu_block_upload_fits(sgpu_block *b, int frame, const void *data_unit, int bitpix,
+		int frame_height, int row0, int shifty, int rescale_ushrt) {
+	if (!b || !data_unit) return SGPU_GENERIC_ERROR;
+	RawSource src; src.mem = (const unsigned char *) data_unit;
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, data_unit) == cudaSuccess) src.pinned = at.type == cudaMemoryTypeHost;
+	else cudaGetLastError();
+	return upload_raw(b, frame, src, bitpix, frame_height, row0, shifty, rescale_ushrt);
+}
+
+int sgpu_block_upload_fits_fd(sgpu_block *b, int frame, int fd, long data_offset, int bitpix,
+		int frame_height, int row0, int shifty, int rescale_ushrt) {
+	if (!b || fd < 0 || data_offset < 0) return SGPU_GENERIC_ERROR;
+	RawSource src; src.fd = fd; src.base = (off_t) data_offset;
+	return upload_raw(b, frame, src, bitpix, frame_height, row0, shifty, rescale_ushrt);
+}
+
+}	// extern "C"

@@ -1,0 +1,77 @@
+"""Host mirror of the block reader for FITS sequences: stack_read_block_data
+(median_and_mean.c:382-545) over uncompressed primary-HDU files.  The host only moves file bytes
+(pread -> pinned staging -> H2D inside libsgpu.so); big-endian decode, BZERO, the DATAMAX rescale,
+y shift and zero fill run on the device (csrc/fitsread.cu).  No CPU decode path exists here."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+from .enums import DATA_FLOAT, DATA_USHORT, ST_SEQUENCE_ERROR
+
+
+def fits_probe(path):
+    """sgpu_fits_probe: BITPIX / NAXISn / BZERO / BSCALE / DATAMAX and the data-unit offset."""
+    info = _lib.FitsInfo()
+    rv = _lib.lib().sgpu_fits_probe(os.fsencode(path), C.byref(info))
+    if rv:
+        raise _lib.SgpuError(rv, f"{path}: not a readable FITS image")
+    return info
+
+
+def read_block_data(ctx, paths, row0=0, height=None, shifty=None, source="fd"):
+    """data->pix[] of one row block: a CUDA tensor [frame][layer][height][width] holding rows
+    [row0, row0 + height) of every file in `paths` (frame f shifted by shifty[f], zeros outside).
+    source: "fd" (pread into the library's pinned staging), "mmap" (pageable mapping of the file) or
+    "pinned" (the data unit read into sgpu_host_alloc memory first)."""
+    import torch
+    L = _lib.lib()
+    infos = [fits_probe(p) for p in paths]
+    i0 = infos[0]
+    w, fh, c = i0.naxes[0], i0.naxes[1], i0.naxes[2]
+    for p, i in zip(paths, infos):
+        if (i.naxes[0], i.naxes[1], i.naxes[2], i.bitpix) != (w, fh, c, i0.bitpix):
+            raise _lib.SgpuError(ST_SEQUENCE_ERROR, f"{p}: geometry differs from the first image")
+        if not i.device_readable:
+            raise _lib.SgpuError(ST_SEQUENCE_ERROR, f"{p}: BITPIX {i.bitpix} BZERO {i.bzero} BSCALE {i.bscale} needs cfitsio")
+    height = fh - row0 if height is None else height
+    dt = DATA_FLOAT if i0.bitpix == -32 else DATA_USHORT
+    n = len(paths)
+    dev = torch.device("cuda", ctx.device)
+    out = torch.empty((n, c, height, w), dtype=torch.float32 if dt == DATA_FLOAT else torch.uint16, device=dev)
+    desc = _lib.BlockDesc(n, c, w, height, dt)
+    blk = C.c_void_p()
+    ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(out.data_ptr()), C.byref(blk)))
+    try:
+        for f, (p, i) in enumerate(zip(paths, infos)):
+            sy = int(shifty[f]) if shifty is not None else 0
+            resc = -1 if not i.has_datamax else int(i.datamax > 10.0)   # image_format_fits.c:995-1011
+            nbytes = w * fh * c * abs(i.bitpix) // 8
+            if source == "fd":
+                fd = os.open(p, os.O_RDONLY)
+                try:
+                    ctx.check(L.sgpu_block_upload_fits_fd(blk, f, fd, i.data_offset, i.bitpix, fh, row0, sy, resc))
+                finally:
+                    os.close(fd)
+            elif source == "mmap":
+                m = np.memmap(p, dtype=np.uint8, mode="r", offset=i.data_offset, shape=(nbytes,))
+                ctx.check(L.sgpu_block_upload_fits(blk, f, C.c_void_p(m.ctypes.data), i.bitpix, fh, row0, sy, resc))
+                ctx.synchronize()
+                del m
+            else:
+                hp = C.c_void_p()
+                ctx.check(L.sgpu_host_alloc(ctx.h, nbytes, C.byref(hp)))
+                try:
+                    buf = (C.c_ubyte * nbytes).from_address(hp.value)
+                    with open(p, "rb") as fh_:
+                        fh_.seek(i.data_offset)
+                        fh_.readinto(buf)
+                    ctx.check(L.sgpu_block_upload_fits(blk, f, hp, i.bitpix, fh, row0, sy, resc))
+                    ctx.synchronize()
+                finally:
+                    L.sgpu_host_free(ctx.h, hp)
+        ctx.synchronize()
+    finally:
+        L.sgpu_block_destroy(blk)
+    return out
