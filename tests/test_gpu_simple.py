@@ -57,6 +57,27 @@ def test_simple_stackers(any_oracle, dtype, op, shape, shifted):
             assert np.array_equal(got, exp), (op, out32, on_device, np.abs(got.astype(np.float64) - exp).max())
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+@pytest.mark.parametrize("op", ["sum", "max", "min"])
+@pytest.mark.parametrize("shape", [(9, 1, 37, 56), (20, 3, 24, 136), (70, 1, 16, 64), (5, 1, 3, 8)])
+@pytest.mark.parametrize("yshift", [False, True], ids=["aligned", "yshifted"])
+def test_simple_stackers_wide_loads(any_oracle, dtype, op, shape, yshift):
+    """no x shift and a width that is a multiple of 16 bytes: the 16-byte-per-thread kernel"""
+    rng = np.random.default_rng(sum(shape) + len(op) + 1)
+    N, C, H, W = shape
+    fr = frames_of(rng, N, C, H, W, dtype)
+    sy = rng.integers(-4, 5, N).astype(np.int32) if yshift else None
+    sx = np.zeros(N, np.int32) if yshift else None
+    if yshift:
+        sy[0] = H + 2
+    for out32 in ((True, False) if (op == "sum" and dtype == np.uint16) else (True,)):
+        exp = any_oracle.stack_simple(fr, op, sx, sy, out32)
+        for on_device in (True, False):
+            got = run(fr, op, sx, sy, out32, on_device)
+            assert got is not None and got.dtype == exp.dtype
+            assert np.array_equal(got, exp), (op, out32, on_device, np.abs(got.astype(np.float64) - exp).max())
+
+
 def test_sum_saturates_to_word(ref):
     """WORD sums above 65535 are rescaled by 65535 / max (sum.c:329-341)"""
     rng = np.random.default_rng(5)
