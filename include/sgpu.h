@@ -170,7 +170,11 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *args
 
 /* End-to-end host call: frames[f] points to a full host frame [nb_layers][height][width];
  * shifty may be NULL.  Uploads (H2D), stacks, applies output_norm, downloads (D2H) into the host
- * outputs and returns when they are complete.  irej may be NULL. */
+ * outputs and returns when they are complete.  irej may be NULL.  Large inputs go through in row
+ * blocks like the reference's block loop (median_and_mean.c:1552): block k + 1 is uploaded on a
+ * copy stream while block k is stacked and its rows are read back (pinned host frames overlap;
+ * pageable ones still work).  output_norm needs the whole image's range and runs as one block.
+ * sgpu_handover_count / sgpu_last_engine then describe the last row block. */
 int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *const *frames,
 		const int *shifty, const sgpu_stack_args *args,
 		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);

@@ -272,38 +272,84 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
 	if (!ctx || !desc || !frames || !out) return SGPU_GENERIC_ERROR;
 	int rv = check_args(ctx, *desc, a); if (rv) return rv;
-	sgpu_block *blk = nullptr;
-	rv = sgpu_block_create(ctx, desc, &blk); if (rv) return rv;
-	const size_t npx = (size_t) desc->nb_layers * desc->height * desc->width;
-	const size_t out_es = a->use_32bit_output ? 4 : 2;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const int H = desc->height, W = desc->width, C = desc->nb_layers;
+	const size_t npx = (size_t) C * H * W;
+	const size_t in_es = desc->dtype == SGPU_F32 ? 4 : 2, out_es = a->use_32bit_output ? 4 : 2;
 	const int nmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
+	// Row blocks, as the reference's own block loop (median_and_mean.c:1552): block k + 1 is on its
+	// way over PCIe (copy stream) while block k is stacked and its rows go back (context stream).
+	// output_norm rescales with the whole image's range: one block.
+	int nblk = 1;
+	if (!(a->use_32bit_output && a->output_norm)) {
+		const size_t in_bytes = npx * in_es * (size_t) desc->nb_frames;
+		if (in_bytes >= ((size_t) 256 << 20) && H >= 512) nblk = 8;
+		if (const char *e = getenv("SGPU_HOST_BLOCKS")) { const int n = atoi(e); if (n >= 1) nblk = n; }
+		if (nblk > H) nblk = H;
+	}
+	int rows = (H + nblk - 1) / nblk;
+	if (nblk > 1) rows = (rows + 3) & ~3;		// keeps h * W a multiple of 4 samples (TMA tile load)
+	nblk = (H + rows - 1) / rows;
+	std::vector<sgpu_block *> blks(nblk, nullptr);
+	std::vector<cudaEvent_t> up(nblk, nullptr);
 	char *d_buf = nullptr;
 	const size_t out_bytes = (npx * out_es + 255) & ~(size_t) 255, map_bytes = (npx * 2 + 255) & ~(size_t) 255;
+	cudaStream_t const compute = ctx->stream;
+	auto cleanup = [&](int code) {
+		ctx->stream = compute;
+		cudaStreamSynchronize(ctx->copy_stream); cudaStreamSynchronize(compute);
+		if (d_buf) cudaFree(d_buf);
+		for (sgpu_block *b : blks) if (b) sgpu_block_destroy(b);
+		for (cudaEvent_t ev : up) if (ev) cudaEventDestroy(ev);
+		return code;
+	};
+	for (int k = 0; k < nblk; k++) {
+		sgpu_block_desc dk = *desc;
+		dk.height = (k + 1) * rows <= H ? rows : H - k * rows;
+		rv = sgpu_block_create(ctx, &dk, &blks[k]); if (rv) return cleanup(rv);
+		if (cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	}
 	cudaError_t e = cudaMalloc(&d_buf, out_bytes + nmaps * map_bytes + 64);
-	if (e != cudaSuccess) { sgpu_block_destroy(blk); return sgpu_cuda_fail(ctx, e, "cudaMalloc(outputs)"); }
-	void *d_out = d_buf;
-	uint16_t *d_lo = nmaps >= 1 ? (uint16_t *) (d_buf + out_bytes) : nullptr;
-	uint16_t *d_hi = nmaps == 2 ? (uint16_t *) (d_buf + out_bytes + map_bytes) : nullptr;
+	if (e != cudaSuccess) return cleanup(sgpu_cuda_fail(ctx, e, "cudaMalloc(outputs)"));
 	uint64_t *d_irej = (uint64_t *) (d_buf + out_bytes + nmaps * map_bytes);
-	auto cleanup = [&](int code) { cudaStreamSynchronize(ctx->stream); cudaFree(d_buf); sgpu_block_destroy(blk); return code; };
-	if (cudaMemsetAsync(d_irej, 0, 48, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	for (int f = 0; f < desc->nb_frames; f++) {
-		rv = sgpu_block_upload_frame(blk, f, frames[f], desc->height, 0, shifty ? shifty[f] : 0);
+	if (cudaMemsetAsync(d_irej, 0, 48, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	// uploads run on the copy stream when there is something to overlap with
+	auto upload = [&](int k) -> int {
+		if (nblk > 1) ctx->stream = ctx->copy_stream;
+		int r = SGPU_OK;
+		for (int f = 0; f < desc->nb_frames && !r; f++)
+			r = sgpu_block_upload_frame(blks[k], f, frames[f], H, k * rows, shifty ? shifty[f] : 0);
+		if (!r && cudaEventRecord(up[k], ctx->stream) != cudaSuccess) r = SGPU_GENERIC_ERROR;
+		ctx->stream = compute;
+		return r;
+	};
+	rv = upload(0); if (rv) return cleanup(rv);
+	for (int k = 0; k < nblk; k++) {
+		if (k + 1 < nblk) { rv = upload(k + 1); if (rv) return cleanup(rv); }
+		if (cudaStreamWaitEvent(compute, up[k], 0) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+		// block k's outputs: [layer][h][W] at the offset of everything the blocks before it wrote
+		const int h = blks[k]->d.height, row0 = k * rows;
+		const size_t off = (size_t) C * row0 * W;
+		char *d_out = d_buf + off * out_es;
+		uint16_t *d_lo = nmaps >= 1 ? (uint16_t *) (d_buf + out_bytes) + off : nullptr;
+		uint16_t *d_hi = nmaps == 2 ? (uint16_t *) (d_buf + out_bytes + map_bytes) + off : nullptr;
+		rv = sgpu_stack_block(ctx, blks[k], a, d_out, d_lo, d_hi, d_irej);
 		if (rv) return cleanup(rv);
+		if (nblk == 1 && a->use_32bit_output && a->output_norm) {
+			float mm[2];
+			rv = sgpu_minmax_nonzero(ctx, (const float *) d_out, npx, 1, mm); if (rv) return cleanup(rv);
+			rv = sgpu_rescale_0_1(ctx, (float *) d_out, npx, mm[0], mm[1]); if (rv) return cleanup(rv);
+		}
+		for (int l = 0; l < C; l++) {
+			const size_t src = (size_t) l * h * W, dst = ((size_t) l * H + row0) * W, n = (size_t) h * W;
+			if (cudaMemcpyAsync((char *) out + dst * out_es, d_out + src * out_es, n * out_es, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+			if (d_lo && rej_low && cudaMemcpyAsync(rej_low + dst, d_lo + src, n * 2, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+			if (d_hi && rej_high && cudaMemcpyAsync(rej_high + dst, d_hi + src, n * 2, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+		}
 	}
-	rv = sgpu_stack_block(ctx, blk, a, d_out, d_lo, d_hi, d_irej);
-	if (rv) return cleanup(rv);
-	if (a->use_32bit_output && a->output_norm) {
-		float mm[2];
-		rv = sgpu_minmax_nonzero(ctx, (const float *) d_out, npx, 1, mm); if (rv) return cleanup(rv);
-		rv = sgpu_rescale_0_1(ctx, (float *) d_out, npx, mm[0], mm[1]); if (rv) return cleanup(rv);
-	}
-	if (cudaMemcpyAsync(out, d_out, npx * out_es, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	if (d_lo && rej_low && cudaMemcpyAsync(rej_low, d_lo, npx * 2, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	if (d_hi && rej_high && cudaMemcpyAsync(rej_high, d_hi, npx * 2, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 	uint64_t h_irej[6] = { 0 };
-	if (cudaMemcpyAsync(h_irej, d_irej, 48, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	e = cudaStreamSynchronize(ctx->stream);
+	if (cudaMemcpyAsync(h_irej, d_irej, 48, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+	e = cudaStreamSynchronize(compute);
 	if (e != cudaSuccess) return cleanup(sgpu_cuda_fail(ctx, e, "stack"));
 	if (irej) memcpy(irej, h_irej, 48);
 	return cleanup(SGPU_OK);

@@ -187,6 +187,22 @@ def test_host_path_and_ragged(orc):
         compare(run_gpu(fr, device_resident=False, **dict(kw)), orc.stack(fr, **kw), f"host {N}x{H}x{W}")
 
 
+@pytest.mark.parametrize("nblk", [1, 2, 3, 7])
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+def test_host_path_row_blocks(orc, monkeypatch, nblk, dtype):
+    """sgpu_stack_host cut into row blocks (upload of block k + 1 overlapping the stack of block k):
+    the same result for every block count, three layers, y shifts, both rejection maps"""
+    monkeypatch.setenv("SGPU_HOST_BLOCKS", str(nblk))
+    rng = np.random.default_rng(80 + nblk)
+    N, Cn, H, W = 14, 3, 23, 70
+    fr = synth(rng, N, Cn, H, W, dtype)
+    kw = dict(rejection=O.WINSORIZED, sig=(3, 3), create_rejmaps=True, shifty=rng.integers(-3, 4, N),
+              shiftx=rng.integers(-2, 3, N))
+    compare(run_gpu(fr, device_resident=False, **dict(kw)), orc.stack(fr, **kw), f"host blocks {nblk}")
+    kw = dict(is_mean=False)
+    compare(run_gpu(fr, device_resident=False, **dict(kw)), orc.stack(fr, **kw), f"host blocks {nblk} median")
+
+
 def test_all_zero_and_single_valid(orc):
     fr = np.zeros((10, 1, 4, 8), dtype=np.float32)
     fr[3, 0, 1, :] = 0.25
