@@ -179,6 +179,14 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 		const int *shifty, const sgpu_stack_args *args,
 		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
 
+/* sgpu_stack_host for a sequence of single-image FITS files on disk (what the `stack` command is given,
+ * command.c:11729 -> stack_mean_or_median): the files are probed (same NAXISn / BITPIX, device
+ * readable, else SGPU_SEQUENCE_ERROR as median_and_mean.c:1300-1310), and every row block is filled by
+ * the raw reader (pread -> pinned staging -> H2D -> device decode) while the block before it is stacked.
+ * out: host [NAXIS3][NAXIS2][NAXIS1] float or uint16_t, sized by the caller from sgpu_fits_probe. */
+int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
+
 /* norm_to_0_1_range (median_and_mean.c:557-582) split for row shards: min/max over non-zero
  * samples (skip_first: the reference's scan starts at index 1 — set it on the shard that holds
  * element 0), then the rescale with the globally reduced min/max. */

@@ -42,6 +42,14 @@ for kind, bitpix, dt in (("f32", -32, ">f4"), ("u16", 16, ">i2")):
         print(f"{kind} {source}: {N} frames {gb:.2f} GB in {dt_s * 1e3:.1f} ms = {gb / dt_s:.1f} GB/s "
               f"({N * H * W / dt_s / 1e9:.2f} G samples/s; 'pinned' includes the host read into pinned memory)")
         del blk
+    # files on disk -> stacked image in one call (sgpu_stack_fits): reader, stack and read-back pipelined by row blocks
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.SIGMA, sig=(3.0, 3.0), ctx=ctx)
+    assert fitsread.stack_fits(args, paths) == 0, getattr(args, "error", "")
+    t0 = time.perf_counter()
+    assert fitsread.stack_fits(args, paths) == 0
+    dt_s = time.perf_counter() - t0
+    print(f"{kind} stack_fits (sigma 3/3): {N} files -> result in {dt_s * 1e3:.1f} ms = {N * H * W / dt_s / 1e9:.2f} G px-frames/s, "
+          f"{N * H * W * abs(bitpix) / 8 / dt_s / 1e9:.1f} GB/s of file data")
     for p in paths:
         os.remove(p)
 ctx.close()

@@ -4,7 +4,11 @@
 #include <cmath>
 #include <new>
 #include <cstdlib>
+#include <functional>
 #include "common.cuh"
+
+int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::function<int(sgpu_block *, int, int)> &upload_one,
+		const sgpu_stack_args *a, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
 
 int sgpu_fail(sgpu_ctx *ctx, int code, const char *fmt, ...) {
 	char buf[512];
@@ -271,6 +275,19 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 		const int *shifty, const sgpu_stack_args *a,
 		void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
 	if (!ctx || !desc || !frames || !out) return SGPU_GENERIC_ERROR;
+	const int H = desc->height;
+	return sgpu_stack_host_impl(ctx, desc, [&](sgpu_block *b, int f, int row0) {
+		return sgpu_block_upload_frame(b, f, frames[f], H, row0, shifty ? shifty[f] : 0);
+	}, a, out, rej_low, rej_high, irej);
+}
+
+}	// extern "C"
+
+// the block loop behind sgpu_stack_host and sgpu_stack_fits: upload_one(block, frame, first image row)
+// fills one frame of one row block on ctx->stream
+int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::function<int(sgpu_block *, int, int)> &upload_one,
+		const sgpu_stack_args *a, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !desc || !out) return SGPU_GENERIC_ERROR;
 	int rv = check_args(ctx, *desc, a); if (rv) return rv;
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
 	const int H = desc->height, W = desc->width, C = desc->nb_layers;
@@ -317,8 +334,7 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 	auto upload = [&](int k) -> int {
 		if (nblk > 1) ctx->stream = ctx->copy_stream;
 		int r = SGPU_OK;
-		for (int f = 0; f < desc->nb_frames && !r; f++)
-			r = sgpu_block_upload_frame(blks[k], f, frames[f], H, k * rows, shifty ? shifty[f] : 0);
+		for (int f = 0; f < desc->nb_frames && !r; f++) r = upload_one(blks[k], f, k * rows);
 		if (!r && cudaEventRecord(up[k], ctx->stream) != cudaSuccess) r = SGPU_GENERIC_ERROR;
 		ctx->stream = compute;
 		return r;
@@ -354,6 +370,8 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 	if (irej) memcpy(irej, h_irej, 48);
 	return cleanup(SGPU_OK);
 }
+
+extern "C" {
 
 /* ---- host-side scalar helpers ---- */
 

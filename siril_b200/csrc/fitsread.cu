@@ -14,6 +14,7 @@
 #include <fcntl.h>
 #include <unistd.h>
 #include <thread>
+#include <functional>
 #include <sys/stat.h>
 #include "common.cuh"
 
@@ -208,6 +209,9 @@ static int upload_raw(sgpu_block *b, int frame, const RawSource &src, int bitpix
 	return SGPU_OK;
 }
 
+int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::function<int(sgpu_block *, int, int)> &upload_one,
+		const sgpu_stack_args *a, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);	// api.cu
+
 // ---- primary header ------------------------------------------------------------------------------
 static bool card_value(const char *card, const char *key, double *v) {
 	const size_t kl = strlen(key);
@@ -295,6 +299,33 @@ int sgpu_block_upload_fits_fd(sgpu_block *b, int frame, int fd, long data_offset
 	if (!b || fd < 0 || data_offset < 0) return SGPU_GENERIC_ERROR;
 	RawSource src; src.fd = fd; src.base = (off_t) data_offset;
 	return upload_raw(b, frame, src, bitpix, frame_height, row0, shifty, rescale_ushrt);
+}
+
+int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !paths || nb_frames < 1 || !out) return SGPU_GENERIC_ERROR;
+	std::vector<sgpu_fits_info> fi(nb_frames);
+	std::vector<int> fds(nb_frames, -1);
+	auto close_all = [&](int code) { for (int fd : fds) if (fd >= 0) close(fd); return code; };
+	for (int f = 0; f < nb_frames; f++) {
+		if (!paths[f] || sgpu_fits_probe(paths[f], &fi[f])) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d of the sequence as FITS", f));
+		if (!fi[f].device_readable) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d (BITPIX %d, BZERO %g, BSCALE %g) needs cfitsio", f, fi[f].bitpix, fi[f].bzero, fi[f].bscale));
+		// "stacking an image sequence with different image sizes is not possible" (median_and_mean.c:1300-1310)
+		if (fi[f].bitpix != fi[0].bitpix || fi[f].naxes[0] != fi[0].naxes[0] || fi[f].naxes[1] != fi[0].naxes[1] || fi[f].naxes[2] != fi[0].naxes[2])
+			return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d differs in size or sample type from the first image", f));
+		fds[f] = open(paths[f], O_RDONLY);
+		if (fds[f] < 0) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open image %d", f));
+	}
+	if (fi[0].naxes[2] > 3) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "more than three layers"));
+	const sgpu_block_desc desc = { nb_frames, (int) fi[0].naxes[2], (int) fi[0].naxes[0], (int) fi[0].naxes[1],
+			fi[0].bitpix == -32 ? SGPU_F32 : SGPU_U16 };
+	const int H = desc.height;
+	const int rv = sgpu_stack_host_impl(ctx, &desc, [&](sgpu_block *b, int f, int row0) {
+		RawSource src; src.fd = fds[f]; src.base = (off_t) fi[f].data_offset;
+		const int rescale = fi[f].has_datamax ? (fi[f].datamax > 10.0) : -1;
+		return upload_raw(b, f, src, fi[f].bitpix, H, row0, shifty ? shifty[f] : 0, rescale);
+	}, args, out, rej_low, rej_high, irej);
+	return close_all(rv);
 }
 
 }	// extern "C"

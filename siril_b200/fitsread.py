@@ -75,3 +75,42 @@ def read_block_data(ctx, paths, row0=0, height=None, shifty=None, source="fd"):
     finally:
         L.sgpu_block_destroy(blk)
     return out
+
+
+def stack_fits(args, paths, is_mean=True):
+    """stack_mean_or_median (median_and_mean.c:1261-1826) for a sequence of FITS files on disk:
+    sgpu_stack_fits.  `args` is a StackingArgs without frames; the result lands in args.result as
+    numpy arrays, like the host-frame path of stack_mean_or_median."""
+    from . import stacking
+    L = _lib.lib()
+    ctx = stacking._context(args)
+    i0 = fits_probe(paths[0])
+    w, h, c = i0.naxes[0], i0.naxes[1], i0.naxes[2]
+    n = len(paths)
+    keep = []
+    try:
+        ca = stacking._fill_cargs(args, n, c, is_mean, keep)
+    except _lib.SgpuError as e:
+        args.retval = e.code
+        return e.code
+    out32 = bool(args.use_32bit_output)
+    nmaps = (1 if args.merge_lowhigh_rejmaps else 2) if (is_mean and args.create_rejmaps) else 0
+    out = np.empty((c, h, w), dtype=np.float32 if out32 else np.uint16)
+    rl = np.zeros((c, h, w), dtype=np.uint16) if nmaps >= 1 else None
+    rh = np.zeros((c, h, w), dtype=np.uint16) if nmaps == 2 else None
+    irej = np.zeros(6, dtype=np.uint64)
+    sy = np.ascontiguousarray(args.shifty, dtype=np.int32) if args.shifty is not None else None
+    cp = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
+    rv = L.sgpu_stack_fits(ctx.h, n, cp, sy.ctypes.data_as(C.c_void_p) if sy is not None else None, C.byref(ca),
+                           out.ctypes.data_as(C.c_void_p),
+                           rl.ctypes.data_as(C.c_void_p) if rl is not None else None,
+                           rh.ctypes.data_as(C.c_void_p) if rh is not None else None,
+                           irej.ctypes.data_as(C.c_void_p))
+    args.retval = rv
+    if rv:
+        args.error = (L.sgpu_last_error(ctx.h) or b"").decode()
+        return rv
+    res = stacking.StackResult()
+    res.data, res.rejmap_low, res.rejmap_high, res.irej = out, rl, rh, irej.reshape(3, 2)
+    args.result = res
+    return rv

@@ -113,3 +113,45 @@ def test_stack_from_fits_equals_stack_from_arrays(tmp_path, orc):
     assert np.array_equal(args.result.irej, ref["irej"])
     rel = np.abs(out - ref["out"]) / np.maximum(np.abs(ref["out"]), 1e-30)
     assert rel.max() <= 1e-6
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+@pytest.mark.parametrize("nblk", [1, 3])
+def test_stack_fits_files(tmp_path, orc, monkeypatch, dtype, nblk):
+    """sgpu_stack_fits: files on disk -> stacked image, row blocks filled by the raw reader while the
+    block before is stacked; against the oracle on the decoded frames"""
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    monkeypatch.setenv("SGPU_HOST_BLOCKS", str(nblk))
+    rng = np.random.default_rng(21 + nblk)
+    N, C, H, W = 15, 3, 26, 90
+    fr = 0.1 + 0.01 * rng.standard_normal((N, C, H, W))
+    fr[rng.random(fr.shape) < 0.01] += 0.4
+    fr = fr.astype(np.float32) if dtype == np.float32 else np.round(fr * 65535).astype(np.uint16)
+    paths = []
+    for f in range(N):
+        p = str(tmp_path / f"q_{f:05d}.fit")
+        fits_ref.write_fits(p, fr[f], datamax=1.0 if dtype == np.float32 else None)
+        paths.append(p)
+    sy = rng.integers(-3, 4, N).astype(np.int32)
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.SIGMA,
+                           sig=(3.0, 3.0), create_rejmaps=True, shifty=sy)
+    assert fitsread.stack_fits(args, paths) == 0, getattr(args, "error", "")
+    ref = orc.stack(fr, rejection=sb.SIGMA, sig=(3.0, 3.0), create_rejmaps=True, shifty=sy)
+    assert np.array_equal(args.result.irej, ref["irej"])
+    assert np.array_equal(args.result.rejmap_low, ref["rej_low"]) and np.array_equal(args.result.rejmap_high, ref["rej_high"])
+    rel = np.abs(args.result.data - ref["out"]) / np.maximum(np.abs(ref["out"]), 1e-30)
+    assert rel.max() <= 1e-6
+
+
+def test_stack_fits_rejects_mixed_sequences(tmp_path):
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    a, b = str(tmp_path / "a.fit"), str(tmp_path / "b.fit")
+    fits_ref.write_fits(a, np.full((1, 8, 8), 0.5, np.float32), datamax=1.0)
+    fits_ref.write_fits(b, np.full((1, 8, 9), 0.5, np.float32), datamax=1.0)
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None)
+    assert fitsread.stack_fits(args, [a, b, a]) == sb.ST_SEQUENCE_ERROR
+    assert fitsread.stack_fits(args, [a, str(tmp_path / "missing.fit")]) == sb.ST_SEQUENCE_ERROR
