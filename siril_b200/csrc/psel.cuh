@@ -1,0 +1,336 @@
+// psel.cuh — per-pixel logic of the SELECTION engine (stack_psel.cu): mean-with-rejection and
+// median WITHOUT sorting the stack.
+//
+// The reference never needs the order of a pixel stack, only (i) the median of the kept samples
+// (quickmedian_float, sorting.c:240-273), (ii) their sums (siril_stats_float_sd,
+// statistics.h:82-107; the mean, median_and_mean.c:1071-1090) and (iii) which samples lie beyond
+// median -+ k * sigma (rejection_float.c:49-60) — a few samples at both ends of the stack.  So
+// the kernel (phase A, stack_psel.cuh) keeps the N samples of a pixel in the registers of a small
+// lane group and makes three streaming passes over them:
+//   sums     n, sum x, sum x^2 in double, min, max;
+//   count    how many samples lie below the (trimmed) mean and how many within 0.45 sd of it:
+//            the first locates the median, the second gives a scale no outlier can inflate;
+//   extract  every sample inside a narrow window around the predicted median ("centre", a few
+//            dozen ranks wide) or beyond a radius the clipping thresholds cannot fall inside
+//            ("tails") is appended to a small per-lane list; the rest is only counted.
+// Phase B (this file, one thread per pixel) sorts the three short lists by insertion into the
+// first rows of the pixel's shared-memory column — they stand for ranks [0, nl), [cl, cl+cc) and
+// [n-nh, n) of the stack — and then runs the very same sorted-stack rejection code as the sorted /
+// lane-sort engines (sorted.cuh) through an accessor that knows which ranks exist.  A lookup of a
+// rank that was not extracted sets a flag and the pixel is handed to the exact engine, exactly
+// as sorted.cuh's own FAST_FALLBACK; the window parameters are chosen (scripts/psel_plan_sim.py)
+// so that this happens for < 1e-5 of well-behaved pixels.
+//
+// Everything here is __host__ __device__: tests/helpers/psel_host.cu replays phase A on the CPU
+// and runs this code against the oracle.
+#pragma once
+#include "sorted.cuh"
+
+namespace sgpu {
+
+enum { PSEL_WEIRD = 1, PSEL_TRIVIAL = 2, PSEL_HANDOVER = 4 };
+
+#define PSEL_NAN __int_as_float_hd(0x7fffffff)
+SGPU_HD __forceinline__ float __int_as_float_hd(int i) {
+#ifdef __CUDA_ARCH__
+	return __int_as_float(i);
+#else
+	float f; memcpy(&f, &i, 4); return f;
+#endif
+}
+
+// per pixel, written by phase A, read by phase B
+struct PselHdr {
+	double S1, S2, K;	// sum (x - K), sum (x - K)^2 over the n kept samples (K = 0 unless the plain sums were ill-conditioned)
+	float mn, mx;		// their minimum and maximum (ranks 0 and n - 1)
+	float p1, w;		// centre window: |x - p1| < w
+	float blo, bhi;		// every kept sample outside the low list is >= blo, outside the high list <= bhi
+	int n;			// kept samples (non-null in mean mode, all N in median mode)
+	int cl;			// kept samples below the centre window: rank of the first centre entry
+	int nl, cc;		// list entries below / inside the centre window (the rest are above)
+	int tid0;		// CTA thread of the group's first lane (its lists follow at tid0 + t)
+	int flags;
+};
+
+#define PSEL_CAP 64	// longest centre / tail list phase B sorts by insertion (ties can make a class arbitrarily long)
+#define PSEL_CAPT 48
+#define PSEL_ROWS (PSEL_CAP + 2 * PSEL_CAPT)	// rows of the column the sorted lists can take
+
+// list slots per lane for groups of T lanes (a lane stops appending when fewer than 8 are left)
+SGPU_HD constexpr int psel_list_cap(int T) { return T == 1 ? 72 : (T == 2 ? 48 : (T == 4 ? 32 : (T == 8 ? 24 : 16))); }
+
+struct PselPlan {
+	float p1, w;		// centre window
+	float cT, rT;		// tails: |x - cT| > rT
+	float blo, bhi;
+};
+
+// inverse of the standard normal distribution function for 0.02425 <= p <= 0.97575 (central
+// rational approximation of P. Acklam, |relative error| < 1.2e-9 in exact arithmetic; only the
+// PLACEMENT of the windows depends on it, never a result)
+SGPU_HD inline float psel_ndtri(float p) {
+	const float q = p - 0.5f, r = q * q;
+	const float num = (((((-3.969683028665376e+01f * r + 2.209460984245205e+02f) * r - 2.759285104469687e+02f) * r
+			+ 1.383577518672690e+02f) * r - 3.066479806614716e+01f) * r + 2.506628277459239e+00f) * q;
+	const float den = ((((-5.447609879822406e+01f * r + 1.615858368580409e+02f) * r - 1.556989798598866e+02f) * r
+			+ 6.680131188771972e+01f) * r - 1.328068155288572e+01f) * r + 1.f;
+	return num / den;
+}
+
+// ---- planning (group level, after each pass) ----------------------------------------------------
+// after the sums: where the count pass looks.  Mean and sd of the samples less their minimum and
+// maximum (one huge outlier is the common way a plain sd gets inflated).  false: degenerate
+// (too few samples, no spread, or sums too ill-conditioned to tell) — take every sample as centre.
+SGPU_HD inline bool psel_plan_count(int n, double S1, double S2, double K, float mn, float mx, float *mean, float *hw) {
+	if (n < 12) return false;
+	const double a = (double) mn - K, b = (double) mx - K;
+	const double T1 = S1 - a - b, T2 = S2 - a * a - b * b;
+	const double nt = (double) (n - 2);
+	const double m = T1 / nt, var = (T2 - T1 * m) / (nt - 1.0);
+	if (!(var > 0.0) || !(var * 1e9 > T2 / nt)) return false;
+	*mean = (float) (K + m);
+	*hw = 0.45f * sqrtf((float) var);
+	return *hw > 0.f && *hw < FLT_MAX;
+}
+
+// after the count pass (c_neg samples below `mean`, c_in within hw of it): the windows.
+// 0: plan filled; 1: the count window swallowed nearly everything (scale still inflated) — count
+// again with the smaller *hw; 2: degenerate
+SGPU_HD inline int psel_plan_window(int n, float *meanp, float *hw, int c_neg, int c_in, bool tails, bool percentile,
+		float s0, float s1, int attempt, PselPlan *pl) {
+	const float fn = (float) n, mean = *meanp;
+	float f = (float) c_in / fn;
+	float q = ((float) c_neg + 0.5f) / fn;
+	q = q < 0.03f ? 0.03f : (q > 0.97f ? 0.97f : q);
+	if (f >= 0.80f && attempt < 2) {	// several outliers: the bulk is a fraction of the window, and the mean sits off its middle
+		*hw *= 0.25f;
+		*meanp = mean - *hw * psel_ndtri(q);
+		return 1;
+	}
+	f = f < 0.05f ? 0.05f : (f > 0.95f ? 0.95f : f);
+	const float srob = *hw / psel_ndtri(0.5f + 0.5f * f);	// scale of the bulk
+	const float p1 = mean - srob * psel_ndtri(q);		// where half of the samples are below
+	const float wr = fmaxf(6.f, 3.0f * sqrtf(sqrtf(fn)));	// half-width of the centre window in ranks
+	const float w = wr * srob * 2.5066283f / fn;
+	float rlo = FLT_MAX, rhi = FLT_MAX;
+	if (tails) {
+		if (percentile) {	// thresholds median * sig (rejection_float.c:31-44), the median within w of p1
+			rlo = fabsf(p1) * s0 - 2.f * w; rhi = fabsf(p1) * s1 - 2.f * w;
+		} else {		// thresholds sig * sigma; the bulk's sigma is known to ~1.7 / sqrt(n) relative (1 sd)
+			const float mf = 1.f / (1.f + 8.f / sqrtf(fn));
+			rlo = mf * s0 * srob; rhi = mf * s1 * srob;
+		}
+		rlo = rlo > w ? rlo : w; rhi = rhi > w ? rhi : w;
+	}
+	if (!(w > 0.f) || !(w < FLT_MAX) || !(fabsf(p1) < FLT_MAX)) return 2;
+	pl->p1 = p1; pl->w = w;
+	if (rlo >= FLT_MAX || rhi >= FLT_MAX) { pl->cT = p1; pl->rT = FLT_MAX; pl->blo = -FLT_MAX; pl->bhi = FLT_MAX; return 0; }
+	const float lo = p1 - rlo, hi = p1 + rhi;
+	pl->cT = 0.5f * (lo + hi); pl->rT = 0.5f * (hi - lo);
+	const float eps = (fabsf(pl->cT) + pl->rT) * 4e-7f + FLT_MIN;	// a sample the tail test keeps out of the lists
+	pl->blo = pl->cT - pl->rT - eps; pl->bhi = pl->cT + pl->rT + eps;	// satisfies |fl(x - cT)| <= rT
+	return 0;
+}
+
+// every sample is centre (small or degenerate stacks)
+SGPU_HD inline void psel_plan_all(PselPlan *pl) {
+	pl->p1 = 0.f; pl->w = FLT_MAX; pl->cT = 0.f; pl->rT = FLT_MAX; pl->blo = -FLT_MAX; pl->bhi = FLT_MAX;
+}
+
+// after the extraction: do the ranks a rejection can ask the median of lie inside the centre
+// window?  (the median of the kept set moves by half the difference of low and high rejections;
+// +-3 ranks are provided for, more ends in a hand-over)
+SGPU_HD inline bool psel_window_ok(int n, int cl, int cc) {
+	int lo = (n - 1) / 2 - 3, hi = n / 2 + 3;
+	lo = lo < 0 ? 0 : lo; hi = hi > n - 1 ? n - 1 : hi;
+	return cl <= lo && cl + cc - 1 >= hi;
+}
+
+// the window moved to where the counts say the median is, and widened
+SGPU_HD inline void psel_replan(int n, int cl, int cc, PselPlan *pl) {
+	const float fn = (float) n;
+	// ranks per unit of value near the window: what the window itself held, else the plan's guess
+	const float dens = cc > 4 ? (float) cc / (2.f * pl->w) : 3.f * sqrtf(sqrtf(fn)) / pl->w;
+	const float shift = ((float) (n - 1) * 0.5f - ((float) cl + 0.5f * (float) cc)) / dens;
+	const float p1 = pl->p1 + shift, w = pl->w * 1.5f + fabsf(shift) * 0.25f;
+	float lo = pl->cT - pl->rT, hi = pl->cT + pl->rT;
+	if (pl->rT < FLT_MAX) {		// keep the tails outside the centre window
+		if (lo > p1 - w) lo = p1 - w;
+		if (hi < p1 + w) hi = p1 + w;
+		pl->cT = 0.5f * (lo + hi); pl->rT = 0.5f * (hi - lo);
+		const float eps = (fabsf(pl->cT) + pl->rT) * 4e-7f + FLT_MIN;
+		pl->blo = pl->cT - pl->rT - eps; pl->bhi = pl->cT + pl->rT + eps;
+	}
+	pl->p1 = p1; pl->w = w;
+}
+
+// ---- phase A, group level ------------------------------------------------------------------------
+// The control flow of a lane group, shared by the kernel (stack_psel.cuh: samples in registers,
+// shuffles inside the passes) and the host replay (tests/helpers/psel_host.cu).  `P` provides
+//   any(b)                            true when b holds for any group that runs in lockstep with this one
+//   sums(is_mean, &n, &S1, &S2, &mn, &mx)   nulls become absent in mean mode
+//   shifted_sums(K, &S1, &S2)         sum (x - K), sum (x - K)^2 of the kept samples
+//   count(mean, hw, &c_neg, &c_in)    kept samples below mean / within hw of it
+//   extract(on, plan, &below, &over)  fills the lane lists (nothing when !on); kept samples below plan.p1; lists overflowed
+//   classify(plan, &cc, &ccb, &nl)    list entries inside the centre window / of those, below plan.p1 / entries below the window
+template <class P>
+SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool percentile, float s0, float s1, PselHdr &h) {
+	double S1, S2; float mn, mx; int n;
+	ps.sums(is_mean, &n, &S1, &S2, &mn, &mx);
+	h.n = n; h.S1 = S1; h.S2 = S2; h.K = 0.0; h.mn = mn; h.mx = mx; h.flags = 0; h.cl = 0; h.nl = 0; h.cc = 0;
+	PselPlan pl; psel_plan_all(&pl);
+	bool live = true;
+	if (!(S2 < (double) FLT_MAX * (double) FLT_MAX)) { h.flags = PSEL_WEIRD; live = false; }	// a NaN or an infinity among the samples
+	else if (n <= 1 || mn == mx) { h.flags = PSEL_TRIVIAL; live = false; }
+	// plain sums lose the variance to cancellation when the spread is tiny beside the level: re-sum about the mean
+	const double fn = (double) n;
+	const bool ill = live && !(((S2 - S1 * S1 / fn) / (fn - 1.0)) * 1e5 > S2 / fn);
+	if (ps.any(ill)) {
+		const double K = (double) (float) (S1 / fn);
+		double T1, T2;
+		ps.shifted_sums(K, &T1, &T2);
+		if (ill) { S1 = T1; S2 = T2; h.K = K; h.S1 = S1; h.S2 = S2; }
+	}
+	// where to count
+	float mean = 0.f, hw = 0.f;
+	bool want = live && psel_plan_count(n, S1, S2, h.K, mn, mx, &mean, &hw);
+	bool all_centre = live && !want;
+	for (int attempt = 0; attempt < 3; attempt++) {
+		if (!ps.any(want)) break;
+		int c_neg, c_in;
+		ps.count(mean, hw, &c_neg, &c_in);
+		if (want) {
+			const int r = psel_plan_window(n, &mean, &hw, c_neg, c_in, tails, percentile, s0, s1, attempt, &pl);
+			if (r == 0) want = false;
+			else if (r == 2) { want = false; all_centre = true; }
+		}
+	}
+	if (want) all_centre = true;
+	if (all_centre) {
+		psel_plan_all(&pl);
+		if (n > PSEL_CAP) { h.flags = PSEL_HANDOVER; live = false; }	// too many to sort by insertion
+	}
+	// extraction, repeated with a moved window when the centre missed the median's ranks
+	bool need = live;
+	for (int attempt = 0; attempt < 3; attempt++) {
+		if (!ps.any(need)) break;
+		int below; bool over;
+		ps.extract(need, pl, &below, &over);
+		int cc, ccb, nl;
+		ps.classify(pl, &cc, &ccb, &nl);
+		if (need) {
+			const int cl = below - ccb;
+			if (over) { h.flags = PSEL_HANDOVER; need = false; }
+			else if (pl.w >= FLT_MAX || psel_window_ok(n, cl, cc)) { h.cl = cl; h.nl = nl; h.cc = cc; need = false; }
+			else psel_replan(n, cl, cc, &pl);
+		}
+	}
+	if (need) h.flags = PSEL_HANDOVER;
+	h.p1 = pl.p1; h.w = pl.w; h.blo = pl.blo; h.bhi = pl.bhi;
+}
+
+// ---- phase B -------------------------------------------------------------------------------------
+
+// the pixel's column as a partially known sorted stack: the three sorted lists sit one after the
+// other in rows [0, nl), [nl, nl + cc), [nl + cc, nl + cc + nh) and stand for ranks [0, nl),
+// [cl, cl + cc), [n - nh, n)
+template <class Store>
+struct PartialAcc {
+	const Store &col;
+	int n, nl, cl, cc, nh;
+	float mn, mx, blo, bhi;
+	bool trivial;
+	mutable bool miss, bound;	// a rank that was not extracted was read / one of the two bounds was
+	SGPU_HD __forceinline__ float operator()(int i) const {
+		if (trivial) return mn;
+		if (i < nl) return col.get(i);
+		if (i >= cl && i < cl + cc) return col.get(nl + i - cl);
+		if (i >= n - nh && i < n) return col.get(nl + cc + i - (n - nh));
+		if (i == 0) return mn;
+		if (i == n - 1) return mx;
+		// the first rank past a tail list: its value is not known, but a bound on it is, and every
+		// predicate the rejections evaluate there is monotone (a kept bound means a kept sample)
+		if (i == nl && nl < cl) { bound = true; return blo; }
+		if (i == n - nh - 1 && i >= cl + cc) { bound = true; return bhi; }
+		miss = true;
+		return i < cl ? blo : bhi;
+	}
+	SGPU_HD __forceinline__ void set(int, float) const { miss = true; }	// no rejection here compacts in place
+};
+
+// ascending insertion of x into rows [base, base + have)
+template <class Store>
+SGPU_HD __forceinline__ void psel_insert(Store &col, int base, int have, float x) {
+	int i = base + have;
+	while (i > base) { const float y = col.get(i - 1); if (!(y > x)) break; col.set(i, y); i--; }
+	col.set(i, x);
+}
+
+// Lists: cnt(t) entries of lane t, entry(t, k).  Store: get(row) / set(row, v) on the pixel's column,
+// which must hold PSEL_ROWS rows (or as many as the stack has samples).
+template <bool U16, class Store, class Lists, typename OrigFn>
+SGPU_HD double psel_pixel(Store &col, const Lists &ls, int T, const PselHdr &h, int N, int is_mean, const RejCfg &c,
+		const double *wts, OrigFn orig, int rej[2], int *status) {
+	*status = FAST_FALLBACK;
+	if (h.flags & (PSEL_WEIRD | PSEL_HANDOVER)) return 0.0;
+	const int n = h.n;
+	int nl = 0, nh = 0, cc = 0;
+	if (!(h.flags & PSEL_TRIVIAL)) {
+		const int bc = h.nl, bh = h.nl + h.cc;	// first row of the centre / of the highs
+		if (h.nl > PSEL_CAPT || h.cc > PSEL_CAP) return 0.0;
+		for (int t = 0; t < T; t++) {
+			const int m = ls.cnt(t);
+			for (int k = 0; k < m; k++) {
+				const float x = ls.entry(t, k);
+				const float d = x - h.p1;
+				if (fabsf(d) < h.w) psel_insert(col, bc, cc++, x);
+				else if (d < 0.f) psel_insert(col, 0, nl++, x);
+				else { if (nh >= PSEL_CAPT) return 0.0; psel_insert(col, bh, nh++, x); }
+			}
+		}
+		if (nl != h.nl || cc != h.cc || h.cl < nl || h.cl + cc > n - nh) return 0.0;	// cannot happen: the lists are what phase A counted
+	}
+	const PartialAcc<Store> acc{ col, n, nl, h.cl, cc, nh, h.mn, h.mx, h.blo, h.bhi, (h.flags & PSEL_TRIVIAL) != 0, false, false };
+	double result;
+	int st = FAST_DONE;
+	if (is_mean) {
+		Sums S0; S0.K = h.K; S0.S1 = h.S1; S0.S2 = h.S2;
+		PartialAcc<Store> a2 = acc;
+		FastRes o;
+		result = 0.0;
+		if (n > 0) {
+			fast_reject<U16>(a2, n, N, c, &S0, rej, o);
+			st = o.status;
+			// a bound stands in for the first sample past a tail list: fine as long as it was KEPT
+			// (every rejected rank must be a real sample)
+			if (a2.miss || rej[0] > nl || rej[1] > nh) st = FAST_FALLBACK;
+			if (st == FAST_DONE) {
+				if (wts && a2.bound) {
+					// the weighted combine re-selects by value between the extremes of the kept set
+					// (median_and_mean.c:1045-1070); where a bound stood in for one of them, find it
+					const int a = rej[0], b = n - rej[1];
+					const bool lo_b = !(a < nl || a == 0), hi_b = !(b - 1 >= n - nh || b == n);
+					const float L = lo_b ? col.get(a - 1) : 0.f, Hh = hi_b ? col.get(nl + cc + b - (n - nh)) : 0.f;	// the innermost rejected samples
+					float pmin = FLT_MAX, pmax = -FLT_MAX;
+					for (int f = 0; f < N; f++) {
+						const float v = orig(f);
+						if (v == 0.f) continue;
+						if (lo_b && v > L && v < pmin) pmin = v;
+						if (hi_b && v < Hh && v > pmax) pmax = v;
+					}
+					if (lo_b) o.pmin = pmin;
+					if (hi_b) o.pmax = pmax;
+				}
+				result = fast_combine(o, N, wts, orig);
+			}
+		}
+	} else {
+		result = median_sorted<U16>(acc, 0, n);	// all N samples, zeros included (median_and_mean.c:1711-1715)
+		if (acc.miss) st = FAST_FALLBACK;
+	}
+	if (st != FAST_DONE) { rej[0] = rej[1] = 0; return 0.0; }
+	*status = FAST_DONE;
+	return result;
+}
+
+}  // namespace sgpu

@@ -417,11 +417,11 @@ SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, const Sums
 // ---- combine: mean_and_reject (median_and_mean.c:956-1101) on the sorted stack ------------------
 // `s` holds the n non-zero samples ascending; nb is the full stack size; orig(f) re-reads the
 // normalized sample of frame f (the reference's o_stack).  status FAST_FALLBACK: result unset.
-template <bool U16, class Acc, typename OrigFn>
-SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const double *w, OrigFn orig,
-		const Sums *S0, int rej[2], int *status) {
-	FastRes o; o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
-	if (n == 0) { *status = FAST_DONE; return 0.0; }	// all samples null: median of zeros
+// the rejection alone: which rank range is kept, its sum and its extremes
+template <bool U16, class Acc>
+SGPU_HD void fast_reject(Acc &s, int n, int nb, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
+	o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
+	if (n == 0) return;	// all samples null: median of zeros
 	if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(s, n, S0, o);
 	else switch (c.type) {
 	case SGPU_PERCENTILE: fast_percentile<U16>(s, n, c, S0, rej, o); break;
@@ -431,8 +431,12 @@ SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, cons
 	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, S0, rej, o); break;
 	default: o.status = FAST_FALLBACK; break;	// MAD, SIGMEDIAN: exact engine
 	}
-	*status = o.status;
-	if (o.status != FAST_DONE || o.kept == 0) { *status = FAST_FALLBACK; return 0.0; }
+	if (o.status != FAST_DONE || o.kept == 0) o.status = FAST_FALLBACK;
+}
+
+// the combine of a decided stack (o.status == FAST_DONE, n > 0)
+template <typename OrigFn>
+SGPU_HD double fast_combine(const FastRes &o, int nb, const double *w, OrigFn orig) {
 	if (w) {
 		double sum = 0.0, norm = 0.0;
 		for (int f = 0; f < nb; f++) {
@@ -447,6 +451,18 @@ SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, cons
 		return sum / norm;
 	}
 	return o.sum / (double) o.kept;
+}
+
+template <bool U16, class Acc, typename OrigFn>
+SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const double *w, OrigFn orig,
+		const Sums *S0, int rej[2], int *status) {
+	*status = FAST_DONE;
+	if (n == 0) return 0.0;
+	FastRes o;
+	fast_reject<U16>(s, n, nb, c, S0, rej, o);
+	*status = o.status;
+	if (o.status != FAST_DONE) return 0.0;
+	return fast_combine(o, nb, w, orig);
 }
 
 }  // namespace sgpu
