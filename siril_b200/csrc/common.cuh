@@ -61,6 +61,9 @@ struct StackDevParams {
 bool sgpu_reg_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_reg(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
+bool sgpu_psel_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
+int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 bool sgpu_lsort_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);

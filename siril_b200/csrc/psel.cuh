@@ -47,17 +47,17 @@ struct PselHdr {
 	float blo, bhi;		// every kept sample outside the low list is >= blo, outside the high list <= bhi
 	int n;			// kept samples (non-null in mean mode, all N in median mode)
 	int cl;			// kept samples below the centre window: rank of the first centre entry
-	int nl, cc;		// list entries below / inside the centre window (the rest are above)
+	int nl, cc, m;		// list entries below / inside the centre window, and all of them (the rest are above)
 	int tid0;		// CTA thread of the group's first lane (its lists follow at tid0 + t)
 	int flags;
 };
 
 #define PSEL_CAP 64	// longest centre / tail list phase B sorts by insertion (ties can make a class arbitrarily long)
 #define PSEL_CAPT 48
-#define PSEL_ROWS (PSEL_CAP + 2 * PSEL_CAPT)	// rows of the column the sorted lists can take
+#define PSEL_ROWS (PSEL_CAP + 2 * PSEL_CAPT + 8)	// rows of the column the sorted lists (and two stand-ins) can take
 
 // list slots per lane for groups of T lanes (a lane stops appending when fewer than 8 are left)
-SGPU_HD constexpr int psel_list_cap(int T) { return T == 1 ? 72 : (T == 2 ? 48 : (T == 4 ? 32 : (T == 8 ? 24 : 16))); }
+SGPU_HD constexpr int psel_list_cap(int T) { return T == 1 ? 56 : (T == 2 ? 40 : (T == 4 ? 32 : (T == 8 ? 24 : 16))); }
 
 struct PselPlan {
 	float p1, w;		// centre window
@@ -85,11 +85,11 @@ SGPU_HD inline bool psel_plan_count(int n, double S1, double S2, double K, float
 	if (n < 12) return false;
 	const double a = (double) mn - K, b = (double) mx - K;
 	const double T1 = S1 - a - b, T2 = S2 - a * a - b * b;
-	const double nt = (double) (n - 2);
-	const double m = T1 / nt, var = (T2 - T1 * m) / (nt - 1.0);
-	if (!(var > 0.0) || !(var * 1e9 > T2 / nt)) return false;
+	const double rnt = rcp_d(n - 2);
+	const double m = T1 * rnt, ss = T2 - T1 * m;		// sum of squares about the trimmed mean
+	if (!(ss > 0.0) || !(ss * 1e9 > T2)) return false;
 	*mean = (float) (K + m);
-	*hw = 0.45f * sqrtf((float) var);
+	*hw = 0.45f * sqrtf((float) ss / (float) (n - 3));
 	return *hw > 0.f && *hw < FLT_MAX;
 }
 
@@ -172,21 +172,21 @@ SGPU_HD inline void psel_replan(int n, int cl, int cc, PselPlan *pl) {
 //   shifted_sums(K, &S1, &S2)         sum (x - K), sum (x - K)^2 of the kept samples
 //   count(mean, hw, &c_neg, &c_in)    kept samples below mean / within hw of it
 //   extract(on, plan, &below, &over)  fills the lane lists (nothing when !on); kept samples below plan.p1; lists overflowed
-//   classify(plan, &cc, &ccb, &nl)    list entries inside the centre window / of those, below plan.p1 / entries below the window
+//   classify(plan, &cc, &ccb, &nl, &m)  list entries inside the centre window / of those, below plan.p1 / entries below the window / all
 template <class P>
 SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool percentile, float s0, float s1, PselHdr &h) {
 	double S1, S2; float mn, mx; int n;
 	ps.sums(is_mean, &n, &S1, &S2, &mn, &mx);
-	h.n = n; h.S1 = S1; h.S2 = S2; h.K = 0.0; h.mn = mn; h.mx = mx; h.flags = 0; h.cl = 0; h.nl = 0; h.cc = 0;
+	h.n = n; h.S1 = S1; h.S2 = S2; h.K = 0.0; h.mn = mn; h.mx = mx; h.flags = 0; h.cl = 0; h.nl = 0; h.cc = 0; h.m = 0;
 	PselPlan pl; psel_plan_all(&pl);
 	bool live = true;
 	if (!(S2 < (double) FLT_MAX * (double) FLT_MAX)) { h.flags = PSEL_WEIRD; live = false; }	// a NaN or an infinity among the samples
 	else if (n <= 1 || mn == mx) { h.flags = PSEL_TRIVIAL; live = false; }
 	// plain sums lose the variance to cancellation when the spread is tiny beside the level: re-sum about the mean
-	const double fn = (double) n;
-	const bool ill = live && !(((S2 - S1 * S1 / fn) / (fn - 1.0)) * 1e5 > S2 / fn);
+	const double rn = rcp_d(n > 0 ? n : 1);
+	const bool ill = live && !((S2 - S1 * S1 * rn) * 1e5 > S2);	// variance * (n - 1) against mean square * n
 	if (ps.any(ill)) {
-		const double K = (double) (float) (S1 / fn);
+		const double K = (double) (float) (S1 * rn);
 		double T1, T2;
 		ps.shifted_sums(K, &T1, &T2);
 		if (ill) { S1 = T1; S2 = T2; h.K = K; h.S1 = S1; h.S2 = S2; }
@@ -195,6 +195,7 @@ SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool per
 	float mean = 0.f, hw = 0.f;
 	bool want = live && psel_plan_count(n, S1, S2, h.K, mn, mx, &mean, &hw);
 	bool all_centre = live && !want;
+#pragma unroll 1
 	for (int attempt = 0; attempt < 3; attempt++) {
 		if (!ps.any(want)) break;
 		int c_neg, c_in;
@@ -212,16 +213,17 @@ SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool per
 	}
 	// extraction, repeated with a moved window when the centre missed the median's ranks
 	bool need = live;
+#pragma unroll 1
 	for (int attempt = 0; attempt < 3; attempt++) {
 		if (!ps.any(need)) break;
 		int below; bool over;
 		ps.extract(need, pl, &below, &over);
-		int cc, ccb, nl;
-		ps.classify(pl, &cc, &ccb, &nl);
+		int cc, ccb, nl, m;
+		ps.classify(pl, &cc, &ccb, &nl, &m);
 		if (need) {
 			const int cl = below - ccb;
-			if (over) { h.flags = PSEL_HANDOVER; need = false; }
-			else if (pl.w >= FLT_MAX || psel_window_ok(n, cl, cc)) { h.cl = cl; h.nl = nl; h.cc = cc; need = false; }
+			if (over || m > PSEL_ROWS - 2) { h.flags = PSEL_HANDOVER; need = false; }
+			else if (pl.w >= FLT_MAX || psel_window_ok(n, cl, cc)) { h.cl = cl; h.nl = nl; h.cc = cc; h.m = m; need = false; }
 			else psel_replan(n, cl, cc, &pl);
 		}
 	}
@@ -230,87 +232,106 @@ SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool per
 }
 
 // ---- phase B -------------------------------------------------------------------------------------
-
-// the pixel's column as a partially known sorted stack: the three sorted lists sit one after the
-// other in rows [0, nl), [nl, nl + cc), [nl + cc, nl + cc + nh) and stand for ranks [0, nl),
-// [cl, cl + cc), [n - nh, n)
-template <class Store>
-struct PartialAcc {
-	const Store &col;
-	int n, nl, cl, cc, nh;
-	float mn, mx, blo, bhi;
-	bool trivial;
-	mutable bool miss, bound;	// a rank that was not extracted was read / one of the two bounds was
-	SGPU_HD __forceinline__ float operator()(int i) const {
-		if (trivial) return mn;
-		if (i < nl) return col.get(i);
-		if (i >= cl && i < cl + cc) return col.get(nl + i - cl);
-		if (i >= n - nh && i < n) return col.get(nl + cc + i - (n - nh));
-		if (i == 0) return mn;
-		if (i == n - 1) return mx;
-		// the first rank past a tail list: its value is not known, but a bound on it is, and every
-		// predicate the rejections evaluate there is monotone (a kept bound means a kept sample)
-		if (i == nl && nl < cl) { bound = true; return blo; }
-		if (i == n - nh - 1 && i >= cl + cc) { bound = true; return bhi; }
-		miss = true;
-		return i < cl ? blo : bhi;
-	}
-	SGPU_HD __forceinline__ void set(int, float) const { miss = true; }	// no rejection here compacts in place
-};
+// B1 (still the lane group): the m extracted samples of a pixel are sorted into the first m rows of
+// its column by value buckets, one per lane — T equal slices of the centre window, the first and the
+// last open-ended — each lane inserting the samples of its bucket behind those of the buckets below.
+// Whatever the rounding, psel_bucket is monotone in x, so the rows end up globally ascending:
+// [lows | centre | highs] = ranks [0, nl), [cl, cl + cc), [n - nh, n) of the stack.
+SGPU_HD __forceinline__ int psel_bucket(float x, float p1, float w, int T) {
+	if (T == 1) return 0;
+	float s = (x - p1 + w) * ((float) T / (2.f * w));
+	s = s > 0.f ? s : 0.f;
+	s = s < (float) (T - 1) ? s : (float) (T - 1);
+	return (int) s;
+}
 
 // ascending insertion of x into rows [base, base + have)
 template <class Store>
-SGPU_HD __forceinline__ void psel_insert(Store &col, int base, int have, float x) {
+SGPU_HD __forceinline__ void psel_insert(const Store &col, int base, int have, float x) {
 	int i = base + have;
 	while (i > base) { const float y = col.get(i - 1); if (!(y > x)) break; col.set(i, y); i--; }
 	col.set(i, x);
 }
 
-// Lists: cnt(t) entries of lane t, entry(t, k).  Store: get(row) / set(row, v) on the pixel's column,
-// which must hold PSEL_ROWS rows (or as many as the stack has samples).
-template <bool U16, class Store, class Lists, typename OrigFn>
-SGPU_HD double psel_pixel(Store &col, const Lists &ls, int T, const PselHdr &h, int N, int is_mean, const RejCfg &c,
+// lane t's share of B1; `base`: entries in the buckets below t.  Lists: cnt(u) entries of lane u, entry(u, k).
+template <class Store, class Lists>
+SGPU_HD __forceinline__ void psel_sort_bucket(const Store &col, const Lists &ls, int T, int t, int base, float p1, float w) {
+	int have = 0;
+	for (int u = 0; u < T; u++) {
+		const int m = ls.cnt(u);
+		for (int k = 0; k < m; k++) {
+			const float x = ls.entry(u, k);
+			if (psel_bucket(x, p1, w, T) == t) psel_insert(col, base, have++, x);
+		}
+	}
+}
+
+// B2 (one thread per pixel): the column as a partially known sorted stack.  Rows [0, nl) are ranks
+// [0, nl), rows [nl, nl + cc) ranks [cl, cl + cc), rows [nl + cc, m) ranks [n - nh, n); rows m and
+// m + 1 hold stand-ins for ranks nl and n - nh - 1: the minimum / maximum of the stack when that tail
+// list is empty (exact), else a bound on the first sample past the list.  Every predicate the
+// rejections evaluate is monotone, so a KEPT bound means a kept sample, and psel_pixel refuses any
+// result that rejected one.
+template <class Store>
+struct PartialAcc {
+	const Store &col;
+	int n, nl, cl, cc, nh;
+	float mn;
+	bool trivial;
+	mutable bool miss;	// a rank that was not extracted was read
+	SGPU_HD __forceinline__ float operator()(int i) const {
+		if (trivial) return mn;
+		int row;
+		if ((unsigned) (i - cl) < (unsigned) cc) row = nl + i - cl;
+		else if (i < nl) row = i;
+		else if (i >= n - nh && i < n) row = nl + cc + i - (n - nh);
+		else if (i == nl) row = nl + cc + nh;
+		else if (i == n - nh - 1) row = nl + cc + nh + 1;
+		else { miss = true; row = nl + cc + nh + (i < cl ? 0 : 1); }
+		return col.get(row);
+	}
+	SGPU_HD __forceinline__ void set(int, float) const { miss = true; }	// no rejection here compacts in place
+};
+
+// Store: get(row) / set(row, v) on the pixel's column: m + 2 rows, the first m sorted by B1
+template <bool U16, class Store, typename OrigFn>
+SGPU_HD double psel_pixel(const Store &col, const PselHdr &h, int N, int is_mean, const RejCfg &c,
 		const double *wts, OrigFn orig, int rej[2], int *status) {
 	*status = FAST_FALLBACK;
 	if (h.flags & (PSEL_WEIRD | PSEL_HANDOVER)) return 0.0;
 	const int n = h.n;
 	int nl = 0, nh = 0, cc = 0;
 	if (!(h.flags & PSEL_TRIVIAL)) {
-		const int bc = h.nl, bh = h.nl + h.cc;	// first row of the centre / of the highs
-		if (h.nl > PSEL_CAPT || h.cc > PSEL_CAP) return 0.0;
-		for (int t = 0; t < T; t++) {
-			const int m = ls.cnt(t);
-			for (int k = 0; k < m; k++) {
-				const float x = ls.entry(t, k);
-				const float d = x - h.p1;
-				if (fabsf(d) < h.w) psel_insert(col, bc, cc++, x);
-				else if (d < 0.f) psel_insert(col, 0, nl++, x);
-				else { if (nh >= PSEL_CAPT) return 0.0; psel_insert(col, bh, nh++, x); }
-			}
-		}
-		if (nl != h.nl || cc != h.cc || h.cl < nl || h.cl + cc > n - nh) return 0.0;	// cannot happen: the lists are what phase A counted
+		nl = h.nl; cc = h.cc; nh = h.m - nl - cc;
+		if (nl > PSEL_CAPT || cc > PSEL_CAP || nh > PSEL_CAPT || nh < 0 || h.cl < nl || h.cl + cc > n - nh) return 0.0;
+		col.set(h.m, nl ? h.blo : h.mn);
+		col.set(h.m + 1, nh ? h.bhi : h.mx);
 	}
-	const PartialAcc<Store> acc{ col, n, nl, h.cl, cc, nh, h.mn, h.mx, h.blo, h.bhi, (h.flags & PSEL_TRIVIAL) != 0, false, false };
+	const PartialAcc<Store> acc{ col, n, nl, h.cl, cc, nh, h.mn, (h.flags & PSEL_TRIVIAL) != 0, false };
 	double result;
 	int st = FAST_DONE;
 	if (is_mean) {
 		Sums S0; S0.K = h.K; S0.S1 = h.S1; S0.S2 = h.S2;
-		PartialAcc<Store> a2 = acc;
 		FastRes o;
 		result = 0.0;
 		if (n > 0) {
-			fast_reject<U16>(a2, n, N, c, &S0, rej, o);
+			// only what this engine serves is instantiated (the others stay with the lane-sort engine)
+			o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
+			if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(acc, n, &S0, o);
+			else if (c.type == SGPU_PERCENTILE) fast_percentile<U16>(acc, n, c, &S0, rej, o);
+			else if (c.type == SGPU_SIGMA) fast_sigma<U16>(acc, n, c, &S0, rej, o);
+			else o.status = FAST_FALLBACK;
+			if (o.status != FAST_DONE || o.kept == 0) o.status = FAST_FALLBACK;
 			st = o.status;
-			// a bound stands in for the first sample past a tail list: fine as long as it was KEPT
-			// (every rejected rank must be a real sample)
-			if (a2.miss || rej[0] > nl || rej[1] > nh) st = FAST_FALLBACK;
+			// a stand-in is fine as long as it was KEPT (every rejected rank must be a real sample)
+			if (acc.miss || rej[0] > nl || rej[1] > nh) st = FAST_FALLBACK;
 			if (st == FAST_DONE) {
-				if (wts && a2.bound) {
+				const int a = rej[0], b = n - rej[1];		// the kept ranks [a, b)
+				const bool lo_b = a > 0 && a == nl, hi_b = b < n && b == n - nh;	// a whole tail list went: its stand-in became an extreme
+				if (wts && (lo_b || hi_b) && !acc.trivial) {
 					// the weighted combine re-selects by value between the extremes of the kept set
 					// (median_and_mean.c:1045-1070); where a bound stood in for one of them, find it
-					const int a = rej[0], b = n - rej[1];
-					const bool lo_b = !(a < nl || a == 0), hi_b = !(b - 1 >= n - nh || b == n);
-					const float L = lo_b ? col.get(a - 1) : 0.f, Hh = hi_b ? col.get(nl + cc + b - (n - nh)) : 0.f;	// the innermost rejected samples
+					const float L = lo_b ? col.get(a - 1) : 0.f, Hh = hi_b ? col.get(nl + cc) : 0.f;	// the innermost rejected samples
 					float pmin = FLT_MAX, pmax = -FLT_MAX;
 					for (int f = 0; f < N; f++) {
 						const float v = orig(f);

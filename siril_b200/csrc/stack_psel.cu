@@ -1,0 +1,73 @@
+// stack_psel.cu — launcher of the selection engine (kernel: stack_psel.cuh): picks the variant
+// (lanes per pixel, register slots) for the stack depth, sizes shared memory (the sample lists lie
+// over the dead upper rows of the tile when the stack is deep enough), clears the hand-over list,
+// launches, then lets the exact engine redo the list.
+#include <cstdlib>
+#include "stack_psel.cuh"
+
+using namespace sgpu;
+
+int sgpu_make_tile_tmap(sgpu_ctx *ctx, CUtensorMap *tm, void *base, size_t npix, int layers, int frames, int box_px, int box_rows);
+
+// 2^lt lanes per pixel, r register slots per lane; serves rf * 2^lt < N <= r * 2^lt; sub sub-tiles of 32 px per CTA
+struct PselVariant { int lt, r, rf, sub; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
+#define PV(LT, R, RF, SUB) { LT, R, RF, SUB, sgpu_launch_psel_variant<LT, R, RF, SUB> }
+static const PselVariant VARIANTS[] = {
+	PV(0, 50, 40, 4), PV(0, 64, 50, 4), PV(0, 80, 64, 4),			// N <= 80
+	PV(1, 50, 40, 2), PV(1, 64, 50, 2), PV(1, 80, 64, 2),			// 160
+	PV(2, 50, 40, 1), PV(2, 64, 50, 1), PV(2, 75, 64, 1), PV(2, 80, 75, 1),	// 320
+	PV(3, 50, 40, 1), PV(3, 64, 50, 1), PV(3, 75, 64, 1),			// 600
+	PV(4, 50, 37, 1), PV(4, 64, 50, 1), PV(4, 72, 64, 1),			// 1152
+};
+
+static const PselVariant *pick(int N) {
+	for (const PselVariant &v : VARIANTS) if ((v.r << v.lt) >= N && (v.rf << v.lt) < N) return &v;
+	return nullptr;
+}
+
+bool sgpu_psel_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
+	if ((size_t) d.height * d.width >= (1u << 30) || !pick(d.nb_frames)) return false;
+	if (!a->is_mean) return true;
+	switch (a->type_of_rejection) {
+	case SGPU_NO_REJEC: case SGPU_PERCENTILE: case SGPU_SIGMA: return true;
+	default: return false;
+	}
+}
+
+int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
+		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej) {
+	const sgpu_block_desc &d = blk->d;
+	const size_t npix = (size_t) d.height * d.width;
+	if (npix == 0) return SGPU_OK;
+	const PselVariant *var = pick(d.nb_frames);
+	if (!var) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "no selection-engine variant for %d frames", d.nb_frames);
+	StackParams p;
+	sgpu_fill_stack_params(p, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
+	const size_t list_bytes = ((npix * d.nb_layers + 1) * sizeof(unsigned) + 255) & ~(size_t) 255;
+	int rv = sgpu_ensure_list(ctx, list_bytes); if (rv) return rv;
+	p.list_count = (unsigned *) ctx->d_list; p.list = p.list_count + 1;
+	SGPU_CUDA(ctx, cudaMemsetAsync(p.list_count, 0, sizeof(unsigned), ctx->stream));
+	ctx->list_used = true;
+	p.is_u16 = d.dtype == SGPU_U16;
+	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes
+	CUtensorMap tmap;
+	p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; p.use_tma = 0;
+	const char *no_tma = getenv("SGPU_NO_TMA");
+	if (d.dtype == SGPU_F32 && !a->shiftx && npix % 4 == 0 && ((uintptr_t) blk->dev & 15) == 0 && !(no_tma && no_tma[0] == '1')) {
+		const int nbox = (d.nb_frames + 255) / 256;
+		p.box_rows = (d.nb_frames + nbox - 1) / nbox;
+		p.tile_rows = p.box_rows * nbox;
+		if (sgpu_make_tile_tmap(ctx, &tmap, blk->dev, npix, d.nb_layers, d.nb_frames, TILE_PX, p.box_rows) == SGPU_OK) p.use_tma = 1;
+		else { p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; }
+	}
+	const int T = 1 << var->lt, nt = var->sub * T * 32, pxc = var->sub * TILE_PX;
+	const int rows8 = (p.tile_rows + 9) & ~7, lcap = psel_list_cap(T);
+	const bool overlay = rows8 > PSEL_ROWS && (size_t) (rows8 - PSEL_ROWS) * TILE_PX * var->sub >= (size_t) lcap * nt;
+	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * rows8 * sizeof(float) + (size_t) pxc * sizeof(PselHdr) + 16
+		+ ((p.use_tma && a->normalize != SGPU_NO_NORM) ? (size_t) d.nb_frames * 16 : 0) + (overlay ? 0 : (size_t) lcap * nt * sizeof(float));
+	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the selection engine");
+	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
+	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);
+	if (rv) return rv;
+	return sgpu_launch_exact_list(ctx, blk, p);
+}

@@ -20,7 +20,8 @@ struct HostPasses {
 	std::vector<std::vector<float>> v;	// v[t][j]: sample j * T + t (NaN: absent)
 	std::vector<std::vector<float>> lists;
 	int passes = 0;
-	bool any(bool b) { return b; }
+	bool lockstep = false;	// the worst the other groups of a warp can do: every pass runs again, with this group switched off
+	bool any(bool b) { return b || lockstep; }
 	static unsigned sgn(float x) { unsigned u; memcpy(&u, &x, 4); return u >> 31; }
 	void sums(int is_mean, int *n, double *S1, double *S2, float *mn, float *mx) {
 		passes++;
@@ -70,7 +71,7 @@ struct HostPasses {
 		passes++;
 		unsigned c = 0; bool ov = false;
 		for (int t = 0; t < T; t++) {
-			lists[t].clear();
+			if (on) lists[t].clear();
 			bool stop = !on;
 			for (int j = 0; j < R; j++) {
 				if (j % LCHUNK == 0 && (int) lists[t].size() > lcap_of(T) - LCHUNK) { stop = true; ov = true; }
@@ -82,13 +83,14 @@ struct HostPasses {
 		}
 		*below = (int) c; *over = ov && on;
 	}
-	void classify(const PselPlan &pl, int *cc, int *ccb, int *nl) {
-		int a = 0, b = 0, l = 0;
+	void classify(const PselPlan &pl, int *cc, int *ccb, int *nl, int *m) {
+		int a = 0, b = 0, l = 0, all = 0;
 		for (int t = 0; t < T; t++) for (float x : lists[t]) {
 			const float d = x - pl.p1;
 			if (fabsf(d) < pl.w) { a++; b += d < 0.f; } else l += d < 0.f;
+			all++;
 		}
-		*cc = a; *ccb = b; *nl = l;
+		*cc = a; *ccb = b; *nl = l; *m = all;
 	}
 };
 
@@ -108,26 +110,31 @@ struct HostLists {
 // returns status (FAST_DONE / FAST_FALLBACK); *result, rej[2] filled when FAST_DONE.
 // diag[0..5]: header flags, streaming passes run, centre entries, low entries, high entries, kept n
 extern "C" int psel_host_pixel(int is_float, const void *stack, int N, int T, int is_mean, int rejtype, float s0, float s1,
-		const double *weights, int rej[2], double *result, int diag[6]) {
+		const double *weights, int rej[2], double *result, int diag[6], int lockstep) {
 	RejCfg c{ is_mean ? rejtype : 0, s0, s1, nullptr, N, 0.f, 0.f, nullptr };
 	std::vector<float> o(N);
 	for (int i = 0; i < N; i++) o[i] = is_float ? ((const float *) stack)[i] : (float) ((const u16 *) stack)[i];
 	HostPasses hp;
-	hp.T = T; hp.R = (N + T - 1) / T; hp.cntN = N;
+	hp.T = T; hp.R = (N + T - 1) / T; hp.cntN = N; hp.lockstep = lockstep != 0;
 	hp.v.assign(T, std::vector<float>(hp.R, PSEL_NAN));
 	hp.lists.assign(T, {});
 	for (int i = 0; i < N; i++) hp.v[i % T][i / T] = o[i];
 	PselHdr h{};
 	const bool tails = is_mean && (rejtype == SGPU_SIGMA || rejtype == SGPU_PERCENTILE);
 	psel_group(hp, is_mean, tails, rejtype == SGPU_PERCENTILE, s0, s1, h);
-	std::vector<float> colbuf(std::max(N, (int) PSEL_ROWS) + 1, -12345.f);
+	std::vector<float> colbuf(std::max(N, (int) PSEL_ROWS) + 3, -12345.f);
 	HostCol col{ colbuf.data() };
 	HostLists ls{ hp };
 	rej[0] = rej[1] = 0;
 	int status;
 	auto orig = [&](int f) { return o[f]; };
-	*result = is_float ? psel_pixel<false>(col, ls, T, h, N, is_mean, c, weights, orig, rej, &status)
-			   : psel_pixel<true>(col, ls, T, h, N, is_mean, c, weights, orig, rej, &status);
+	if (!(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL))) {	// B1, lane after lane
+		std::vector<int> bc(T, 0);
+		for (int t = 0; t < T; t++) for (float x : hp.lists[t]) bc[psel_bucket(x, h.p1, h.w, T)]++;
+		for (int t = 0, base = 0; t < T; base += bc[t], t++) psel_sort_bucket(col, ls, T, t, base, h.p1, h.w);
+	}
+	*result = is_float ? psel_pixel<false>(col, h, N, is_mean, c, weights, orig, rej, &status)
+			   : psel_pixel<true>(col, h, N, is_mean, c, weights, orig, rej, &status);
 	if (diag) {
 		int cc = 0, nl = 0, nh = 0;
 		for (int t = 0; t < T; t++) for (float x : hp.lists[t]) {

@@ -35,17 +35,17 @@ def ph():
     L = C.CDLL(SO)
     L.psel_host_pixel.restype = C.c_int
     L.psel_host_pixel.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,
-                                  C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+                                  C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_int]
     return L
 
 
-def run(ph, st, T, is_mean, algo, sig, weights=None):
+def run(ph, st, T, is_mean, algo, sig, weights=None, lockstep=0):
     rej = (C.c_int * 2)()
     res = C.c_double()
     diag = (C.c_int * 6)()
     w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float64)
     status = ph.psel_host_pixel(int(st.dtype == np.float32), st.ctypes.data_as(C.c_void_p), len(st), T, int(is_mean), algo,
-                                sig[0], sig[1], None if w is None else w.ctypes.data_as(C.c_void_p), rej, C.byref(res), diag)
+                                sig[0], sig[1], None if w is None else w.ctypes.data_as(C.c_void_p), rej, C.byref(res), diag, lockstep)
     return status, res.value, rej[0], rej[1], list(diag)
 
 
@@ -115,6 +115,20 @@ def test_median_mode(ph, orc, dtype):
                     om, _ = orc.quickmedian(st)
                     assert m == om, (n, kind, T, m, om, diag)
     assert done / tot > 0.97, done / tot
+
+
+def test_lockstep_with_other_groups(ph):
+    """on the device the groups of a warp run every pass together: a group that is done must come
+    through the passes other groups still need (re-counts, moved windows) unchanged"""
+    rng = np.random.default_rng(12)
+    for n in (64, 100, 300):
+        for kind in ("clean", "hot", "zeros", "outliers"):
+            for _ in range(40):
+                st = make_stack(rng, n, np.float32, kind)
+                for is_mean, algo in ((True, O.SIGMA), (True, O.PERCENTILE), (False, O.NO_REJEC)):
+                    a = run(ph, st, 4, is_mean, algo, SIGS[algo])
+                    b = run(ph, st, 4, is_mean, algo, SIGS[algo], lockstep=1)
+                    assert a[:4] == b[:4], (n, kind, algo, a, b)
 
 
 def test_weird_samples_are_handed_over(ph):
