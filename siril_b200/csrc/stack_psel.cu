@@ -1,7 +1,6 @@
 // stack_psel.cu — launcher of the selection engine (kernel: stack_psel.cuh): picks the variant
-// (lanes per pixel, register slots) for the stack depth, sizes shared memory (the sample lists lie
-// over the dead upper rows of the tile when the stack is deep enough), clears the hand-over list,
-// launches, then lets the exact engine redo the list.
+// (lanes per pixel) for the stack depth, sizes shared memory, clears the hand-over list, launches,
+// then lets the exact engine redo the list.
 #include <cstdlib>
 #include "stack_psel.cuh"
 
@@ -9,19 +8,17 @@ using namespace sgpu;
 
 int sgpu_make_tile_tmap(sgpu_ctx *ctx, CUtensorMap *tm, void *base, size_t npix, int layers, int frames, int box_px, int box_rows);
 
-// 2^lt lanes per pixel, r register slots per lane; serves rf * 2^lt < N <= r * 2^lt; sub sub-tiles of 32 px per CTA
-struct PselVariant { int lt, r, rf, sub; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
-#define PV(LT, R, RF, SUB) { LT, R, RF, SUB, sgpu_launch_psel_variant<LT, R, RF, SUB> }
-static const PselVariant VARIANTS[] = {
-	PV(0, 50, 40, 4), PV(0, 64, 50, 4), PV(0, 80, 64, 4),			// N <= 80
-	PV(1, 50, 40, 2), PV(1, 64, 50, 2), PV(1, 80, 64, 2),			// 160
-	PV(2, 50, 40, 1), PV(2, 64, 50, 1), PV(2, 75, 64, 1), PV(2, 80, 75, 1),	// 320
-	PV(3, 50, 40, 1), PV(3, 64, 50, 1), PV(3, 75, 64, 1),			// 600
-	PV(4, 50, 37, 1), PV(4, 64, 50, 1), PV(4, 72, 64, 1),			// 1152
-};
+// 2^lt lanes per pixel; serves nmin <= N <= nmax (about 40 to 80 samples per lane); sub sub-tiles of 32 px per CTA
+struct PselVariant { int lt, nmin, nmax, sub; int (*launch)(sgpu_ctx *, const StackParams &, const CUtensorMap *, dim3, size_t); };
+#define PV(LT, NMIN, NMAX, SUB) { LT, NMIN, NMAX, SUB, sgpu_launch_psel_variant<LT, SUB> }
+static const PselVariant VARIANTS[] = { PV(0, 41, 80, 4), PV(1, 81, 160, 2), PV(2, 161, 320, 1), PV(3, 321, 640, 1), PV(4, 641, 1280, 1) };
 
 static const PselVariant *pick(int N) {
-	for (const PselVariant &v : VARIANTS) if ((v.r << v.lt) >= N && (v.rf << v.lt) < N) return &v;
+	if (const char *e = getenv("SGPU_PSEL_LT")) {	// tuning aid: force the group size (any depth the kernel's loops can walk)
+		const int lt = atoi(e);
+		for (const PselVariant &v : VARIANTS) if (v.lt == lt && N >= 41 && N <= 1280) return &v;
+	}
+	for (const PselVariant &v : VARIANTS) if (N >= v.nmin && N <= v.nmax) return &v;
 	return nullptr;
 }
 
@@ -62,9 +59,8 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	}
 	const int T = 1 << var->lt, nt = var->sub * T * 32, pxc = var->sub * TILE_PX;
 	const int rows8 = (p.tile_rows + 9) & ~7, lcap = psel_list_cap(T);
-	const bool overlay = rows8 > PSEL_ROWS && (size_t) (rows8 - PSEL_ROWS) * TILE_PX * var->sub >= (size_t) lcap * nt;
-	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * rows8 * sizeof(float) + (size_t) pxc * sizeof(PselHdr) + 16
-		+ ((p.use_tma && a->normalize != SGPU_NO_NORM) ? (size_t) d.nb_frames * 16 : 0) + (overlay ? 0 : (size_t) lcap * nt * sizeof(float));
+	const size_t shm = (size_t) var->sub * TILE_PX * rows8 * sizeof(float) + (size_t) pxc * sizeof(int) + 16
+		+ ((p.use_tma && a->normalize != SGPU_NO_NORM) ? (size_t) d.nb_frames * 16 : 0) + (size_t) lcap * nt * sizeof(float);
 	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the selection engine");
 	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
 	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);

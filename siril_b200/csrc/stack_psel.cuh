@@ -4,63 +4,102 @@
 //
 // One CTA owns SUB sub-tiles of 32 consecutive pixels of one layer (tile load: TMA, one 3-D box per
 // sub-tile and <= 256 frames, 128B swizzle; or coalesced row loads with x shifts / 16-bit samples —
-// stack_sorted.cuh's loaders).  A group of T = 2^LT lanes owns one pixel: lane t takes the samples
-// of rows j*T + t (bank-conflict free, as the lane-sort engine) into R registers and KEEPS them
-// there; a sub-tile is T warp-rounds of 32/T pixels and the CTA has SUB*T warps, one round each.
-//  phase A  psel_group (psel.cuh) drives the streaming passes below over the registers: sums
-//           (F2F.F64 + DADD + DFMA + 2 FMNMX per sample), count (2 FADD + 2 LEA.HI: sign bits added
-//           up, no compare), extract (2 FADD, LEA.HI, 2 FSETP, predicated STS + pointer bump).
-//           Scalars of a pixel are combined over its T lanes with shuffles.  The extracted samples
-//           go to per-thread lists laid over the (by then dead) upper rows of the tile when the
-//           stack is deep enough, else to shared memory of their own.
-//  phase B  B1, still the group: the lists are sorted in registers (the lane-sort engine's networks)
-//           into the first rows of the pixel's column; B2, after a barrier: thread i of the CTA finishes pixel
-//           i (psel_pixel: sorted.cuh's rejection code through the partial-rank accessor).
+// stack_sorted.cuh's loaders).  A group of T = 2^LT lanes owns one pixel: lane t walks the samples
+// of rows t, t + T, ... of the pixel's column (bank-conflict free, as the lane-sort engine); a
+// sub-tile is T warp-rounds of 32/T pixels and the CTA has SUB*T warps, one round each.
+//  phase A  psel_group (psel.cuh) drives the streaming passes below.  The samples STAY in shared
+//           memory and every pass is a compact loop of eight loads and eight bodies (an earlier
+//           version kept them in registers with every pass unrolled: 19 k SASS lines, and the
+//           instruction cache, not the pipes, set the pace): sums (LDS, F2F.F64, DADD, DFMA, FMNMX3),
+//           count (LDS, 2 FADD, 2 LEA.HI: sign bits added up, no compare), extract (LDS, 2 FADD,
+//           LEA.HI, 2 FSETP, predicated STS + pointer bump into a per-lane list).  Scalars of a
+//           pixel are combined over its T lanes with shuffles.
+//  phase B  B1, still the group: the lists are dealt out evenly over the lanes, sorted in registers
+//           (the lane-sort engine's networks) and written over the first rows of the pixel's column;
+//           B2, after a barrier: thread i of the CTA finishes pixel i (psel_pixel: sorted.cuh's
+//           rejection code through the partial-rank accessor).
 #pragma once
 #include "stack_lsort.cuh"
 #include "psel.cuh"
 
 namespace sgpu {
 
+__device__ __forceinline__ float lds_f32(unsigned a) { float x; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(a)); return x; }
+__device__ __forceinline__ void sts_f32(unsigned a, float x) { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(x) : "memory"); }
+
 // the streaming passes of one lane (psel_group's `P`)
-template <int LT, int R, int RF>
+template <int LT>
 struct PselLane {
 	static constexpr int T = 1 << LT;
-	float v[R];		// samples j*T + t; NaN: absent (beyond the stack, or a null in mean mode)
+	static constexpr int NA = (T >= 8) ? 1 : 8 / T;	// distinct values of row & 7 among a lane's rows
+	unsigned la[NA];	// shared-memory address of (row q*T + t, px): rows 8 apart share the swizzle term
 	int t, N;
-	unsigned gmask;
 	unsigned list0;		// shared-memory address of this thread's first list slot
 	unsigned lstride;	// bytes between its slots
 	unsigned lcap;		// slots
 	int cnt;		// entries after the last extraction
+	unsigned pk;		// of which: centre | centre below p1 << 10 | low tail << 20 (classify)
+	const double2 *coef;	// per-frame {scale, offset | mul} when the tile holds raw samples, else null
+	int norm_mode;		// 1 additive family, 2 multiplicative family (with coef)
 
 	__device__ __forceinline__ bool any(bool b) const { return __any_sync(0xffffffffu, b); }
 	template <typename V> __device__ __forceinline__ V gsum(V x) const {
 #pragma unroll
-		for (int m = 1; m < T; m <<= 1) x += __shfl_xor_sync(gmask, x, m);
+		for (int m = 1; m < T; m <<= 1) x += __shfl_xor_sync(0xffffffffu, x, m);
 		return x;
 	}
 	__device__ __forceinline__ float gmin(float x) const {
 #pragma unroll
-		for (int m = 1; m < T; m <<= 1) x = fminf(x, __shfl_xor_sync(gmask, x, m));
+		for (int m = 1; m < T; m <<= 1) x = fminf(x, __shfl_xor_sync(0xffffffffu, x, m));
 		return x;
 	}
 	__device__ __forceinline__ float gmax(float x) const {
 #pragma unroll
-		for (int m = 1; m < T; m <<= 1) x = fmaxf(x, __shfl_xor_sync(gmask, x, m));
+		for (int m = 1; m < T; m <<= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, m));
 		return x;
+	}
+
+	// f(k, x, row, address) for every sample of the lane, eight at a time: loads first, then the
+	// bodies; k = 0..7 is the position inside the batch (compile-time: accumulator chains alternate on it)
+	template <class F> __device__ __forceinline__ void each(F f) const {
+		const int nfull = N / (8 * T);
+		unsigned off = 0;
+#pragma unroll 1
+		for (int it = 0; it < nfull; it++, off += 1024u * T) {
+			float x[8];
+#pragma unroll
+			for (int k = 0; k < 8; k++) x[k] = lds_f32(la[k % NA] + off + (unsigned) ((k - k % NA) * T * 128));
+#pragma unroll
+			for (int k = 0; k < 8; k++) f(k, x[k], it * 8 * T + k * T + t, la[k % NA] + off + (unsigned) ((k - k % NA) * T * 128));
+		}
+		// the rest (< 8 T rows): batches of NA samples, one of each swizzle term
+		for (int row = nfull * 8 * T + t; row < N; row += NA * T, off += (unsigned) (NA * T * 128)) {
+#pragma unroll
+			for (int q = 0; q < NA; q++) if (row + q * T < N) {
+				const unsigned a = la[q] + off;
+				f(q, lds_f32(a), row + q * T, a);
+			}
+		}
 	}
 
 	__device__ __forceinline__ void sums(int is_mean, int *n, double *S1, double *S2, float *mn, float *mx) {
 		double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
 		float lo = SGPU_INF, hi = -SGPU_INF;
-#pragma unroll
-		for (int j = 0; j < R; j++) {
-			const float x = v[j];
-			double xd = (double) x;
-			if (j >= RF && j * T + t >= N) xd = 0.0;	// beyond the stack (a NaN among the samples must poison the sums)
-			if (j & 1) { b1 += xd; b2 = fma(xd, xd, b2); } else { a1 += xd; a2 = fma(xd, xd, a2); }
-			lo = fminf(lo, x); hi = fmaxf(hi, x);		// NaN is ignored
+		if (coef) {	// raw samples in the tile: normalize (median_and_mean.c:1644-1686) and park the result
+			each([&](int k, float x, int row, unsigned a) {
+				const double2 c = coef[row];
+				x = norm_mode == 1 ? normalize_sample<float, 1>(x, c.x, c.y) : normalize_sample<float, 2>(x, c.x, c.y);
+				sts_f32(a, x);
+				const double xd = (double) x;
+				if (k & 1) { b1 += xd; b2 = fma(xd, xd, b2); } else { a1 += xd; a2 = fma(xd, xd, a2); }
+				lo = fminf(lo, x); hi = fmaxf(hi, x);
+			});
+		} else {
+			each([&](int k, float x, int, unsigned) {
+				const double xd = (double) x;
+				if (k & 1) { b1 += xd; b2 = fma(xd, xd, b2); } else { a1 += xd; a2 = fma(xd, xd, a2); }
+				lo = fminf(lo, x); hi = fmaxf(hi, x);		// NaN is ignored
+			});
 		}
 		*S1 = gsum(a1 + b1); *S2 = gsum(a2 + b2);
 		lo = gmin(lo); hi = gmax(hi);
@@ -68,11 +107,10 @@ struct PselLane {
 		if (is_mean && any(lo <= 0.f && hi >= 0.f)) {	// nulls: drop them (rejection_float.c:128-135)
 			const bool mine = lo <= 0.f && hi >= 0.f;
 			lo = SGPU_INF; hi = -SGPU_INF;
-#pragma unroll
-			for (int j = 0; j < R; j++) {
-				if (mine && v[j] == 0.f) { v[j] = PSEL_NAN; nz++; }
-				lo = fminf(lo, v[j]); hi = fmaxf(hi, v[j]);
-			}
+			each([&](int, float x, int, unsigned a) {
+				if (mine && x == 0.f) { x = PSEL_NAN; sts_f32(a, x); nz++; }
+				lo = fminf(lo, x); hi = fmaxf(hi, x);
+			});
 			nz = gsum(nz); lo = gmin(lo); hi = gmax(hi);
 		}
 		*n = N - nz; *mn = lo; *mx = hi;
@@ -80,55 +118,50 @@ struct PselLane {
 
 	__device__ __forceinline__ void shifted_sums(double K, double *S1, double *S2) {
 		double a1 = 0.0, a2 = 0.0;
-#pragma unroll
-		for (int j = 0; j < R; j++) {
-			const float x = v[j];
+		each([&](int, float x, int, unsigned) {
 			const double y = (x == x) ? (double) x - K : 0.0;
 			a1 += y; a2 = fma(y, y, a2);
-		}
+		});
 		*S1 = gsum(a1); *S2 = gsum(a2);
 	}
 
 	// sign bits added up: x < mean, |x - mean| < hw (NaN: neither)
 	__device__ __forceinline__ void count(float mean, float hw, int *c_neg, int *c_in) {
 		unsigned a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-#pragma unroll
-		for (int j = 0; j < R; j++) {
-			const float d = v[j] - mean;
+		each([&](int k, float x, int, unsigned) {
+			const float d = x - mean;
 			const float u = fabsf(d) - hw;
-			if (j & 1) { a1 += __float_as_uint(d) >> 31; b1 += __float_as_uint(u) >> 31; }
+			if (k & 1) { a1 += __float_as_uint(d) >> 31; b1 += __float_as_uint(u) >> 31; }
 			else { a0 += __float_as_uint(d) >> 31; b0 += __float_as_uint(u) >> 31; }
-		}
-		const unsigned pk = gsum((a0 + a1) | ((b0 + b1) << 16));	// stacks are at most 2560 deep
+		});
+		const unsigned pk = gsum((a0 + a1) | ((b0 + b1) << 16));	// stacks are at most 1280 deep
 		*c_neg = (int) (pk & 0xffffu); *c_in = (int) (pk >> 16);
 	}
 
 	__device__ __forceinline__ void extract(bool on, const PselPlan &pl, int *below, bool *over) {
 		unsigned ptr = list0;
-		const unsigned lim = list0 + (lcap - 8u) * lstride;	// a chunk of 8 samples starts only with 8 free slots
+		const unsigned lim = list0 + (lcap - 8u) * lstride;	// a batch of 8 samples starts only with 8 free slots
 		float w = on ? pl.w : -1.f, rT = on ? pl.rT : FLT_MAX;
 		const float p1 = pl.p1, cT = pl.cT;
+		const unsigned ls = lstride;
 		unsigned c0 = 0, c1 = 0;
 		bool ov = false;
-#pragma unroll
-		for (int j = 0; j < R; j++) {
-			if (j % 8 == 0 && j > 0) { if (ptr > lim) { w = -1.f; rT = FLT_MAX; ov = true; } }
-			const float x = v[j];
+		each([&](int k, float x, int, unsigned) {
+			if (k == 0 && ptr > lim) { w = -1.f; rT = FLT_MAX; ov = true; }
 			const float d1 = x - p1, d2 = x - cT;
-			if (j & 1) c1 += __float_as_uint(d1) >> 31; else c0 += __float_as_uint(d1) >> 31;
+			if (k & 1) c1 += __float_as_uint(d1) >> 31; else c0 += __float_as_uint(d1) >> 31;
 			asm volatile("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %2, %3;\n\tsetp.lt.or.f32 q, %4, %5, q;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %6;\n\t}"
-				: "+r"(ptr) : "f"(x), "f"(fabsf(d2)), "f"(rT), "f"(fabsf(d1)), "f"(w), "r"(lstride) : "memory");
-		}
-		if (on) cnt = (int) ((ptr - list0) / lstride);	// a group that is done keeps its lists while others extract again
+				: "+r"(ptr) : "f"(x), "f"(fabsf(d2)), "f"(rT), "f"(fabsf(d1)), "f"(w), "r"(ls) : "memory");
+		});
+		if (on) cnt = (int) ((ptr - list0) / ls);	// a group that is done keeps its lists while others extract again
 		*below = (int) gsum(c0 + c1);
 		*over = gsum((int) ov) != 0;
 	}
 
-	__device__ __forceinline__ void classify(const PselPlan &pl, int *cc, int *ccb, int *nl, int *m) const {
-		unsigned pk = 0;	// centre | centre below p1 << 10 | low tail << 20
+	__device__ __forceinline__ void classify(const PselPlan &pl, int *cc, int *ccb, int *nl, int *m) {
+		pk = 0;
 		for (int k = 0; k < cnt; k++) {
-			float x;
-			asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(list0 + (unsigned) k * lstride));
+			const float x = lds_f32(list0 + (unsigned) k * lstride);
 			const float d = x - pl.p1;
 			const bool in = fabsf(d) < pl.w, neg = d < 0.f;
 			pk += in ? (neg ? 1u + (1u << 10) : 1u) : (neg ? (1u << 20) : 0u);
@@ -139,38 +172,52 @@ struct PselLane {
 	}
 };
 
-// phase B's views of shared memory.  The tile is dead once every sample sits in a register, so a
-// pixel's column is addressed plainly (row i at i * 128 + px * 4 bytes: bank = px whatever the row)
+// a pixel's column inside the 128B-swizzled tile: row i, as the TMA wrote it (B1 sorts into the
+// column while other groups of the sub-tile still read theirs, so the swizzle stays)
 struct PselCol {
-	unsigned a0;	// shared-memory address of row 0
-	__device__ __forceinline__ float get(int i) const { float x; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(a0 + (unsigned) i * 128u)); return x; }
-	__device__ __forceinline__ void set(int i, float x) const { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a0 + (unsigned) i * 128u), "f"(x) : "memory"); }
+	unsigned a0, c;	// address of (row 0, chunk 0) + (px & 3) * 4; c = px >> 2
+	__device__ __forceinline__ PselCol(const float *srows, int px) : a0(smem_u32(srows) + ((unsigned) (px & 3) << 2)), c((unsigned) px >> 2) { }
+	__device__ __forceinline__ unsigned at(int i) const { return a0 + (unsigned) i * 128u + ((((unsigned) i ^ c) & 7u) << 4); }
+	__device__ __forceinline__ float get(int i) const { return lds_f32(at(i)); }
+	__device__ __forceinline__ void set(int i, float x) const { sts_f32(at(i), x); }
 };
 
-// register slots per lane for the sort of the lists (stack_lsort.cuh's network sizes)
-constexpr int psel_sort_slots(int T) { return T == 1 ? 50 : (T == 2 ? 32 : (T == 4 ? 24 : (T == 8 ? 16 : 8))); }
+// register slots per lane for the sort of the lists (network sizes of the lane-sort engine): 64 entries
+// in all, and 96 and more for the rare long list
+constexpr int psel_sort_slots(int T) { return T == 1 ? 64 : (T == 2 ? 32 : (T == 4 ? 16 : (T == 8 ? 8 : 4))); }
+constexpr int psel_sort_slots2(int T) { return T == 1 ? 80 : (T == 2 ? 48 : (T == 4 ? 24 : (T == 8 ? 16 : 8))); }
 
-constexpr int psel_min_blocks(int nt, int r) {
-	const int regs = (r + 53 + 7) & ~7, b = 65536 / (nt * regs);
-	return b < 1 ? 1 : (b > 6 ? 6 : b);
+// rows [0, m) of the column, dealt out over the group's lanes (lane t: rows t, t + T, ...), sorted,
+// and written back lane-major (lane t: rows t * RB ...)
+template <int LT, int RB>
+__device__ __forceinline__ void psel_sort_rows(const PselCol &col, int t, int m, unsigned gmask) {
+	constexpr int T = 1 << LT;
+	float e[RB];
+#pragma unroll
+	for (int k = 0; k < RB; k++) { e[k] = SGPU_INF; if (t + T * k < m) e[k] = col.get(t + T * k); }
+	__syncwarp();
+	LocalNet<RB>::template run<RB>(e);
+	if constexpr (LT > 0) group_merge<LT, RB>(e, t, gmask);
+#pragma unroll
+	for (int k = 0; k < RB; k++) if (t * RB + k < m) col.set(t * RB + k, e[k]);	// rank t*RB + k goes to row t*RB + k
 }
 
-template <int LT, int R, int RF, int SUB>
-__global__ void __launch_bounds__((SUB << LT) * 32, psel_min_blocks((SUB << LT) * 32, R))
+template <int LT, int SUB>
+__global__ void __launch_bounds__((SUB << LT) * 32, (SUB << LT) <= 4 ? 4 : ((SUB << LT) <= 8 ? 2 : 1))
 stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int T = 1 << LT, NW = SUB << LT, NT = NW * 32, PXC = SUB * TILE_PX;
 	extern __shared__ __align__(1024) unsigned char smem_raw[];
 	const int N = p.N;
-	float *rows = (float *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);	// [SUB][tile_rows8][32]
+	float *rows = (float *) smem_raw;	// [SUB][rows8][32]; the swizzle needs it 1024-byte aligned: the kernel has no static shared memory before it
+	if (smem_u32(smem_raw) & 1023u) __trap();
 	const int rows8 = (p.tile_rows + 9) & ~7;	// two rows more than the stack is deep: phase B adds two stand-ins to the sorted lists
 	const size_t sub_floats = (size_t) rows8 * TILE_PX;	// sub-tiles start on 1024-byte swizzle atoms
-	PselHdr *hdr = (PselHdr *) (rows + SUB * sub_floats);
-	unsigned long long *bar = (unsigned long long *) (hdr + PXC);
+	int *pix2tid = (int *) (rows + SUB * sub_floats);	// first thread of the group that worked on a pixel (its header lies in the group's list slots)
+	unsigned long long *bar = (unsigned long long *) (pix2tid + PXC);
 	double2 *coef = (double2 *) (bar + 2);		// [N] {scale, offset | mul} when the tile holds raw samples
-	// lists: over the tile rows the sorted lists of phase B cannot reach, when those suffice
+	const bool raw_norm = p.use_tma && p.normalize != SGPU_NO_NORM;
 	constexpr int LCAP = psel_list_cap(T);
-	const bool overlay = (size_t) (rows8 - PSEL_ROWS) * TILE_PX * SUB >= (size_t) LCAP * NT && rows8 > PSEL_ROWS;
-	float *lists = overlay ? nullptr : (float *) (coef + (p.normalize != SGPU_NO_NORM && p.use_tma ? N : 0));
+	float *lists = (float *) (coef + (raw_norm ? N : 0));	// [LCAP][NT]
 	const int layer = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * PXC;
 
@@ -185,7 +232,7 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 				for (int r0 = 0; r0 < p.tile_rows; r0 += p.box_rows)
 					tma_load_3d(rows + sb * sub_floats + (size_t) r0 * TILE_PX, &tmap, (int) (pix0 + sb * TILE_PX), layer, r0, bar);
 		}
-		if (p.normalize != SGPU_NO_NORM) {	// per-frame coefficients, staged while the tile is in flight
+		if (raw_norm) {	// per-frame coefficients, staged while the tile is in flight
 			const bool add = p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING;
 			const double *c0 = p.scale + layer * N, *c1 = (add ? p.offset : p.mul) + layer * N;
 			for (int i = threadIdx.x; i < N; i += NT) coef[i] = make_double2(c0[i], c1[i]);
@@ -199,85 +246,66 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 		}
 		__syncthreads();
 	}
-	const int tma_mode = !p.use_tma ? 0 : (p.normalize == SGPU_NO_NORM ? 0 : ((p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2));
 
 	// ---- phase A: warp w works on sub-tile w % SUB, round w / SUB ----
 	{
-		PselLane<LT, R, RF> ln;
+		PselLane<LT> ln;
 		const int t = lane & (T - 1), g = lane >> LT;
 		ln.t = t; ln.N = N;
-		ln.gmask = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane & ~(T - 1)));
 		const int sb = warp % SUB, r = warp / SUB;
-		float *srows = rows + sb * sub_floats;	// 1024-byte aligned
-		constexpr int NA = (T >= 8) ? 1 : 8 / T;	// distinct values of (j*T) & 7
+		const float *srows = rows + sb * sub_floats;	// 1024-byte aligned
 		const int px = lsort_pixel<LT>(r, g);
-		// byte address of (row j*T + t, px) = (la[k] + j*T*128) with k = ((j*T) & 7) / T: the 128B swizzle
-		// XORs the 16-byte chunk index with row & 7 = ((j*T) & 7) | (t & 7) [T <= 8], t & 7 [T > 8]
-		const char *la[NA];
-		{
-			const unsigned a0 = (unsigned) (t * 128) | ((unsigned) (((px >> 2) ^ t) & 7) << 4) | ((unsigned) (px & 3) << 2);
+		{	// address of (row q*T + t, px): the 128B swizzle XORs the 16-byte chunk index with row & 7
+			const unsigned a0 = smem_u32(srows) + (((unsigned) (t * 128) | ((unsigned) (((px >> 2) ^ t) & 7) << 4) | ((unsigned) (px & 3) << 2)));
 #pragma unroll
-			for (int k = 0; k < NA; k++) la[k] = (const char *) srows + (a0 ^ ((unsigned) ((k * T) & 7) << 4));
+			for (int q = 0; q < PselLane<LT>::NA; q++) ln.la[q] = (a0 ^ ((unsigned) ((q * T) & 7) << 4)) + (unsigned) (q * T * 128);
 		}
-#pragma unroll
-		for (int j = 0; j < R; j++) {
-			float x = PSEL_NAN;
-			const int i = j * T + t;
-			if (j < RF || i < N) {	// rows below RF are full for every stack depth this variant serves
-				x = *(const float *) (la[(((j * T) & 7) / T) % NA] + j * T * 128);
-				if (tma_mode) {
-					const double2 c = coef[i];
-					x = tma_mode == 1 ? normalize_sample<float, 1>(x, c.x, c.y) : normalize_sample<float, 2>(x, c.x, c.y);
-				}
-			}
-			ln.v[j] = x;
-		}
-		__syncthreads();	// every sample of the tile is in a register now: its rows become scratch (sorted lists below PSEL_ROWS, sample lists above when they fit)
-		// lists: one array [LCAP][NT] when separate, [LCAP][32 T] per sub-tile when laid over the tile
-		unsigned l0, lstr;
-		if (overlay) {
-			constexpr int per_sub = 32 * T;		// threads that work on one sub-tile
-			const int q = r * 32 + lane;		// this thread among them
-			l0 = smem_u32(rows + sb * sub_floats + (size_t) PSEL_ROWS * TILE_PX + q); lstr = per_sub * 4;
-		} else { l0 = smem_u32(lists + threadIdx.x); lstr = NT * 4; }
-		ln.list0 = l0; ln.lstride = lstr; ln.lcap = LCAP; ln.cnt = 0;
+		ln.coef = raw_norm ? coef : nullptr;
+		ln.norm_mode = (p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2;
+		ln.list0 = smem_u32(lists + threadIdx.x); ln.lstride = NT * 4; ln.lcap = LCAP; ln.cnt = 0;
 		const int rt = p.is_mean ? p.rc.type : SGPU_NO_REJEC;
 		PselHdr h;
 		psel_group(ln, p.is_mean, rt == SGPU_SIGMA || rt == SGPU_PERCENTILE, rt == SGPU_PERCENTILE, p.rc.s0, p.rc.s1, h);
 		h.tid0 = (int) threadIdx.x - t;
-		// ---- B1: the group sorts its lists in registers (the lane-sort engine's networks: every lane
-		// sorts its own entries, then the runs are merged lane-major) into the first rows of the column ----
-		constexpr int RE = psel_sort_slots(T);
-		const bool sorting = !(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL));
-		if (ln.gsum((int) (sorting && ln.cnt > RE)) > 0) h.flags |= PSEL_HANDOVER;	// a lane with more entries than sort slots
-		if (t == 0) hdr[sb * TILE_PX + px] = h;
-		{
-			float e[RE];
-			const int mine = sorting ? ln.cnt : 0;
+		// ---- B1: the group's entries, dealt out evenly over its lanes, sorted in registers (the
+		// lane-sort engine's networks) and written over the first rows of the pixel's (now dead) column ----
+		constexpr int RB = psel_sort_slots(T), RB2 = psel_sort_slots2(T);
+		const bool live = !(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL));
+		if (live && h.m > T * RB2) h.flags |= PSEL_HANDOVER;	// more than the networks take
+		const bool sorting = live && h.m <= T * RB2;
+		const PselCol col(srows, px);
+		const int mine = sorting ? ln.cnt : 0, m = sorting ? h.m : 0;
+		int pre = mine;		// entries of the lanes before this one
 #pragma unroll
-			for (int k = 0; k < RE; k++) {
-				e[k] = SGPU_INF;
-				if (k < mine) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(e[k]) : "r"(l0 + (unsigned) k * lstr));
-			}
-			LocalNet<RE>::template run<RE>(e);
-			if constexpr (LT > 0) group_merge<LT, RE>(e, t, ln.gmask);
-			__syncwarp();
-			const unsigned c0 = smem_u32(srows + px) + (unsigned) (t * RE) * 128u;
-			const int lim = sorting ? h.m - t * RE : 0;	// rank t*RE + k goes to row t*RE + k
+		for (int d = 1; d < T; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, pre, d, T); if (t >= d) pre += o; }
+		pre -= mine;
+		for (int k = 0; k < mine; k++) col.set(pre + k, lds_f32(ln.list0 + (unsigned) k * ln.lstride));
+		__syncwarp();
+		if (t == 0) {	// the lists are spent: the header goes over the group's first slots, word j to lane j % T
+			pix2tid[sb * TILE_PX + px] = h.tid0;
+			const unsigned *hw = (const unsigned *) &h;
 #pragma unroll
-			for (int k = 0; k < RE; k++) if (k < lim) asm volatile("st.shared.f32 [%0], %1;" :: "r"(c0 + (unsigned) k * 128u), "f"(e[k]) : "memory");
+			for (int j = 0; j < (int) (sizeof(PselHdr) / 4); j++) ((unsigned *) lists)[(j / T) * NT + h.tid0 + (j % T)] = hw[j];
 		}
+		if (!ln.any(m > T * RB)) psel_sort_rows<LT, RB>(col, t, m, 0xffffffffu);
+		else psel_sort_rows<LT, RB2>(col, t, m, 0xffffffffu);	// a long list somewhere in the warp: the larger network
 	}
 	__syncthreads();
 	if (threadIdx.x >= PXC) return;
 
-	// ---- phase B: thread i of the CTA owns pixel i of the tile ----
+	// ---- B2: thread i of the CTA owns pixel i of the tile ----
 	const int sb = threadIdx.x >> 5;
 	const size_t pix = pix0 + threadIdx.x;
 	int rej[2] = { 0, 0 };
 	if (pix < npix) {
-		const PselHdr h = hdr[threadIdx.x];
-		const PselCol col{ smem_u32(rows + sb * sub_floats + lane) };
+		PselHdr h;
+		{
+			const int tid0 = pix2tid[threadIdx.x];
+			unsigned *hw = (unsigned *) &h;
+#pragma unroll
+			for (int j = 0; j < (int) (sizeof(PselHdr) / 4); j++) hw[j] = ((const unsigned *) lists)[(j / T) * NT + tid0 + (j % T)];
+		}
+		const PselCol col(rows + sb * sub_floats, lane);
 		int status;
 		double result;
 		const int x = (int) (pix % p.W);
@@ -310,12 +338,12 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 
 }  // namespace sgpu
 
-template <int LT, int R, int RF, int SUB>
+template <int LT, int SUB>
 int sgpu_launch_psel_variant(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm);
 
-#define SGPU_PSEL_VARIANT(LT, R, RF, SUB) \
-	template <> int sgpu_launch_psel_variant<LT, R, RF, SUB>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
-		auto kern = sgpu::stack_psel_kernel<LT, R, RF, SUB>; \
+#define SGPU_PSEL_VARIANT(LT, SUB) \
+	template <> int sgpu_launch_psel_variant<LT, SUB>(sgpu_ctx *ctx, const sgpu::StackParams &p, const CUtensorMap *tmap, dim3 grid, size_t shm) { \
+		auto kern = sgpu::stack_psel_kernel<LT, SUB>; \
 		const CUtensorMap tm = tmap ? *tmap : CUtensorMap{}; \
 		if (shm > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm)); \
 		kern<<<grid, (SUB << LT) * 32, shm, ctx->stream>>>(p, tm); \

@@ -1,10 +1,12 @@
-// explicit instantiations of the selection engine kernel (split over files to build in parallel)
+// explicit instantiation of the selection engine kernel (one file per group size: parallel builds)
 #include "stack_psel.cuh"
 #define CE(a, b) LCE(a, b)
 namespace sgpu {
-SGPU_LOCALNET(24) {
-#include "gen/sortnet_24.inc"
+SGPU_LOCALNET(8) {
+#include "gen/sortnet_8.inc"
+}
+SGPU_LOCALNET(16) {
+#include "gen/sortnet_16.inc"
 }
 }  // namespace sgpu
-SGPU_PSEL_VARIANT(2, 75, 64, 1)
-SGPU_PSEL_VARIANT(2, 80, 75, 1)
+SGPU_PSEL_VARIANT(3, 1)

@@ -128,10 +128,17 @@ extern "C" int psel_host_pixel(int is_float, const void *stack, int N, int T, in
 	rej[0] = rej[1] = 0;
 	int status;
 	auto orig = [&](int f) { return o[f]; };
-	if (!(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL))) {	// B1, lane after lane
-		std::vector<int> bc(T, 0);
-		for (int t = 0; t < T; t++) for (float x : hp.lists[t]) bc[psel_bucket(x, h.p1, h.w, T)]++;
-		for (int t = 0, base = 0; t < T; base += bc[t], t++) psel_sort_bucket(col, ls, T, t, base, h.p1, h.w);
+	if (!(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL))) {	// B1 as the kernel leaves it: every entry, sorted
+		std::vector<float> lo, ce, hi;
+		for (int t = 0; t < T; t++) for (float x : hp.lists[t]) {
+			const float d = x - h.p1;
+			(fabsf(d) < h.w ? ce : (d < 0.f ? lo : hi)).push_back(x);
+		}
+		std::sort(lo.begin(), lo.end()); std::sort(ce.begin(), ce.end()); std::sort(hi.begin(), hi.end());
+		int r = 0;
+		for (float x : lo) col.set(r++, x);
+		for (float x : ce) col.set(r++, x);
+		for (float x : hi) col.set(r++, x);
 	}
 	*result = is_float ? psel_pixel<false>(col, h, N, is_mean, c, weights, orig, rej, &status)
 			   : psel_pixel<true>(col, h, N, is_mean, c, weights, orig, rej, &status);

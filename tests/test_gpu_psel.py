@@ -118,4 +118,4 @@ def test_config_strips(ref, name, n, c, w, full_h, dtype, seed, kw):
     r = args.result
     g = dict(out=tp.to_np(r.data), rej_low=tp.to_np(r.rejmap_low), rej_high=tp.to_np(r.rejmap_high), irej=r.irej)
     compare(g, ref.stack(host, **kw), name)
-    assert handed <= 2e-4 * c * rows * w + 2, handed     # the selection engine decides (nearly) every pixel itself
+    assert handed <= 1e-3 * c * rows * w + 2, handed     # the selection engine decides (nearly) every pixel itself
