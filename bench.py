@@ -1,16 +1,18 @@
 #!/usr/bin/env python3
 """bench.py — rejection-stacking hot path: input px-frames/s and fraction of the HBM roofline.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C2] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload target] [--impl reference]
 
-One "step" = one pass of the stacking call (normalization apply + rejection + combine + output
-write; for N > 1 also the NCCL gather of the output rows to rank 0) over one synthetic frame
-block resident in HBM.  Workloads are BASELINE.json's configs; the default (N = 1) is configs[1]:
-C2 = 100 x 6248x4176 mono float32, winsorized sigma clip 3/3, additive+scaling normalization.
-For N > 1 the image is row-sharded, one shard of the workload's height per rank (weak scaling).
+One "step" = one pass of the stacking call (normalization apply + rejection + combine + output and
+rejection-map writes; for N > 1 also the NCCL gather of the output rows and both rejection maps to
+rank 0 and the all-reduce of the rejection counters) over one synthetic frame block resident in
+HBM.  Workloads are BASELINE.json's configs plus the north-star target (sigma clip of 300 x 61 MP
+float frames), which is the default.  For N > 1 ONE image is row-sharded over the ranks (strong
+scaling): rank g holds rows [H*g/N, H*(g+1)/N) of every frame.
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the reference's own CPU implementation
-(oracle/_ref built from /root/reference, else the oracle port) on the host cores.
+(oracle/_ref built from /root/reference, else the oracle port) on the host cores, on a bounded row
+sample of the same workload, same generator, same coefficients.
 """
 import argparse
 import json
@@ -45,6 +47,7 @@ WORKLOADS = {
 }
 REJ_NAMES = ["none", "percentile", "sigma", "mad", "sigmedian", "winsorized", "linearfit", "gesdt"]
 METRIC = "input px-frames/s, rejection stacking"
+N_REJMAPS = 2       # both rejection maps are part of the output (median_and_mean.c:1333-1342)
 
 
 def measured_peak_gbs():
@@ -105,18 +108,33 @@ def algorithmic_bytes(n, c, h, w, es, out_es=4, n_rejmaps=0):
     return w * h * c * (n * es + out_es + 2 * n_rejmaps)
 
 
+def config_of(args, wl, world, extra=None):
+    """the `config` object: identical keys (and, for the same workload, values) in both arms"""
+    n, c, h, w, dt, is_mean, rej, sig, nrm, seed, label = wl
+    cfg = {"workload": label, "name": args.workload, "rejection": REJ_NAMES[rej] if is_mean else "median",
+           "frames": n, "width": w, "height": h, "layers": c, "rejection_maps": N_REJMAPS if is_mean and rej != NO_REJEC else 0,
+           "l2": "inputs larger than L2 (%.1f GB per step)" % (n * c * h * w * (4 if dt == "f32" else 2) / 1e9),
+           "sharding": ("rows [H*g/N, H*(g+1)/N) of one image per rank; output rows and both rejection maps gathered to rank 0 "
+                        "with NCCL, counters all-reduced") if world > 1 else "single GPU"}
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
 def cpu_reference_run(frames_np, wl, coeff, nthreads, budget_s=15.0):
     """Time the reference's CPU implementation on a bounded row sample of the same workload."""
     from oracle import oracle as O
     kind = "reference_fast" if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsiril_ref_fast.so")) else "port"
     orc = O.Oracle(kind)
     n, c, h, w, dt, is_mean, rej, sig, nrm, seed, label = wl
-    kw = dict(is_mean=is_mean, rejection=rej, sig=sig, normalize=nrm, nthreads=nthreads)
+    kw = dict(is_mean=is_mean, rejection=rej, sig=sig, normalize=nrm, nthreads=nthreads,
+              create_rejmaps=bool(is_mean and rej != NO_REJEC))
     if nrm != NO_NORM:
         kw.update(scale=coeff[2], offset=coeff[0], mul=coeff[1])
     rows_avail = frames_np.shape[2]
     # the reference's block planner needs at least a few rows per thread
     nthreads = max(1, min(nthreads, rows_avail // 4))
+    kw["nthreads"] = nthreads
     probe = min(rows_avail, max(16, 4 * nthreads))
     t0 = time.perf_counter()
     orc.stack(frames_np[:, :, :probe, :], **kw)
@@ -131,16 +149,64 @@ def cpu_reference_run(frames_np, wl, coeff, nthreads, budget_s=15.0):
             "sample": f"{n} frames x {rows} rows x {w} px x {c} layer(s) of the workload ({units:.3g} px-frames, {dt_s:.1f} s), frames in RAM"}, dt_s
 
 
-def synth_numpy(n, c, h, w, dt, seed):
-    """host-side synthetic rows for --impl reference when no GPU generator is available"""
+def synth_numpy(n, c, h, w, dt, seed, full_h):
+    """host twin of sgpu_synth_fill's model (misc.cu: per-frame sky / gain, a smooth signal, Gaussian
+    noise 0.01, hot and cold outliers) for --impl reference on a box without a GPU; not bit-equal"""
     rng = np.random.default_rng(seed)
-    sky = 0.10 * (1 + 0.02 * rng.uniform(-1, 1, (n, 1, 1, 1)))
-    gain = 1 + 0.05 * rng.uniform(-1, 1, (n, 1, 1, 1))
-    fr = gain * sky + 0.01 * rng.standard_normal((n, c, h, w))
-    hot = rng.random((n, c, h, w)) < 1e-3
-    fr[hot] += rng.uniform(0.2, 0.6, int(hot.sum()))
+    sky = 0.10 * (1 + 0.02 * rng.uniform(-1, 1, (n, c, 1, 1)))
+    gain = 1 + 0.05 * rng.uniform(-1, 1, (n, c, 1, 1))
+    yy, xx = np.mgrid[0:h, 0:w]
+    fx, fy = xx / w - 0.5, (yy + full_h // 2) / full_h - 0.5
+    sig = np.abs(0.3 * np.exp(-(fx * fx + fy * fy) * 8) * (0.6 + 0.4 * np.sin(12 * fx) * np.cos(9 * fy)))
+    fr = gain * (sky + sig[None, None]) + 0.01 * rng.standard_normal((n, c, h, w))
+    u = rng.random((n, c, h, w))
+    hot = u < 1e-3
+    fr[hot] += 0.2 + 0.4 * rng.random(int(hot.sum()))
+    fr[(u >= 1e-3) & (u < 1.2e-3)] -= 0.05
     fr = np.clip(fr, 1e-4, 1.0)
-    return np.round(fr * 65535).astype(np.uint16) if dt == "u16" else fr.astype(np.float32)
+    return np.maximum(np.rint(fr * 65535), 1).astype(np.uint16) if dt == "u16" else fr.astype(np.float32)
+
+
+def sample_rows(wl, rows):
+    """`rows` rows from the middle of the workload's frames, as the GPU arm stacks them: generated by
+    sgpu_synth_fill and downloaded when a GPU is there, else by the host twin.  Returns (frames,
+    coefficients (offset, mul, scale) or None, how)"""
+    n, c, h, w, dt, is_mean, rej, sig, nrm, seed, label = wl
+    row0 = max(0, (h - rows) // 2)
+    try:
+        import ctypes as C
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("no GPU")
+        import siril_b200 as sb
+        from siril_b200 import _lib
+        L = _lib.lib()
+        ctx = sb.Context(0, torch.cuda.current_stream().cuda_stream)
+        tdt = torch.float32 if dt == "f32" else torch.uint16
+        fr = torch.empty((n, c, rows, w), dtype=tdt, device="cuda")
+        desc = _lib.BlockDesc(n, c, w, rows, sb.DATA_FLOAT if dt == "f32" else sb.DATA_USHORT)
+        blk = C.c_void_p()
+        ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(fr.data_ptr()), C.byref(blk)))
+        ctx.check(L.sgpu_synth_fill(ctx.h, blk, seed, row0, h))
+        ctx.synchronize()
+        L.sgpu_block_destroy(blk)
+        coeff = None
+        if nrm != NO_NORM:      # the statistics of the strip stand in for the frame's (same code path, a fraction of the rows)
+            sargs = sb.StackingArgs(frames=fr, normalize=nrm, ctx=ctx)
+            sb.do_normalization(sargs)
+            coeff = (sargs.coeff.offset, sargs.coeff.mul, sargs.coeff.scale)
+        host = fr.view(torch.int16).cpu().numpy().view(np.uint16) if dt == "u16" else fr.cpu().numpy()
+        del fr
+        torch.cuda.empty_cache()
+        return host, coeff, "sgpu_synth_fill (the GPU arm's generator), downloaded"
+    except Exception as e:  # noqa: BLE001 — no GPU or no library: the host twin
+        frames = synth_numpy(n, c, rows, w, dt, seed, h)
+        coeff = None
+        if nrm != NO_NORM:
+            rng = np.random.default_rng(1)
+            coeff = (0.002 * rng.standard_normal((c, n)) * (65535 if dt == "u16" else 1),
+                     1 + 0.02 * rng.standard_normal((c, n)), 1 + 0.02 * rng.standard_normal((c, n)))
+        return frames, coeff, f"host twin of the generator ({type(e).__name__}: no GPU generator here)"
 
 
 def run_reference(args, wl):
@@ -149,14 +215,9 @@ def run_reference(args, wl):
         return 0
     n, c, h, w, dt, is_mean, rej, sig, nrm, seed, label = wl
     nthreads = os.cpu_count() or 1
-    rows = min(h, max(256, 8 * nthreads))
-    frames = synth_numpy(n, c, rows, w, dt, seed)
-    coeff = None
-    if nrm != NO_NORM:
-        rng = np.random.default_rng(1)
-        coeff = (0.002 * rng.standard_normal((c, n)) * (65535 if dt == "u16" else 1),
-                 1 + 0.02 * rng.standard_normal((c, n)), 1 + 0.02 * rng.standard_normal((c, n)))
-    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    rows = min(h, 640)      # enough rows for a few seconds of CPU work at any depth
+    frames, coeff, how = sample_rows(wl, rows)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))      # at least 2 s of CPU work per step
     vals, times = [], []
     for i in range(args.warmup + args.steps):
         cb, dt_s = cpu_reference_run(frames, wl, coeff, nthreads, budget_s=per_step)
@@ -164,13 +225,25 @@ def run_reference(args, wl):
             vals.append(cb["value"]); times.append(dt_s)
     v = float(np.mean(vals))
     cb["value"] = v
+    cb["sample"] += "; " + how
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     line = {"metric": METRIC, "value": v, "unit": "px-frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": float(np.mean(times) * 1e3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": dt, "data": "synthetic", "impl": "reference",
-            "config": {"workload": label, "name": args.workload, "rejection": REJ_NAMES[rej] if is_mean else "median"},
+            "ms_per_step": float(np.mean(times) * 1e3), "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": dt, "data": "synthetic", "impl": "reference",
+            "config": config_of(args, wl, world),
             "cpu_baseline": cb, "e2e": {"value": v, "unit": "px-frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+    return 0
+
+
+def mem_available_bytes():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except Exception:
+        pass
     return 0
 
 
@@ -179,9 +252,9 @@ def run_ours(args, wl):
     import torch
     import torch.distributed as dist
     import siril_b200 as sb
-    from siril_b200 import _lib
+    from siril_b200 import _lib, sharding
 
-    n, c, h, w, dt, is_mean, rej, sig, nrm, seed, label = wl
+    n, c, H, w, dt, is_mean, rej, sig, nrm, seed, label = wl
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -198,33 +271,36 @@ def run_ours(args, wl):
     ctx = sb.Context(local, stream.cuda_stream)
     tdt = torch.float32 if dt == "f32" else torch.uint16
     es = 4 if dt == "f32" else 2
+    r0, r1 = sharding.row_shard(H, rank, world)
+    h = r1 - r0                                     # this rank's rows of the ONE image (strong scaling)
+    maps = N_REJMAPS if (is_mean and rej != NO_REJEC) else 0
 
-    # ---- synthetic frame block for this rank's row shard (device-side generator) ----
+    # ---- synthetic frame block: this rank's rows of every frame (device-side generator) ----
     frames = torch.empty((n, c, h, w), dtype=tdt, device=dev)
     desc = _lib.BlockDesc(n, c, w, h, sb.DATA_FLOAT if dt == "f32" else sb.DATA_USHORT)
     blk = C.c_void_p()
     ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
-    ctx.check(L.sgpu_synth_fill(ctx.h, blk, seed, rank * h, world * h))
+    ctx.check(L.sgpu_synth_fill(ctx.h, blk, seed, r0, H))
     ctx.synchronize()
 
-    # ---- normalization coefficients (K3/K4): frame-parallel estimators, all-gathered ----
+    # ---- normalization coefficients (K3/K4) from whole-frame statistics ----
     sargs = sb.StackingArgs(method=sb.stack_mean_with_rejection if is_mean else sb.stack_median, frames=frames,
-                            type_of_rejection=rej, sig=sig, normalize=nrm, ctx=ctx,
+                            type_of_rejection=rej, sig=sig, normalize=nrm, ctx=ctx, create_rejmaps=maps > 0,
                             weighting_type=sb.NOISE_WEIGHT if args.workload == "C3" else sb.NO_WEIGHT)
     stats_ms = None
     if nrm != NO_NORM:
-        from siril_b200.stacking import compute_estimators, finalize_factors
-        if world > 1:       # the first collective pays the communicator set-up: keep it out of stats_ms
-            dist.all_reduce(torch.zeros(1, device=dev))
-        mine = list(range(rank, n, world))
-        from siril_b200.stacking import STATS_WORKERS
-        compute_estimators(sargs, mine[:STATS_WORKERS])     # warm-up: worker contexts, scratch, kernel attributes
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        off, mul, sc, bg = compute_estimators(sargs, mine)
-        if world > 1:
-            from siril_b200 import sharding
-            off, mul, sc, bg = sharding.merge_estimators(dist, [off, mul, sc, bg], mine, device=dev)
+        from siril_b200.stacking import compute_estimators, finalize_factors, STATS_WORKERS
+        if world > 1:       # every rank holds rows of every frame: the reductions behind the statistics are all-reduced
+            dist.all_reduce(torch.zeros(1, device=dev))     # the first collective pays the communicator set-up
+            reducer = sharding.make_reducer(dist, dev)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            off, mul, sc, bg = compute_estimators(sargs, shard=(reducer, r0, H))
+        else:
+            compute_estimators(sargs, list(range(min(n, STATS_WORKERS))))     # warm-up: worker contexts, scratch, kernel attributes
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            off, mul, sc, bg = compute_estimators(sargs)
         finalize_factors(sargs, off, mul, sc)
         sargs.bgnoise = bg
         torch.cuda.synchronize()
@@ -235,13 +311,52 @@ def run_ours(args, wl):
     keep = []
     cargs = sb.stacking._fill_cargs(sargs, n, c, is_mean, keep)
     out = torch.empty((c, h, w), dtype=torch.float32, device=dev)
+    rlo = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if maps else None
+    rhi = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if maps else None
     irej = torch.zeros(6, dtype=torch.int64, device=dev)
-    gathered = [torch.empty_like(out) for _ in range(world)] if (world > 1 and rank == 0) else None
+    full = None
+    if world > 1 and rank == 0:     # the whole image on rank 0: [C][H][W] result and both maps
+        full = [torch.empty((c, H, w), dtype=torch.float32, device=dev)] + \
+               ([torch.empty((c, H, w), dtype=torch.uint16, device=dev) for _ in range(2)] if maps else [])
+    bounds = [sharding.row_shard(H, g, world) for g in range(world)]
+
+    def stack():
+        irej.zero_()
+        ctx.check(L.sgpu_stack_block(ctx.h, blk, C.byref(cargs), C.c_void_p(out.data_ptr()),
+                                     C.c_void_p(rlo.data_ptr()) if maps else None, C.c_void_p(rhi.data_ptr()) if maps else None,
+                                     C.c_void_p(irej.data_ptr())))
+
+    def gather():
+        """output rows and rejection maps of every rank into the image on rank 0; counters summed"""
+        parts = [out] + ([rlo, rhi] if maps else [])
+        ops = []
+        if rank == 0:
+            for t_full, t_mine in zip(full, parts):
+                t_full[:, r0:r1, :].copy_(t_mine)
+            recv = []
+            for g in range(1, world):
+                a, b = bounds[g]
+                for t_full in full:
+                    view = t_full[:, a:b, :]        # mono: the rows of a rank are one contiguous piece of the image
+                    buf = view if view.is_contiguous() else torch.empty((c, b - a, w), dtype=t_full.dtype, device=dev)
+                    if buf is not view:
+                        recv.append((view, buf))
+                    ops.append(dist.P2POp(dist.irecv, buf, g))
+            for q in dist.batch_isend_irecv(ops):
+                q.wait()
+            for view, buf in recv:
+                view.copy_(buf)
+        else:
+            for t_mine in parts:
+                ops.append(dist.P2POp(dist.isend, t_mine, 0))
+            for q in dist.batch_isend_irecv(ops):
+                q.wait()
+        dist.all_reduce(irej)
 
     def step():
-        ctx.check(L.sgpu_stack_block(ctx.h, blk, C.byref(cargs), C.c_void_p(out.data_ptr()), None, None, C.c_void_p(irej.data_ptr())))
+        stack()
         if world > 1:
-            dist.gather(out, gathered, dst=0)
+            gather()
 
     for _ in range(args.warmup):
         step()
@@ -259,10 +374,10 @@ def run_ours(args, wl):
     for i in range(args.steps):
         k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         k0.record(stream)
-        ctx.check(L.sgpu_stack_block(ctx.h, blk, C.byref(cargs), C.c_void_p(out.data_ptr()), None, None, C.c_void_p(irej.data_ptr())))
+        stack()
         k1.record(stream)
         if world > 1:
-            dist.gather(out, gathered, dst=0)
+            gather()
         ev[i + 1].record(stream)
         kev.append((k0, k1))
     torch.cuda.synchronize()
@@ -271,31 +386,47 @@ def run_ours(args, wl):
     total_ms = ev[0].elapsed_time(ev[-1])
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
     launches = ctx.launches - launches0
-    handed = ctx.handovers
+    handed = torch.tensor([ctx.handovers], dtype=torch.int64, device=dev)
     kernel_name = ctx.last_engine
     clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(handed)
     total_ms, kernel_ms_max = float(t[0]), float(t[1])
     ms_per_step = total_ms / args.steps
-    units = n * c * h * w * world
+    units = n * c * H * w                           # the whole job: every rank's rows
     value = units / (ms_per_step * 1e-3)
 
     # ---- end-to-end step through the host entry point (pinned host frames, H2D + D2H inside) ----
     e2e = None
     if not args.no_e2e:
         frame_bytes = c * h * w * es
-        host = torch.empty((n, c, h, w), dtype=tdt).pin_memory()
-        host.copy_(frames)
+        need = n * frame_bytes
+        avail = mem_available_bytes()
+        e_rows = h
+        if need > 0.6 * avail or need > (100 << 30):     # host RAM decides how much of the shard the host arm can hold pinned
+            e_rows = max(16, int(h * min(0.6 * avail, 100 << 30) / need) // 4 * 4)
+        e_rows = min(e_rows, h)
+        eframe = c * e_rows * w * es
+        host = torch.empty((n, c, e_rows, w), dtype=tdt).pin_memory()
+        host.copy_(frames[:, :, :e_rows, :])
         torch.cuda.synchronize()
-        hout = torch.empty((c, h, w), dtype=torch.float32).pin_memory()
-        ptrs = (C.c_void_p * n)(*[host.data_ptr() + f * frame_bytes for f in range(n)])
+        edesc = _lib.BlockDesc(n, c, w, e_rows, sb.DATA_FLOAT if dt == "f32" else sb.DATA_USHORT)
+        hout = torch.empty((c, e_rows, w), dtype=torch.float32).pin_memory()
+        hlo = torch.empty((c, e_rows, w), dtype=torch.uint16).pin_memory() if maps else None
+        hhi = torch.empty((c, e_rows, w), dtype=torch.uint16).pin_memory() if maps else None
+        ptrs = (C.c_void_p * n)(*[host.data_ptr() + f * eframe for f in range(n)])
         hirej = (C.c_uint64 * 6)()
-        e2e_steps = max(1, min(args.steps, 3))
+        e2e_steps = max(1, min(args.steps, 2))
+        del frames      # the resident block makes room for the host arm's row blocks
+        L.sgpu_block_destroy(blk)
+        blk = None
+        torch.cuda.empty_cache()
 
         def e2e_step():
-            ctx.check(L.sgpu_stack_host(ctx.h, C.byref(desc), ptrs, None, C.byref(cargs), C.c_void_p(hout.data_ptr()), None, None, hirej))
+            ctx.check(L.sgpu_stack_host(ctx.h, C.byref(edesc), ptrs, None, C.byref(cargs), C.c_void_p(hout.data_ptr()),
+                                        C.c_void_p(hlo.data_ptr()) if maps else None, C.c_void_p(hhi.data_ptr()) if maps else None, hirej))
         e2e_step()   # warm-up
         if world > 1:
             dist.barrier()
@@ -305,47 +436,51 @@ def run_ours(args, wl):
             e2e_step()
         torch.cuda.synchronize()
         dt_s = (time.perf_counter() - t0) / e2e_steps
+        e_units = torch.tensor([float(n * c * e_rows * w)], dtype=torch.float64, device=dev)
         tt = torch.tensor([dt_s], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e = {"value": units / float(tt[0]), "unit": "px-frames/s", "h2d_bytes_per_step": n * frame_bytes * world,
-               "d2h_bytes_per_step": (c * h * w * 4 + 48) * world, "ms_per_step": float(tt[0]) * 1e3, "steps": e2e_steps,
-               "path": "sgpu_stack_host: pinned host frames -> H2D -> stack -> D2H result"}
+            dist.all_reduce(e_units)
+        e2e = {"value": float(e_units[0]) / float(tt[0]), "unit": "px-frames/s",
+               "h2d_bytes_per_step": int(float(e_units[0]) * es),
+               "d2h_bytes_per_step": int(float(e_units[0]) / n * (4 + 2 * maps) + 48 * world),
+               "ms_per_step": float(tt[0]) * 1e3, "steps": e2e_steps,
+               "rows_per_rank": e_rows, "rows_of_shard": h,
+               "path": "sgpu_stack_host: pinned host frames -> H2D in row blocks (three rotating device buffers) -> stack -> D2H result + rejection maps"
+                       + ("" if e_rows == h else f"; host RAM holds {e_rows} of the shard's {h} rows")}
         del host
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
-        B = algorithmic_bytes(n, c, h, w, es)
+        B = algorithmic_bytes(n, c, h, w, es, n_rejmaps=maps)   # rank 0's launch: its rows
         achieved = B / (kernel_ms_max * 1e-3) / 1e9
         traffic = None    # DRAM bytes per launch from the committed ncu --set full capture (per px-frame x units)
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            t = json.load(open(tp)).get(args.workload)
-            if t and t.get("kernel") == kernel_name:
-                traffic = t["dram_bytes_per_px_frame"] * n * c * h * w
+            tj = json.load(open(tp)).get(args.workload)
+            if tj and tj.get("kernel") == kernel_name:
+                traffic = tj["dram_bytes_per_px_frame"] * n * c * h * w
         cb = None
-        if world == 1 or True:
-            rows = min(h, max(256, 8 * (os.cpu_count() or 1)))
-            sample = frames[:, :, :rows, :].contiguous()
-            sample_np = (sample.view(torch.int16).cpu().numpy().view(np.uint16) if dt == "u16" else sample.cpu().numpy())
+        if not args.no_cpu:
+            rows = min(H, 640)
+            sample_np, _, how = sample_rows(wl, rows)
             cb, _ = cpu_reference_run(sample_np, wl, coeff_np, os.cpu_count() or 1, budget_s=args.cpu_budget)
+            cb["sample"] += "; " + how
         line = {
             "metric": METRIC, "value": value, "unit": "px-frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
             "dtype": dt, "data": "synthetic",
-            "config": {"workload": label, "name": args.workload, "rejection": REJ_NAMES[rej] if is_mean else "median",
-                       "frames": n, "width": w, "height_per_gpu": h, "layers": c,
-                       "l2": "inputs larger than L2 (%.1f GB per GPU per step)" % (n * c * h * w * es / 1e9),
-                       "sharding": "row shards, one per rank; output rows gathered to rank 0 with NCCL" if world > 1 else "single GPU",
-                       "stats_ms": stats_ms,
-                       "handed_to_exact_engine_px": handed},
+            "config": config_of(args, wl, world),
+            "detail": {"rows_on_rank0": h, "stats_ms": stats_ms, "handed_to_exact_engine_px": int(handed[0])},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": kernel_name, "kernel_ms": kernel_ms_max,
-                         "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0},
+                         "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0,
+                         "note": "per GPU: the stack kernel of rank 0's rows (slowest rank's time)" if world > 1 else "the stack kernel"},
             "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line))
-    L.sgpu_block_destroy(blk)
+    if blk is not None:
+        L.sgpu_block_destroy(blk)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -357,9 +492,10 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="target", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's rows per GPU")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's image height")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--rej", default="", help="profiling only: override the workload's rejection (none, sigma, winsorized, ...)")
     args = ap.parse_args()

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SGPU_ABI_VERSION 1
+#define SGPU_ABI_VERSION 2
 
 enum {	/* stacking.h:18-24 */
 	SGPU_OK = 0,
@@ -159,6 +159,7 @@ typedef struct {
 	int use_32bit_output;		/* args->use_32bit_output: float result, else WORD result */
 	int create_rejmaps;		/* args->create_rejmaps */
 	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
+	int nb_critical;		/* entries critical_value holds; 0: not stated (trusted to be (int) floor((float) nb_frames * sig[0])) */
 	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 3: force the register engine; 4: force the thread-sort engine; 5: force the lane-sort engine; 6: force the selection engine */
 } sgpu_stack_args;
 
@@ -228,6 +229,20 @@ typedef struct {
 #define SGPU_STATS_NOISE_ONLY 2
 int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny,
 		int lite, sgpu_imstats *out);
+
+/* The same statistics of a frame held as ROW SHARDS, one process per GPU: `shard` is
+ * rows [row0, row0 + ny) of a plane of full_ny rows.  The estimators are whole-frame quantities
+ * (normalization.c:217-294 -> statistics_float.c:281-481), so every reduction over the plane — counts,
+ * sums, minima / maxima, the integer histograms the medians are read from, the per-row noise values —
+ * goes through `reduce` before it is used: an in-place all-reduce over all ranks of `count` elements
+ * of host memory (what ncclAllReduce / MPI_Allreduce do; return 0 on success).  Every rank must make
+ * the call for the same plane; every rank gets the whole frame's statistics — the counts and medians
+ * bit-identical to the unsharded ones, the double sums to ~1e-15 (the summation order differs). */
+enum { SGPU_RED_F32 = 0, SGPU_RED_F64 = 1, SGPU_RED_U32 = 2, SGPU_RED_U64 = 3 };
+enum { SGPU_RED_SUM = 0, SGPU_RED_MIN = 1, SGPU_RED_MAX = 2 };
+typedef int (*sgpu_reduce_fn)(void *user, void *host_buf, size_t count, int dtype, int op);
+int sgpu_image_stats_sharded(sgpu_ctx *ctx, const void *shard, int on_device, int dtype, long nx, long ny,
+		long row0, long full_ny, int lite, sgpu_reduce_fn reduce, void *user, sgpu_imstats *out);
 
 /* host-side scalar work, [nb_layers * nb_frames] arrays */
 /* _compute_estimators_for_image's choice of estimators (normalization.c:98-141) */

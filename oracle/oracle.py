@@ -49,7 +49,7 @@ def gesdt_critical_values(nb_frames, sig0, sig1):
     unpinned system dependency of the reference) is rounded to float, and the rest is float."""
     from scipy.stats import t as tdist
     f32 = np.float32
-    n_out = int(np.floor(nb_frames * float(f32(sig0))))
+    n_out = int(np.floor(f32(nb_frames) * f32(sig0)))     # int * float is a FLOAT product in the reference (median_and_mean.c:1479)
     out = np.empty(max(n_out, 0), dtype=np.float32)
     size = nb_frames
     for j in range(n_out):

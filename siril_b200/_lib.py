@@ -26,7 +26,8 @@ class StackArgs(C.Structure):
                 ("scale", C.c_void_p), ("offset", C.c_void_p), ("mul", C.c_void_p),
                 ("weights", C.c_void_p), ("shiftx", C.c_void_p),
                 ("output_norm", C.c_int), ("use_32bit_output", C.c_int),
-                ("create_rejmaps", C.c_int), ("merge_lowhigh_rejmaps", C.c_int), ("engine", C.c_int)]
+                ("create_rejmaps", C.c_int), ("merge_lowhigh_rejmaps", C.c_int), ("nb_critical", C.c_int),
+                ("engine", C.c_int)]
 
 
 class ImStats(C.Structure):
@@ -35,6 +36,9 @@ class ImStats(C.Structure):
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+REDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int)   # sgpu_reduce_fn
 
 
 class FitsInfo(C.Structure):
@@ -80,6 +84,8 @@ SIGNATURES = {
     "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_rescale_0_1": (C.c_int, [P, P, C.c_size_t, C.c_float, C.c_float]),
     "sgpu_image_stats": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_int, C.POINTER(ImStats)]),
+    "sgpu_image_stats_sharded": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_long, C.c_long, C.c_int, P, P,
+                                           C.POINTER(ImStats)]),
     "sgpu_estimators_from_stats": (C.c_int, [C.c_int, C.c_int, C.POINTER(ImStats), C.POINTER(C.c_double),
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "sgpu_compute_factors": (C.c_int, [C.c_int] * 6 + [P, P, P]),

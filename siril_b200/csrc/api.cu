@@ -79,6 +79,7 @@ void sgpu_ctx_destroy(sgpu_ctx *ctx) {
 	if (ctx->h_params) cudaFreeHost(ctx->h_params);
 	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
 	if (ctx->d_list) cudaFree(ctx->d_list);
+	if (ctx->d_arena) cudaFree(ctx->d_arena);
 	sgpu_free_stage(ctx);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -140,7 +141,7 @@ int sgpu_block_create(sgpu_ctx *ctx, const sgpu_block_desc *desc, sgpu_block **o
 	sgpu_block *b = new (std::nothrow) sgpu_block();
 	if (!b) return SGPU_ALLOC_ERROR;
 	b->ctx = ctx; b->d = *desc; b->owned = true;
-	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	if (cudaSetDevice(ctx->device) != cudaSuccess) { delete b; return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "cudaSetDevice(%d) failed", ctx->device); }
 	cudaError_t e = cudaMalloc(&b->dev, b->bytes() ? b->bytes() : 16);
 	if (e != cudaSuccess) { delete b; return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "cannot allocate %zu bytes of HBM for the frame block: %s", b->bytes(), cudaGetErrorString(e)); }
 	*out = b;
@@ -197,6 +198,8 @@ static int check_args(sgpu_ctx *ctx, const sgpu_block_desc &d, const sgpu_stack_
 	if (a->normalize < SGPU_NO_NORM || a->normalize > SGPU_MULTIPLICATIVE_SCALING) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "unknown normalization %d", a->normalize);
 	if (a->normalize != SGPU_NO_NORM && (!a->scale || !a->offset || !a->mul)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "normalization requested without coefficients");
 	if (a->is_mean && a->type_of_rejection == SGPU_GESDT && !a->critical_value) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "GESDT needs critical values");
+	if (a->is_mean && a->type_of_rejection == SGPU_GESDT && a->nb_critical > 0 && a->nb_critical < (int) floorf((float) d.nb_frames * a->sig[0]))
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "GESDT: %d critical values given, %d needed", a->nb_critical, (int) floorf((float) d.nb_frames * a->sig[0]));
 	if (!a->use_32bit_output && d.dtype == SGPU_F32) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "16-bit output needs 16-bit input");
 	return SGPU_OK;
 }
@@ -223,7 +226,7 @@ static int stage_params(sgpu_ctx *ctx, const sgpu_block_desc &d, const sgpu_stac
 	dp.weights = (const double *) put(a->is_mean ? a->weights : nullptr, cn * 8);
 	dp.shiftx = (const int *) put(a->shiftx, (size_t) d.nb_frames * 4);
 	int ncrit = 0;
-	if (a->is_mean && a->type_of_rejection == SGPU_GESDT) ncrit = (int) floor(d.nb_frames * a->sig[0]);
+	if (a->is_mean && a->type_of_rejection == SGPU_GESDT) ncrit = (int) floorf((float) d.nb_frames * a->sig[0]);	// int * float: a float product (median_and_mean.c:1479)
 	dp.crit = (const float *) put(ncrit ? a->critical_value : nullptr, (size_t) ncrit * 4);
 	if ((norm && (!dp.scale || !dp.offset || !dp.mul)) || (a->is_mean && a->weights && !dp.weights) ||
 	    (a->shiftx && !dp.shiftx) || (ncrit && !dp.crit))
@@ -301,46 +304,68 @@ int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::
 	const size_t npx = (size_t) C * H * W;
 	const size_t in_es = desc->dtype == SGPU_F32 ? 4 : 2, out_es = a->use_32bit_output ? 4 : 2;
 	const int nmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
-	// Row blocks, as the reference's own block loop (median_and_mean.c:1552): block k + 1 is on its
-	// way over PCIe (copy stream) while block k is stacked and its rows go back (context stream).
-	// output_norm rescales with the whole image's range: one block.
+	const bool renorm = a->use_32bit_output && a->output_norm;	// rescaled with the whole image's range once every block is in
+	const size_t out_bytes = (npx * out_es + 255) & ~(size_t) 255, map_bytes = (npx * 2 + 255) & ~(size_t) 255;
+	const size_t fixed = out_bytes + nmaps * map_bytes + 256;
+	// Row blocks, as the reference's own block loop (median_and_mean.c:1552; rows per block from the
+	// memory budget, stack_get_max_number_of_rows :1234): NBUF device buffers take turns, block k + 1 is
+	// on its way over PCIe (copy stream) while block k is stacked and its rows go back (context stream),
+	// so the device holds NBUF blocks and the outputs whatever the size of the sequence.
+	const size_t row_bytes = (size_t) C * W * in_es * (size_t) desc->nb_frames;	// one image row of every frame and layer
+	const size_t in_bytes = row_bytes * (size_t) H;
 	int nblk = 1;
-	if (!(a->use_32bit_output && a->output_norm)) {
-		const size_t in_bytes = npx * in_es * (size_t) desc->nb_frames;
-		if (in_bytes >= ((size_t) 256 << 20) && H >= 512) nblk = 8;
-		if (const char *e = getenv("SGPU_HOST_BLOCKS")) { const int n = atoi(e); if (n >= 1) nblk = n; }
-		if (nblk > H) nblk = H;
+	if (in_bytes >= ((size_t) 256 << 20) && H >= 512) nblk = 8;
+	{
+		size_t fr = 0, tot = 0;
+		SGPU_CUDA(ctx, cudaMemGetInfo(&fr, &tot));
+		fr += ctx->d_arena_cap;		// what the cached arena holds is ours to reuse
+		const size_t budget = fr > fixed + ((size_t) 512 << 20) ? (size_t) ((fr - fixed - ((size_t) 512 << 20)) * 0.9) : 0;
+		const int nbuf = nblk > 1 ? 3 : 1;
+		while ((size_t) nbuf * (((size_t) H + nblk - 1) / nblk + 4) * row_bytes > budget && nblk < H) nblk = nblk < 4 ? 4 : nblk * 2;
 	}
+	if (const char *e = getenv("SGPU_HOST_BLOCKS")) { const int n = atoi(e); if (n >= 1) nblk = n; }
+	if (nblk > H) nblk = H > 0 ? H : 1;
 	int rows = (H + nblk - 1) / nblk;
 	if (nblk > 1) rows = (rows + 3) & ~3;		// keeps h * W a multiple of 4 samples (TMA tile load)
-	nblk = (H + rows - 1) / rows;
+	if (rows < 1) rows = 1;
+	nblk = H > 0 ? (H + rows - 1) / rows : 1;
+	const int NBUF = nblk < 3 ? nblk : 3;
+	const size_t blk_bytes = ((size_t) rows * row_bytes + 255) & ~(size_t) 255;
+	// one cached device arena: [NBUF blocks | result | rejection maps | counters]
+	const size_t need = (size_t) NBUF * blk_bytes + fixed;
+	if (need > ctx->d_arena_cap) {
+		if (ctx->d_arena) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->d_arena); ctx->d_arena = nullptr; ctx->d_arena_cap = 0; }
+		cudaError_t e = cudaMalloc(&ctx->d_arena, need);
+		if (e != cudaSuccess) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "cannot allocate %zu bytes of HBM for %d row blocks and the outputs: %s", need, NBUF, cudaGetErrorString(e));
+		ctx->d_arena_cap = need;
+	}
+	char *d_buf = (char *) ctx->d_arena + (size_t) NBUF * blk_bytes;
+	std::vector<cudaEvent_t> up(nblk, nullptr), done(nblk, nullptr);
 	std::vector<sgpu_block *> blks(nblk, nullptr);
-	std::vector<cudaEvent_t> up(nblk, nullptr);
-	char *d_buf = nullptr;
-	const size_t out_bytes = (npx * out_es + 255) & ~(size_t) 255, map_bytes = (npx * 2 + 255) & ~(size_t) 255;
 	cudaStream_t const compute = ctx->stream;
 	auto cleanup = [&](int code) {
 		ctx->stream = compute;
 		cudaStreamSynchronize(ctx->copy_stream); cudaStreamSynchronize(compute);
-		if (d_buf) cudaFree(d_buf);
 		for (sgpu_block *b : blks) if (b) sgpu_block_destroy(b);
 		for (cudaEvent_t ev : up) if (ev) cudaEventDestroy(ev);
+		for (cudaEvent_t ev : done) if (ev) cudaEventDestroy(ev);
 		return code;
 	};
 	for (int k = 0; k < nblk; k++) {
 		sgpu_block_desc dk = *desc;
 		dk.height = (k + 1) * rows <= H ? rows : H - k * rows;
-		rv = sgpu_block_create(ctx, &dk, &blks[k]); if (rv) return cleanup(rv);
-		if (cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+		rv = sgpu_block_wrap(ctx, &dk, (char *) ctx->d_arena + (size_t) (k % NBUF) * blk_bytes, &blks[k]); if (rv) return cleanup(rv);
+		if (cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 	}
-	cudaError_t e = cudaMalloc(&d_buf, out_bytes + nmaps * map_bytes + 64);
-	if (e != cudaSuccess) return cleanup(sgpu_cuda_fail(ctx, e, "cudaMalloc(outputs)"));
 	uint64_t *d_irej = (uint64_t *) (d_buf + out_bytes + nmaps * map_bytes);
 	if (cudaMemsetAsync(d_irej, 0, 48, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	// uploads run on the copy stream when there is something to overlap with
+	// uploads run on the copy stream when there is something to overlap with; a buffer is filled
+	// again only once the stack of the block that used it has run
 	auto upload = [&](int k) -> int {
 		if (nblk > 1) ctx->stream = ctx->copy_stream;
 		int r = SGPU_OK;
+		if (k >= NBUF && cudaStreamWaitEvent(ctx->stream, done[k - NBUF], 0) != cudaSuccess) r = SGPU_GENERIC_ERROR;
 		for (int f = 0; f < desc->nb_frames && !r; f++) r = upload_one(blks[k], f, k * rows);
 		if (!r && cudaEventRecord(up[k], ctx->stream) != cudaSuccess) r = SGPU_GENERIC_ERROR;
 		ctx->stream = compute;
@@ -358,21 +383,32 @@ int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::
 		uint16_t *d_hi = nmaps == 2 ? (uint16_t *) (d_buf + out_bytes + map_bytes) + off : nullptr;
 		rv = sgpu_stack_block(ctx, blks[k], a, d_out, d_lo, d_hi, d_irej);
 		if (rv) return cleanup(rv);
-		if (nblk == 1 && a->use_32bit_output && a->output_norm) {
-			float mm[2];
-			rv = sgpu_minmax_nonzero(ctx, (const float *) d_out, npx, 1, mm); if (rv) return cleanup(rv);
-			rv = sgpu_rescale_0_1(ctx, (float *) d_out, npx, mm[0], mm[1]); if (rv) return cleanup(rv);
-		}
+		if (cudaEventRecord(done[k], compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 		for (int l = 0; l < C; l++) {
 			const size_t src = (size_t) l * h * W, dst = ((size_t) l * H + row0) * W, n = (size_t) h * W;
-			if (cudaMemcpyAsync((char *) out + dst * out_es, d_out + src * out_es, n * out_es, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+			if (!renorm && cudaMemcpyAsync((char *) out + dst * out_es, d_out + src * out_es, n * out_es, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 			if (d_lo && rej_low && cudaMemcpyAsync(rej_low + dst, d_lo + src, n * 2, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 			if (d_hi && rej_high && cudaMemcpyAsync(rej_high + dst, d_hi + src, n * 2, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 		}
 	}
+	if (renorm) {	// norm_to_0_1_range (median_and_mean.c:557-582) over the whole result, which stayed on the device.
+		// The blocks lie one after the other, [block][layer][h][W]: the scan order differs from the image's but
+		// min / max do not care; the reference skips element 0 of the IMAGE, which is element 0 of block 0
+		float mm[2];
+		rv = sgpu_minmax_nonzero(ctx, (const float *) d_buf, npx, 1, mm); if (rv) return cleanup(rv);
+		rv = sgpu_rescale_0_1(ctx, (float *) d_buf, npx, mm[0], mm[1]); if (rv) return cleanup(rv);
+		for (int k = 0; k < nblk; k++) {
+			const int h = blks[k]->d.height, row0 = k * rows;
+			const size_t off = (size_t) C * row0 * W;
+			for (int l = 0; l < C; l++) {
+				const size_t src = off + (size_t) l * h * W, dst = ((size_t) l * H + row0) * W, n = (size_t) h * W;
+				if (cudaMemcpyAsync((char *) out + dst * 4, d_buf + src * 4, n * 4, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
+			}
+		}
+	}
 	uint64_t h_irej[6] = { 0 };
 	if (cudaMemcpyAsync(h_irej, d_irej, 48, cudaMemcpyDeviceToHost, compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
-	e = cudaStreamSynchronize(compute);
+	cudaError_t e = cudaStreamSynchronize(compute);
 	if (e != cudaSuccess) return cleanup(sgpu_cuda_fail(ctx, e, "stack"));
 	if (irej) memcpy(irej, h_irej, 48);
 	return cleanup(SGPU_OK);

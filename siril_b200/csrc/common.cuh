@@ -25,6 +25,7 @@ struct sgpu_ctx {
 	void *d_params = nullptr; size_t d_params_cap = 0;
 	void *h_params = nullptr;			// pinned mirror
 	void *d_scratch = nullptr; size_t d_scratch_cap = 0;	// global-column fallback, stats temporaries
+	void *d_arena = nullptr; size_t d_arena_cap = 0;	// sgpu_stack_host / sgpu_stack_fits: row-block buffers and outputs, kept between calls
 	void *d_list = nullptr; size_t d_list_cap = 0; bool list_used = false; int last_engine = 0;		// sorted engine: pixels handed to the exact engine
 	// raw FITS reader (fitsread.cu): two pinned + two device staging chunks, recycled by events
 	void *h_stage[2] = { nullptr, nullptr }, *d_stage[2] = { nullptr, nullptr };

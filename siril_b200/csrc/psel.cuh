@@ -65,6 +65,16 @@ struct PselPlan {
 	float blo, bhi;
 };
 
+// planning arithmetic: approximate division / square root on the device (the PLACEMENT of the windows
+// is all that depends on it, never a result), the plain operators on the host
+#ifdef __CUDA_ARCH__
+#define PSEL_DIV(a, b) __fdividef((a), (b))
+#define PSEL_SQRT(x) ((x) * rsqrtf(x))
+#else
+#define PSEL_DIV(a, b) ((a) / (b))
+#define PSEL_SQRT(x) sqrtf(x)
+#endif
+
 // inverse of the standard normal distribution function for 0.02425 <= p <= 0.97575 (central
 // rational approximation of P. Acklam, |relative error| < 1.2e-9 in exact arithmetic; only the
 // PLACEMENT of the windows depends on it, never a result)
@@ -74,7 +84,7 @@ SGPU_HD inline float psel_ndtri(float p) {
 			+ 1.383577518672690e+02f) * r - 3.066479806614716e+01f) * r + 2.506628277459239e+00f) * q;
 	const float den = ((((-5.447609879822406e+01f * r + 1.615858368580409e+02f) * r - 1.556989798598866e+02f) * r
 			+ 6.680131188771972e+01f) * r - 1.328068155288572e+01f) * r + 1.f;
-	return num / den;
+	return PSEL_DIV(num, den);
 }
 
 // ---- planning (group level, after each pass) ----------------------------------------------------
@@ -89,7 +99,7 @@ SGPU_HD inline bool psel_plan_count(int n, double S1, double S2, double K, float
 	const double m = T1 * rnt, ss = T2 - T1 * m;		// sum of squares about the trimmed mean
 	if (!(ss > 0.0) || !(ss * 1e9 > T2)) return false;
 	*mean = (float) (K + m);
-	*hw = 0.45f * sqrtf((float) ss / (float) (n - 3));
+	*hw = 0.45f * PSEL_SQRT(PSEL_DIV((float) ss, (float) (n - 3)));
 	return *hw > 0.f && *hw < FLT_MAX;
 }
 
@@ -99,8 +109,9 @@ SGPU_HD inline bool psel_plan_count(int n, double S1, double S2, double K, float
 SGPU_HD inline int psel_plan_window(int n, float *meanp, float *hw, int c_neg, int c_in, bool tails, bool percentile,
 		float s0, float s1, int attempt, PselPlan *pl) {
 	const float fn = (float) n, mean = *meanp;
-	float f = (float) c_in / fn;
-	float q = ((float) c_neg + 0.5f) / fn;
+	const float rfn = PSEL_DIV(1.f, fn);
+	float f = (float) c_in * rfn;
+	float q = ((float) c_neg + 0.5f) * rfn;
 	q = q < 0.03f ? 0.03f : (q > 0.97f ? 0.97f : q);
 	if (f >= 0.80f && attempt < 2) {	// several outliers: the bulk is a fraction of the window, and the mean sits off its middle
 		*hw *= 0.25f;
@@ -108,16 +119,17 @@ SGPU_HD inline int psel_plan_window(int n, float *meanp, float *hw, int c_neg, i
 		return 1;
 	}
 	f = f < 0.05f ? 0.05f : (f > 0.95f ? 0.95f : f);
-	const float srob = *hw / psel_ndtri(0.5f + 0.5f * f);	// scale of the bulk
+	const float srob = PSEL_DIV(*hw, psel_ndtri(0.5f + 0.5f * f));	// scale of the bulk
 	const float p1 = mean - srob * psel_ndtri(q);		// where half of the samples are below
-	const float wr = fmaxf(6.f, 3.0f * sqrtf(sqrtf(fn)));	// half-width of the centre window in ranks
-	const float w = wr * srob * 2.5066283f / fn;
+	const float sq = PSEL_SQRT(fn);
+	const float wr = fmaxf(6.f, 3.0f * PSEL_SQRT(sq));	// half-width of the centre window in ranks
+	const float w = wr * srob * 2.5066283f * rfn;
 	float rlo = FLT_MAX, rhi = FLT_MAX;
 	if (tails) {
 		if (percentile) {	// thresholds median * sig (rejection_float.c:31-44), the median within w of p1
 			rlo = fabsf(p1) * s0 - 2.f * w; rhi = fabsf(p1) * s1 - 2.f * w;
 		} else {		// thresholds sig * sigma; the bulk's sigma is known to ~1.7 / sqrt(n) relative (1 sd)
-			const float mf = 1.f / (1.f + 8.f / sqrtf(fn));
+			const float mf = PSEL_DIV(sq, sq + 8.f);
 			rlo = mf * s0 * srob; rhi = mf * s1 * srob;
 		}
 		rlo = rlo > w ? rlo : w; rhi = rhi > w ? rhi : w;

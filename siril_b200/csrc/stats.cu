@@ -322,6 +322,16 @@ namespace {
 struct Sweep {
 	sgpu_ctx *ctx; const void *d; int dtype; size_t n;
 	unsigned *d_hist; void *d_part; void *h_part;
+	// row-sharded frames (one process per GPU holds rows [row0, row0 + ny) of every frame): every
+	// reduction over the plane passes through the caller's all-reduce before it is used, so each
+	// rank walks identical histograms and sums (integer counts make the medians
+	// bit-identical to the single-GPU ones)
+	sgpu_reduce_fn reduce = nullptr; void *reduce_user = nullptr;
+	int allreduce(void *buf, size_t count, int dtype_, int op) const {
+		if (!reduce) return SGPU_OK;
+		const int rv = reduce(reduce_user, buf, count, dtype_, op);
+		return rv ? sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the all-reduce callback failed (%d)", rv) : SGPU_OK;
+	}
 };
 
 // rt_algo.cc:112-138 on a finished histogram (minPrct = maxPrct = 0.5, outputs aliased).
@@ -368,6 +378,13 @@ int minmax_sel(Sweep &w, const Sel &s, float &mn, float &mx, size_t &cnt) {
 	const MMPartial *p = (const MMPartial *) w.h_part;
 	mn = FLT_MAX; mx = -FLT_MAX; cnt = 0;
 	for (int i = 0; i < NB; i++) { mn = std::min(mn, p[i].mn); mx = std::max(mx, p[i].mx); cnt += p[i].cnt; }
+	if (w.reduce) {
+		unsigned long long c = cnt;
+		int rv = w.allreduce(&mn, 1, SGPU_RED_F32, SGPU_RED_MIN); if (rv) return rv;
+		rv = w.allreduce(&mx, 1, SGPU_RED_F32, SGPU_RED_MAX); if (rv) return rv;
+		rv = w.allreduce(&c, 1, SGPU_RED_U64, SGPU_RED_SUM); if (rv) return rv;
+		cnt = (size_t) c;
+	}
 	return SGPU_OK;
 }
 
@@ -382,6 +399,7 @@ int run_window(Sweep &w, Launch launch, const unsigned *&h, size_t &below) {
 	unsigned *hh = (unsigned *) ctx->h_params;	// pinned: the read-back is a 5 us DMA, not a staged copy
 	SGPU_CUDA(ctx, cudaMemcpyAsync(hh, w.d_hist, (HWIN + 2) * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	{ int rv = w.allreduce(hh, HWIN, SGPU_RED_U32, SGPU_RED_SUM); if (rv) return rv; rv = w.allreduce(hh + HWIN, 1, SGPU_RED_U64, SGPU_RED_SUM); if (rv) return rv; }
 	unsigned long long b; memcpy(&b, hh + HWIN, sizeof b);
 	below = (size_t) b;
 	h = hh;
@@ -394,6 +412,7 @@ inline int read_full_hist(Sweep &w, const unsigned *&h) {
 	unsigned *hh = (unsigned *) ctx->h_params;
 	SGPU_CUDA(ctx, cudaMemcpyAsync(hh, w.d_hist, 65536 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	{ int rv = w.allreduce(hh, 65536, SGPU_RED_U32, SGPU_RED_SUM); if (rv) return rv; }
 	h = hh;
 	return SGPU_OK;
 }
@@ -463,6 +482,7 @@ int ikss(Sweep &w, float inv, float median, float mad, double &location, double 
 		const BwPartial *p = (const BwPartial *) w.h_part;
 		double up = 0, down = 0;
 		for (int i = 0; i < NB; i++) { up += p[i].up; down += p[i].down; }
+		{ double ud[2] = { up, down }; rv = w.allreduce(ud, 2, SGPU_RED_F64, SGPU_RED_SUM); if (rv) return rv; up = ud[0]; down = ud[1]; }
 		bw = down ? kept * (up / (down * down)) : 0.0;
 	}
 	scale = sqrt(bw) * .991;
@@ -470,7 +490,8 @@ int ikss(Sweep &w, float inv, float median, float mad, double &location, double 
 }
 
 template <typename T>
-int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu_imstats *out) {
+int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu_imstats *out,
+		sgpu_reduce_fn reduce = nullptr, void *reduce_user = nullptr, long row0 = 0, long full_ny = 0) {
 	const size_t n = (size_t) nx * ny;
 	const size_t part_bytes = NB * 64;
 	const size_t need = 65536 * sizeof(unsigned) + part_bytes + (size_t) ny * sizeof(double) + 256;
@@ -479,6 +500,9 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 		 (char *) ctx->d_scratch + 65536 * sizeof(unsigned), nullptr };
 	double *d_rows = (double *) ((char *) w.d_part + part_bytes);
 	w.h_part = (char *) ctx->h_params + 512 * 1024;	// pinned arena: [0, 256 KB) histograms, [512 KB, ...) partials and row noise
+	w.reduce = reduce; w.reduce_user = reduce_user;
+	if (!reduce) { row0 = 0; full_ny = ny; }
+	if (row0 < 0 || row0 + ny > full_ny) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "row shard [%ld, %ld) outside the frame of %ld rows", row0, row0 + ny, full_ny);
 	memset(out, 0, sizeof(*out));
 
 	// pass A
@@ -487,7 +511,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	SGPU_CUDA(ctx, cudaGetLastError());
 	SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(BasicPartial), cudaMemcpyDeviceToHost, ctx->stream));
 	// pass B (bgnoise) queued behind it
-	if (nx >= 3) {
+	if (nx >= 3 && ny > 0) {
 		const size_t shm = (size_t) nx * 8 + 16;
 		if (shm + 4096 > ctx->smem_optin) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "rows of %ld pixels do not fit in shared memory", nx);	// + the kernel's static arrays
 		if (shm + 4096 > 48 * 1024) SGPU_CUDA(ctx, cudaFuncSetAttribute(noise_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) shm));
@@ -497,7 +521,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	}
 	std::vector<double> rows_big;
 	const double *rows = nullptr;
-	const long nrows = nx >= 3 ? ny : 0;
+	long nrows = nx >= 3 ? ny : 0;
 	if (nrows) {
 		double *dst = (double *) ((char *) ctx->h_params + 576 * 1024);
 		if ((size_t) nrows * sizeof(double) > ctx->d_params_cap - 576 * 1024) { rows_big.resize(nrows); dst = rows_big.data(); }
@@ -505,6 +529,13 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 		rows = dst;
 	}
 	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	std::vector<double> rows_all;
+	if (reduce && nx >= 3) {	// every rank's row values, in image order: a sum over zero-padded arrays is an all-gather
+		rows_all.assign((size_t) full_ny, 0.0);
+		for (long i = 0; i < nrows; i++) rows_all[(size_t) (row0 + i)] = rows[i];
+		rv = w.allreduce(rows_all.data(), (size_t) full_ny, SGPU_RED_F64, SGPU_RED_SUM); if (rv) return rv;
+		rows = rows_all.data(); nrows = full_ny;
+	}
 
 	const BasicPartial *bp = (const BasicPartial *) w.h_part;
 	double sum = 0, sum2 = 0; unsigned long long ngood = 0, isum = 0, isum2 = 0;
@@ -512,6 +543,16 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	for (int i = 0; i < NB; i++) {
 		sum += bp[i].sum; sum2 += bp[i].sum2; ngood += bp[i].ngood; isum += bp[i].isum; isum2 += bp[i].isum2;
 		mn = std::min(mn, bp[i].mn); mx = std::max(mx, bp[i].mx); nzmn = std::min(nzmn, bp[i].nzmn); nzmx = std::max(nzmx, bp[i].nzmx);
+	}
+	unsigned long long total = n;
+	if (reduce) {
+		double sd[2] = { sum, sum2 }; unsigned long long cu[4] = { ngood, isum, isum2, total }; float lo[2] = { mn, nzmn }, hi[2] = { mx, nzmx };
+		rv = w.allreduce(sd, 2, SGPU_RED_F64, SGPU_RED_SUM); if (rv) return rv;
+		rv = w.allreduce(cu, 4, SGPU_RED_U64, SGPU_RED_SUM); if (rv) return rv;
+		rv = w.allreduce(lo, 2, SGPU_RED_F32, SGPU_RED_MIN); if (rv) return rv;
+		rv = w.allreduce(hi, 2, SGPU_RED_F32, SGPU_RED_MAX); if (rv) return rv;
+		sum = sd[0]; sum2 = sd[1]; ngood = cu[0]; isum = cu[1]; isum2 = cu[2]; total = cu[3];
+		mn = lo[0]; nzmn = lo[1]; mx = hi[0]; nzmx = hi[1];
 	}
 	if (sizeof(T) == 2) { sum = (double) isum; sum2 = (double) isum2; }
 	const double normValue = sizeof(T) == 4 ? 1.0 : 65535.0;
@@ -527,7 +568,7 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 		else if (v.size() > 1) { std::sort(v.begin(), v.end()); bgnoise = (v[(v.size() - 1) / 2] + v[v.size() / 2]) / 2.; }
 		bgnoise *= .70710678;
 	}
-	out->total = (double) n; out->ngoodpix = (double) ngood; out->mean = mean; out->sigma = sigma;
+	out->total = (double) total; out->ngoodpix = (double) ngood; out->mean = mean; out->sigma = sigma;
 	out->min = mn; out->max = mx; out->normValue = normValue; out->bgnoise = bgnoise;
 	if (ngood == 0) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "image has no non-null pixel");	// statistics_float.c:399-403
 	if (lite == SGPU_STATS_NOISE_ONLY) return SGPU_OK;	// STATS_BASIC | STATS_BGNOISE: what the noise estimate of a stacked result needs
@@ -585,8 +626,22 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 
 }  // namespace
 
+static int image_stats_any(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny, int lite, sgpu_imstats *out,
+		sgpu_reduce_fn reduce, void *user, long row0, long full_ny);
+
 extern "C" int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny,
 		int lite, sgpu_imstats *out) {
+	return image_stats_any(ctx, plane, on_device, dtype, nx, ny, lite, out, nullptr, nullptr, 0, ny);
+}
+
+extern "C" int sgpu_image_stats_sharded(sgpu_ctx *ctx, const void *shard, int on_device, int dtype, long nx, long ny,
+		long row0, long full_ny, int lite, sgpu_reduce_fn reduce, void *user, sgpu_imstats *out) {
+	if (!reduce) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "sgpu_image_stats_sharded needs an all-reduce callback");
+	return image_stats_any(ctx, shard, on_device, dtype, nx, ny, lite, out, reduce, user, row0, full_ny);
+}
+
+static int image_stats_any(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny, int lite, sgpu_imstats *out,
+		sgpu_reduce_fn reduce, void *user, long row0, long full_ny) {
 	if (!ctx || !plane || !out || nx < 1 || ny < 1) return SGPU_GENERIC_ERROR;
 	if (dtype != SGPU_F32 && dtype != SGPU_U16) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "bad dtype");
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -599,8 +654,8 @@ extern "C" int sgpu_image_stats(sgpu_ctx *ctx, const void *plane, int on_device,
 		if (e != cudaSuccess) { cudaFree(staged); return sgpu_cuda_fail(ctx, e, "upload plane"); }
 		d = staged;
 	}
-	int rv = dtype == SGPU_F32 ? image_stats_impl<float>(ctx, (const float *) d, nx, ny, lite, out)
-				   : image_stats_impl<uint16_t>(ctx, (const uint16_t *) d, nx, ny, lite, out);
+	int rv = dtype == SGPU_F32 ? image_stats_impl<float>(ctx, (const float *) d, nx, ny, lite, out, reduce, user, row0, full_ny)
+				   : image_stats_impl<uint16_t>(ctx, (const uint16_t *) d, nx, ny, lite, out, reduce, user, row0, full_ny);
 	if (staged) { cudaStreamSynchronize(ctx->stream); cudaFree(staged); }
 	return rv;
 }

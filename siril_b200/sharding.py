@@ -2,7 +2,10 @@
 tests).  The stacking path shards by image rows — the reference's own block unit
 (`struct _image_block`, src/stacking/stacking.h:167-169; OpenMP loop median_and_mean.c:1552) — so
 no collective is needed while stacking; what is exchanged is
-  * per-frame normalization estimators, computed frame-parallel (frames f = rank mod world),
+  * the reductions behind the per-frame normalization statistics (counts, sums, minima / maxima,
+    integer histograms, per-row noise values): every rank holds only its rows of a frame and the
+    estimators are whole-frame quantities, so each reduction is all-reduced before it is used
+    (make_reducer + sgpu_image_stats_sharded; stacking.compute_estimators(..., shard=...)),
   * the output rows (and rejection maps), gathered to rank 0,
   * the rejection counters irej[3][2] (median_and_mean.c:1748-1757) and, for output_norm, the
     min/max of the non-zero result pixels (norm_to_0_1_range, :557-582)."""
@@ -17,6 +20,31 @@ def row_shard(height, rank, world):
 def my_frames(nb_frames, rank, world):
     """frames whose statistics this rank computes (whole frames, frame-parallel)"""
     return list(range(rank, nb_frames, world))
+
+
+def make_reducer(dist, device=None):
+    """sgpu_reduce_fn over torch.distributed: an in-place all-reduce of a HOST buffer (NCCL: through
+    a device copy; gloo: in place).  Unsigned counts travel as int64.  Keep the returned object alive
+    for as long as the C side may call it."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    ctypes_of = {0: C.c_float, 1: C.c_double, 2: C.c_uint32, 3: C.c_uint64}
+    ops = {0: dist.ReduceOp.SUM, 1: dist.ReduceOp.MIN, 2: dist.ReduceOp.MAX}
+
+    def cb(_user, buf, count, dtype, op):
+        try:
+            arr = np.ctypeslib.as_array(C.cast(buf, C.POINTER(ctypes_of[dtype])), shape=(count,))
+            t = torch.from_numpy(arr.astype(np.int64) if dtype >= 2 else arr.copy())
+            if device is not None:
+                t = t.to(device)
+            dist.all_reduce(t, op=ops[op])
+            arr[:] = t.cpu().numpy().astype(arr.dtype)
+            return 0
+        except Exception as e:   # noqa: BLE001 — nothing may propagate through the C frames
+            print(f"sgpu all-reduce callback failed: {e!r}", flush=True)
+            return 1
+    return _lib.REDUCE_FN(cb)
 
 
 def merge_estimators(dist, arrays, mine, device=None):

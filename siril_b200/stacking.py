@@ -26,7 +26,7 @@ def gesdt_critical_values(nb_frames, sig0, sig1):
     then float arithmetic.  The reference uses GSL's quantile; this harness uses scipy's."""
     from scipy.stats import t as tdist
     f32 = np.float32
-    n_out = int(np.floor(nb_frames * float(f32(sig0))))
+    n_out = int(np.floor(f32(nb_frames) * f32(sig0)))     # int * float is a FLOAT product in the reference (median_and_mean.c:1479)
     out = np.empty(max(n_out, 0), dtype=np.float32)
     size = nb_frames
     for j in range(n_out):
@@ -144,6 +144,7 @@ def _fill_cargs(args, n, c, is_mean, keep):
         if args.critical_value is None:   # stack_mean_or_median computes it itself (:1479-1486)
             args.critical_value = gesdt_critical_values(n, args.sig[0], args.sig[1])
         a.critical_value = arr(args.critical_value, np.float32, len(args.critical_value))
+        a.nb_critical = len(args.critical_value)
     a.normalize = args.normalize
     if args.normalize != NO_NORM:
         a.scale = arr(args.coeff.scale, np.float64, n * c)
@@ -377,14 +378,47 @@ def result_bgnoise(args: StackingArgs):
     return [image_stats(ctx, data[layer], lite=2).bgnoise for layer in range(data.shape[0])]
 
 
-def compute_estimators(args: StackingArgs, frame_indices=None):
+def image_stats_sharded(ctx, shard, row0, full_height, reducer, lite=False):
+    """statistics of a frame plane of which this rank holds rows [row0, row0 + shard rows): every
+    rank calls it for the same plane and gets the WHOLE frame's statistics (sgpu_image_stats_sharded)"""
+    L = _lib.lib()
+    st = _lib.ImStats()
+    if _is_torch_cuda(shard):
+        import torch
+        shard = shard.contiguous()
+        ny, nx = shard.shape
+        dt = DATA_FLOAT if shard.dtype == torch.float32 else DATA_USHORT
+        ptr, on_dev = C.c_void_p(shard.data_ptr()), 1
+    else:
+        shard = np.ascontiguousarray(shard)
+        ny, nx = shard.shape
+        dt = DATA_FLOAT if shard.dtype == np.float32 else DATA_USHORT
+        ptr, on_dev = shard.ctypes.data_as(C.c_void_p), 0
+    ctx.check(L.sgpu_image_stats_sharded(ctx.h, ptr, on_dev, dt, nx, ny, row0, full_height, int(lite),
+                                         C.cast(reducer, C.c_void_p), None, C.byref(st)))
+    return st
+
+
+def compute_estimators(args: StackingArgs, frame_indices=None, shard=None):
     """_compute_estimators_for_image over the given frames (all by default): returns
-    (offset, mul, scale, bgnoise) arrays [C][N] holding ESTIMATORS (normalization.c:98-141)."""
+    (offset, mul, scale, bgnoise) arrays [C][N] holding ESTIMATORS (normalization.c:98-141).
+
+    shard = (reducer, row0, full_height): args.frames holds only rows [row0, row0 + h) of every frame
+    (one process per GPU); every rank then walks every plane, one after the other and in the same
+    order, and the reductions are all-reduced (sharding.make_reducer)."""
     L = _lib.lib()
     ctx = _context(args)
     n, c, h, w, dt = _shape_dtype(args.frames)
     off = np.zeros((c, n)); mul = np.ones((c, n)); sc = np.ones((c, n)); bg = np.zeros((c, n))
     todo = [(f, layer) for f in (range(n) if frame_indices is None else frame_indices) for layer in range(c)]
+    if shard is not None:
+        reducer, row0, full_h = shard
+        for f, layer in todo:
+            st = image_stats_sharded(ctx, args.frames[f][layer], row0, full_h, reducer, args.lite_norm)
+            o, m, s = C.c_double(), C.c_double(), C.c_double()
+            L.sgpu_estimators_from_stats(args.normalize, int(args.lite_norm), C.byref(st), C.byref(o), C.byref(m), C.byref(s))
+            off[layer, f], mul[layer, f], sc[layer, f], bg[layer, f] = o.value, m.value, s.value, st.bgnoise
+        return off, mul, sc, bg
 
     def one(wctx, f, layer):
         st = image_stats(wctx, args.frames[f][layer], args.lite_norm)

@@ -42,8 +42,28 @@ def _worker(rank, world, port, q):
         full_loc = np.array([[orc.image_stats(fr[f, c])["location"] for f in range(N)] for c in range(C)])
         assert np.array_equal(loc_all, full_loc)
         assert np.all(sc_all > 0)
-        # shard, stack, gather
+        # the all-reduce callback behind the statistics of row-sharded frames (sgpu_reduce_fn): every
+        # element type and operator, and the property the sharded medians rest on — integer
+        # histograms of the shards, summed, are the histogram of the frame
+        import ctypes as ct
         r0, r1 = sh.row_shard(H, rank, world)
+        red = sh.make_reducer(dist)
+        fn = ct.cast(red, ct.CFUNCTYPE(ct.c_int, ct.c_void_p, ct.c_void_p, ct.c_size_t, ct.c_int, ct.c_int))
+        plane = fr[3, 1]
+        edges = np.linspace(plane.min(), plane.max() + 1e-6, 65)
+        hist = np.histogram(plane[r0:r1], bins=edges)[0].astype(np.uint32)
+        assert fn(None, hist.ctypes.data_as(ct.c_void_p), hist.size, 2, 0) == 0
+        assert np.array_equal(hist, np.histogram(plane, bins=edges)[0].astype(np.uint32))
+        cnt = np.array([np.count_nonzero(plane[r0:r1]), (r1 - r0) * W], dtype=np.uint64)
+        assert fn(None, cnt.ctypes.data_as(ct.c_void_p), 2, 3, 0) == 0 and cnt.tolist() == [np.count_nonzero(plane), H * W]
+        lo = np.array([plane[r0:r1].min()], dtype=np.float32); hi = np.array([plane[r0:r1].max()], dtype=np.float32)
+        assert fn(None, lo.ctypes.data_as(ct.c_void_p), 1, 0, 1) == 0 and fn(None, hi.ctypes.data_as(ct.c_void_p), 1, 0, 2) == 0
+        assert lo[0] == plane.min() and hi[0] == plane.max()
+        sd = np.array([plane[r0:r1].astype(np.float64).sum()])
+        assert fn(None, sd.ctypes.data_as(ct.c_void_p), 1, 1, 0) == 0 and abs(sd[0] - plane.astype(np.float64).sum()) <= 1e-12 * abs(sd[0])
+        rows = np.zeros(H); rows[r0:r1] = np.arange(r0, r1) + 1.0       # the zero-padded sum that gathers per-row values
+        assert fn(None, rows.ctypes.data_as(ct.c_void_p), H, 1, 0) == 0 and np.array_equal(rows, np.arange(H) + 1.0)
+        # shard, stack, gather: every rank stacks ONLY its rows
         kw = dict(rejection=O.SIGMA, sig=(3.0, 3.0), create_rejmaps=True)
         part = orc.stack(np.ascontiguousarray(fr[:, :, r0:r1, :]), **kw)
         out = sh.gather_rows(dist, torch.from_numpy(part["out"]))
@@ -58,7 +78,8 @@ def _worker(rank, world, port, q):
             assert out is None
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
-        q.put((rank, repr(e)))
+        import traceback
+        q.put((rank, repr(e) + traceback.format_exc()[-600:]))
     finally:
         dist.destroy_process_group()
 
