@@ -77,9 +77,9 @@ const char *sgpu_last_error(const sgpu_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 uint64_t sgpu_launch_count(const sgpu_ctx *ctx);
 /* number of pixels the last sgpu_stack_block / sgpu_stack_host call of this context handed from the
- * register / sorted engine to the exact engine (diagnostic; synchronizes the context stream) */
+ * selection / lane-sort / sorted engine to the exact engine (diagnostic; synchronizes the context stream) */
 uint64_t sgpu_handover_count(sgpu_ctx *ctx);
-/* engine the last stack call of this context ran on: 1 exact, 2 sorted, 3 register, 4 thread-sort, 5 lane-sort, 6 selection */
+/* engine the last stack call of this context ran on: 1 exact, 2 sorted, 5 lane-sort, 6 selection */
 int sgpu_last_engine(const sgpu_ctx *ctx);
 /* sgpu_image_stats: medians of this context that fell outside the shared-memory histogram window and
  * were recomputed on the full 65536-bin histogram (diagnostic; results are identical either way) */
@@ -160,7 +160,7 @@ typedef struct {
 	int create_rejmaps;		/* args->create_rejmaps */
 	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
 	int nb_critical;		/* entries critical_value holds; 0: not stated (trusted to be (int) floor((float) nb_frames * sig[0])) */
-	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 3: force the register engine; 4: force the thread-sort engine; 5: force the lane-sort engine; 6: force the selection engine */
+	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 5: force the lane-sort engine; 6: force the selection engine */
 } sgpu_stack_args;
 
 /* All outputs are DEVICE pointers: d_out [nb_layers][height][width] float or uint16_t,

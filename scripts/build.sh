@@ -2,7 +2,7 @@
 # builds libsgpu.so and says so only when the library is newer than every source
 set -o pipefail
 cd "$(dirname "$0")/../siril_b200/csrc" || exit 1
-make -j8 > build/make.log 2>&1; rc=$?
+mkdir -p build; make -j8 > build/make.log 2>&1; rc=$?
 grep -E "error|Error|Stop" build/make.log | head -20
 if [ $rc -ne 0 ]; then echo "BUILD FAILED (rc=$rc)"; exit $rc; fi
 newest=$(ls -t *.cu *.cuh ../../include/sgpu.h | head -1)

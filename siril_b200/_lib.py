@@ -150,8 +150,8 @@ class Context:
 
     @property
     def last_engine(self):
-        return {1: "stack_exact_kernel", 2: "stack_sorted_kernel", 3: "stack_reg_kernel",
-                4: "stack_tsort_kernel", 5: "stack_lsort_kernel", 6: "stack_psel_kernel"}.get(int(self.L.sgpu_last_engine(self.h)), "none")
+        return {1: "stack_exact_kernel", 2: "stack_sorted_kernel",
+                5: "stack_lsort_kernel", 6: "stack_psel_kernel"}.get(int(self.L.sgpu_last_engine(self.h)), "none")
 
     def close(self):
         if getattr(self, "h", None):

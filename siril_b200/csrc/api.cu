@@ -247,16 +247,15 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
 	StackDevParams dp;
 	rv = stage_params(ctx, blk->d, a, dp); if (rv) return rv;
-	// engine: 0 automatic, 1 exact thread-per-pixel, 2 sorted or fail, 3 register or fail,
-	// 4 thread-sort or fail, 5 lane-sort or fail, 6 selection or fail
-	if (a->engine == 3 && !sgpu_reg_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the register engine does not cover this configuration");
+	// engine: 0 automatic, 1 exact thread-per-pixel, 2 sorted or fail, 5 lane-sort or fail, 6 selection or fail
+	// (3 and 4 were round 1's register and thread-sort engines: gone, the numbers stay reserved)
+	if (a->engine == 3 || a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "engine %d does not exist any more", a->engine);
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
 	ctx->list_used = false;
 	sgpu_stack_args forced;
 	if (a->engine == 0) if (const char *e = getenv("SGPU_ENGINE")) {	// tuning aid: force an engine from the environment
 		forced = *a; forced.engine = atoi(e);
-		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 3 && sgpu_reg_supports(blk->d, a)) ||
-		    (forced.engine == 4 && sgpu_tsort_supports(blk->d, a)) || (forced.engine == 5 && sgpu_lsort_supports(blk->d, a)) ||
+		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 5 && sgpu_lsort_supports(blk->d, a)) ||
 		    (forced.engine == 6 && sgpu_psel_supports(blk->d, a)) || forced.engine == 1) a = &forced;
 	}
 	// automatic (by measurement on B200, profiles/): the selection engine for what it serves (no /
@@ -270,11 +269,6 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	if ((a->engine == 0 || a->engine == 5) && sgpu_lsort_supports(blk->d, a))
 		return ctx->last_engine = 5, sgpu_launch_lsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 5) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the lane-sort engine does not cover this configuration");
-	if (a->engine == 3 && sgpu_reg_supports(blk->d, a))
-		return ctx->last_engine = 3, sgpu_launch_reg(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
-	if (a->engine == 4 && sgpu_tsort_supports(blk->d, a))
-		return ctx->last_engine = 4, sgpu_launch_tsort(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
-	if (a->engine == 4) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the thread-sort engine does not cover this configuration");
 	if (a->engine != 1 && sgpu_sorted_supports(blk->d, a))
 		return ctx->last_engine = 2, sgpu_launch_sorted(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	ctx->last_engine = 1;

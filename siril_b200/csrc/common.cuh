@@ -59,17 +59,11 @@ struct StackDevParams {
 };
 
 // engines
-bool sgpu_reg_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
-int sgpu_launch_reg(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
-		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 bool sgpu_psel_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 bool sgpu_lsort_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
-		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
-bool sgpu_tsort_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
-int sgpu_launch_tsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
 		void *d_out, uint16_t *d_rej_low, uint16_t *d_rej_high, uint64_t *d_irej);
 bool sgpu_sorted_supports(const sgpu_block_desc &d, const sgpu_stack_args *a);
 int sgpu_launch_sorted(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, const StackDevParams &dp,
