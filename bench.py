@@ -328,17 +328,19 @@ def run_ours(args, wl):
 
     def gather():
         """output rows and rejection maps of every rank into the image on rank 0; counters summed"""
-        parts = [out] + ([rlo, rhi] if maps else [])
+        # (torch's NCCL binding has no 16-bit integer type: the maps travel as byte views of the same memory)
+        i16 = lambda t: t.view(torch.uint8) if t.dtype == torch.uint16 else t    # noqa: E731
+        parts = [i16(t) for t in [out] + ([rlo, rhi] if maps else [])]
         ops = []
         if rank == 0:
-            for t_full, t_mine in zip(full, parts):
+            for t_full, t_mine in zip([i16(t) for t in full], parts):
                 t_full[:, r0:r1, :].copy_(t_mine)
             recv = []
             for g in range(1, world):
                 a, b = bounds[g]
-                for t_full in full:
+                for t_full in [i16(t) for t in full]:
                     view = t_full[:, a:b, :]        # mono: the rows of a rank are one contiguous piece of the image
-                    buf = view if view.is_contiguous() else torch.empty((c, b - a, w), dtype=t_full.dtype, device=dev)
+                    buf = view if view.is_contiguous() else torch.empty(view.shape, dtype=t_full.dtype, device=dev)
                     if buf is not view:
                         recv.append((view, buf))
                     ops.append(dist.P2POp(dist.irecv, buf, g))

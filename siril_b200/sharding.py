@@ -68,6 +68,9 @@ def gather_rows(dist, shard, dst=0):
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return shard
     world, rank = dist.get_world_size(), dist.get_rank()
+    u16 = shard.dtype == torch.uint16      # no 16-bit integer type in torch's NCCL binding: sent as byte views
+    if u16:
+        shard = shard.contiguous().view(torch.uint8)
     rows = torch.tensor([shard.shape[1]], dtype=torch.int64, device=shard.device)
     all_rows = [torch.zeros_like(rows) for _ in range(world)]
     dist.all_gather(all_rows, rows)
@@ -79,7 +82,10 @@ def gather_rows(dist, shard, dst=0):
         send = torch.cat([send, pad], dim=1)
     parts = [torch.empty_like(send) for _ in range(world)] if rank == dst else None
     dist.gather(send, parts, dst=dst)
-    return torch.cat([p[:, :c, :] for p, c in zip(parts, counts)], dim=1) if rank == dst else None
+    if rank != dst:
+        return None
+    full = torch.cat([p[:, :c, :] for p, c in zip(parts, counts)], dim=1)
+    return full.view(torch.uint16) if u16 else full
 
 
 def reduce_irej(dist, irej):

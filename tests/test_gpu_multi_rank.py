@@ -51,7 +51,7 @@ def _worker(rank, world, port, q, dtype_name, normalize, rejection, sig):
                                normalize=normalize, create_rejmaps=True)
         red = sh.make_reducer(dist, dev)
         off, mul, sc, bg = compute_estimators(args, shard=(red, r0, H))
-        finalize_factors(args, off, mul, sc)
+        finalize_factors(args, off.copy(), mul.copy(), sc.copy())      # (works in place)
         assert args.method(args) == 0, getattr(args, "error", "")
         out = sh.gather_rows(dist, args.result.data)
         lo = sh.gather_rows(dist, args.result.rejmap_low)
@@ -105,7 +105,7 @@ def test_row_sharded_normalization_and_stack(orc, dtype, normalize, rejection, s
         assert np.array_equal(a, b), (name, np.abs(a - b).max())
     assert np.allclose(got["sc"], sc, rtol=1e-12, atol=0), np.abs(got["sc"] / sc - 1).max()
     assert np.allclose(got["bg"], bg, rtol=1e-12, atol=0), np.abs(got["bg"] / bg - 1).max()
-    finalize_factors(args, off, mul, sc)
+    finalize_factors(args, off.copy(), mul.copy(), sc.copy())
     for a, b in zip(got["coeff"], (args.coeff.offset, args.coeff.mul, args.coeff.scale)):
         assert np.allclose(a, b, rtol=1e-12, atol=1e-300)
     coeff = (args.coeff.offset.copy(), args.coeff.mul.copy(), args.coeff.scale.copy())
