@@ -264,3 +264,20 @@ def test_deep_stacks(orc, case):
     else:
         kw.update(rejection=algo, sig=SIGS[algo], create_rejmaps=True)
     compare(run_gpu(fr, **dict(kw)), orc.stack(fr, **kw), str(case))
+
+
+@pytest.mark.parametrize("N,s0", [(20, 0.35), (10, 0.7), (40, 0.35), (10, 0.9)])
+def test_gesdt_outlier_budget_is_a_float_product(orc, N, s0):
+    """median_and_mean.c:1479: the critical-value table has (int) floor(nb_frames * sig[0]) entries with the
+    product taken in FLOAT — one more than the double product for these depths; a shorter table is refused"""
+    import ctypes as C
+    import siril_b200 as sb
+    rng = np.random.default_rng(N)
+    fr = synth(rng, N, 1, 8, 40, np.float32, zeros=0.0, hot=0.05)
+    kw = dict(rejection=O.GESDT, sig=(s0, 0.05), create_rejmaps=True)
+    crit = O.gesdt_critical_values(N, s0, 0.05)
+    assert len(crit) == int(np.floor(np.float32(N) * np.float32(s0)))
+    compare(run_gpu(fr, **dict(kw)), orc.stack(fr, crit=crit, **kw), f"gesdt N={N} sig0={s0}")
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=to_dev(fr), type_of_rejection=O.GESDT, sig=(s0, 0.05),
+                           critical_value=crit[:-1], engine=ENGINE)
+    assert sb.main_stack(args) == sb.ST_GENERIC_ERROR and "critical values" in args.error
