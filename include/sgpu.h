@@ -88,6 +88,15 @@ uint64_t sgpu_stats_window_misses(const sgpu_ctx *ctx);
  * (median_and_mean.c:1563); return non-zero from the callback to get SGPU_CANCEL */
 int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*should_cancel)(void *), void *user);
 
+/* device memory as the runtime sees it (the glue sizes its row blocks from it, as the reference sizes
+ * its own from get_max_memory_in_MB(), median_and_mean.c:1234) */
+int sgpu_mem_info(sgpu_ctx *ctx, size_t *free_bytes, size_t *total_bytes);
+/* zeroed device memory for the outputs of sgpu_stack_block, and an asynchronous device -> host copy on
+ * the context stream (sgpu_ctx_synchronize completes it) */
+int sgpu_device_alloc(sgpu_ctx *ctx, size_t bytes, void **dev_ptr);
+void sgpu_device_free(sgpu_ctx *ctx, void *dev_ptr);
+int sgpu_download(sgpu_ctx *ctx, void *host_dst, const void *dev_src, size_t bytes);
+
 /* pinned host memory for the upload / download legs */
 int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr);
 void sgpu_host_free(sgpu_ctx *ctx, void *ptr);

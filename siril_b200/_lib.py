@@ -67,6 +67,10 @@ SIGNATURES = {
     "sgpu_sum_convert": (C.c_int, [P, P, C.c_int, C.c_size_t, C.c_double, C.c_int, P]),
     "sgpu_stats_window_misses": (C.c_uint64, [P]),
     "sgpu_ctx_set_cancel_callback": (C.c_int, [P, P, P]),
+    "sgpu_mem_info": (C.c_int, [P, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "sgpu_device_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
+    "sgpu_device_free": (None, [P, P]),
+    "sgpu_download": (C.c_int, [P, P, P, C.c_size_t]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_host_free": (None, [P, P]),
     "sgpu_block_create": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P)]),

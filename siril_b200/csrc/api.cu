@@ -117,6 +117,31 @@ int sgpu_ctx_set_cancel_callback(sgpu_ctx *ctx, int (*cb)(void *), void *user) {
 	return SGPU_OK;
 }
 
+int sgpu_mem_info(sgpu_ctx *ctx, size_t *free_bytes, size_t *total_bytes) {
+	if (!ctx || !free_bytes || !total_bytes) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	SGPU_CUDA(ctx, cudaMemGetInfo(free_bytes, total_bytes));
+	return SGPU_OK;
+}
+
+int sgpu_device_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr) {
+	if (!ctx || !ptr) return SGPU_GENERIC_ERROR;
+	*ptr = nullptr;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaError_t e = cudaMalloc(ptr, bytes ? bytes : 16);
+	if (e != cudaSuccess) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+	e = cudaMemsetAsync(*ptr, 0, bytes ? bytes : 16, ctx->stream);
+	if (e != cudaSuccess) { cudaFree(*ptr); *ptr = nullptr; return sgpu_cuda_fail(ctx, e, "cudaMemsetAsync"); }
+	return SGPU_OK;
+}
+void sgpu_device_free(sgpu_ctx *ctx, void *ptr) { if (ptr) { if (ctx) cudaStreamSynchronize(ctx->stream); cudaFree(ptr); } }
+
+int sgpu_download(sgpu_ctx *ctx, void *host_dst, const void *dev_src, size_t bytes) {
+	if (!ctx || !host_dst || !dev_src) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	return SGPU_OK;
+}
+
 int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr) {
 	if (!ctx || !ptr) return SGPU_GENERIC_ERROR;
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
