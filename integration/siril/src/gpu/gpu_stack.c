@@ -194,6 +194,10 @@ int gpu_stack_mean_or_median(struct stacking_args *args, gboolean is_mean) {
 	size_t budget = free_b > out_b ? (size_t) ((free_b - out_b) * 0.85) : 0;
 	long rows = budget / row_b;
 	if (rows < 1) { siril_log_error(_("GPU stacking: not enough device memory for one image row of the sequence\n")); retval = ST_ALLOC_ERROR; goto free_and_close; }
+	{	/* SIRIL_GPU_MAX_ROWS: caps the block height (the tests use it to force several blocks) */
+		const char *cap = getenv("SIRIL_GPU_MAX_ROWS");
+		if (cap && atol(cap) > 0 && atol(cap) < rows) rows = atol(cap);
+	}
 	if (rows > naxes[1]) rows = naxes[1];
 	if (rows < naxes[1]) rows = rows >= 4 ? rows & ~3L : rows;	/* keeps block planes 16-byte multiples (TMA tile load) */
 	const long nblocks = (naxes[1] + rows - 1) / rows;

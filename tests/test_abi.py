@@ -84,3 +84,20 @@ def test_factors_and_weights_match_oracle(orc):
         w = np.zeros((Cn, N))
         assert L.sgpu_noise_weights(Cn, N, s.ctypes.data_as(C.c_void_p), bg.ctypes.data_as(C.c_void_p), w.ctypes.data_as(C.c_void_p)) == 0
         assert np.array_equal(w, orc.noise_weights(s, bg))
+
+
+def test_siril_glue_builds_against_the_reference_header_and_keeps_its_symbols():
+    """integration/siril/src/gpu/gpu_stack.c compiles against the reference's stacking.h; the harness
+    library carries the reference's own symbol names around it (no compute without a GPU)"""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    so = os.path.join(root, "integration", "_build", "libgpu_stack_harness.so")
+    if os.path.isdir("/root/reference"):
+        subprocess.check_call([sys.executable, os.path.join(root, "integration", "build_harness.py")], stdout=subprocess.DEVNULL)
+    elif not os.path.exists(so):
+        pytest.skip("neither the reference's header nor a prebuilt harness library here")
+    H = C.CDLL(so)
+    for name in ("stack_mean_with_rejection", "stack_median", "do_normalization", "gpu_stack_mean_or_median",
+                 "gpu_do_normalization", "harness_stack"):
+        assert hasattr(H, name), name
