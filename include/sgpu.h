@@ -203,6 +203,19 @@ int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, cons
 int sgpu_minmax_nonzero(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]);
 int sgpu_rescale_0_1(sgpu_ctx *ctx, float *d_img, size_t n, float mini, float maxi);
 
+/* sgpu_minmax_nonzero for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same inputs, outputs and results as sgpu_minmax_nonzero; the call allocates
+ * nothing (no cudaMalloc / cudaFree, no host allocation): its per-chunk partials live in a file-scope
+ * static device array of SGPU_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * Limit: n <= SGPU_STATIC_MAX_PIXELS (one 8-byte partial per 65536 pixels, one slot for the result);
+ * beyond it the call fails with SGPU_ALLOC_ERROR and a message in sgpu_last_error.  All calls (of all
+ * contexts on a device) share the array: calls that overlap on the GPU race — serialize them. */
+#define SGPU_STATIC_SCRATCH_BYTES 65536
+#define SGPU_STATIC_MAX_PIXELS ((SGPU_STATIC_SCRATCH_BYTES / 8 - 1) * (size_t) 65536)	/* 536 805 376 */
+#define SGPU_STATIC_MAX_DEVICES 64
+int sgpu_minmax_nonzero_static(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]);
+
 /* ---- sum / max / min stackers (replace sum_stacking_image_hook + _finalize_hook, sum.c:107-372,
  * and minmax_stacking_image_hook, stackminmax.c:103-184) ------------------------------------- */
 #define SGPU_SIMPLE_SUM 0	/* stack_summing_generic (sum.c:418) */

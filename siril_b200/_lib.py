@@ -86,6 +86,7 @@ SIGNATURES = {
     "sgpu_stack_host": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P), P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_stack_fits": (C.c_int, [P, C.c_int, C.POINTER(C.c_char_p), P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
+    "sgpu_minmax_nonzero_static": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_rescale_0_1": (C.c_int, [P, P, C.c_size_t, C.c_float, C.c_float]),
     "sgpu_image_stats": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_int, C.POINTER(ImStats)]),
     "sgpu_image_stats_sharded": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_long, C.c_long, C.c_int, P, P,

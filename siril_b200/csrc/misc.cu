@@ -1,6 +1,8 @@
 // misc.cu — output renormalization (norm_to_0_1_range, median_and_mean.c:557-582) and the
 // device-side synthetic frame generator used by bench.py / tests.
 #include <cfloat>
+#include <cstdio>
+#include <mutex>
 #include "common.cuh"
 
 namespace sgpu {
@@ -25,6 +27,74 @@ __global__ void minmax_nonzero_kernel(const float *img, size_t n, size_t first, 
 		for (int w = 1; w < (int) (blockDim.x >> 5); w++) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
 		partial[blockIdx.x] = make_float2(mn, mx);
 	}
+}
+
+// ---- the same reduction with NO allocation: its scratch is this file-scope array (64 KiB held by every
+// GPU that loads the library, until exit).  Slot 0: the result; slots 1..: one partial per chunk of
+// SGPU_STATIC_CHUNK pixels.  Every slot a call reads was written by that call: nothing has to start
+// at zero.  All calls share the array: two calls overlapping on the GPU race.
+#define SGPU_STATIC_CHUNK 65536
+__device__ __align__(256) float2 g_static_scratch[SGPU_STATIC_SCRATCH_BYTES / sizeof(float2)];
+
+__global__ void __launch_bounds__(256) minmax_nonzero_chunk_kernel(const float *img, size_t n, size_t first, float2 *scratch) {
+	float mn = FLT_MAX, mx = -FLT_MAX;
+	const size_t lo = first + (size_t) blockIdx.x * SGPU_STATIC_CHUNK;
+	const size_t hi = lo + SGPU_STATIC_CHUNK < n ? lo + SGPU_STATIC_CHUNK : n;
+	for (size_t i = lo + threadIdx.x; i < hi; i += 256) {
+		const float t = img[i];
+		if (t == 0.f) continue;
+		if (t < mn) mn = t;
+		if (t > mx) mx = t;
+	}
+	for (int o = 16; o; o >>= 1) {
+		mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+		mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+	}
+	__shared__ float smn[8], smx[8];
+	if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		for (int w = 1; w < 8; w++) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+		scratch[1 + blockIdx.x] = make_float2(mn, mx);
+	}
+}
+
+__global__ void __launch_bounds__(256) minmax_final_kernel(float2 *scratch, int nparts) {
+	float mn = FLT_MAX, mx = -FLT_MAX;
+	for (int i = threadIdx.x; i < nparts; i += 256) { const float2 p = scratch[1 + i]; mn = fminf(mn, p.x); mx = fmaxf(mx, p.y); }
+	for (int o = 16; o; o >>= 1) {
+		mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+		mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+	}
+	__shared__ float smn[8], smx[8];
+	if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		for (int w = 1; w < 8; w++) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+		scratch[0] = make_float2(mn, mx);
+	}
+}
+
+// device address of g_static_scratch, per device: in host code the array's NAME is only a stand-in
+static float2 *static_scratch_of(sgpu_ctx *ctx) {
+	static std::mutex mu;
+	static float2 *addr[SGPU_STATIC_MAX_DEVICES];
+	if (ctx->device < 0 || ctx->device >= SGPU_STATIC_MAX_DEVICES) {
+		sgpu_fail(ctx, SGPU_GENERIC_ERROR, "device %d is beyond the %d devices the static scratch is tracked for", ctx->device, SGPU_STATIC_MAX_DEVICES);
+		return nullptr;
+	}
+	std::lock_guard<std::mutex> lk(mu);
+	if (!addr[ctx->device]) {	// set-up, once per device, with that device current
+		void *p = nullptr;
+		cudaError_t e = cudaSetDevice(ctx->device);
+		if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_static_scratch);
+		if (e != cudaSuccess) {
+			sgpu_cuda_fail(ctx, e, "cudaGetSymbolAddress(g_static_scratch)");
+			return nullptr;
+		}
+		addr[ctx->device] = (float2 *) p;
+	}
+	return addr[ctx->device];
 }
 
 __global__ void rescale_kernel(float *img, size_t n, float mini, float maxi) {
@@ -90,6 +160,29 @@ int sgpu_minmax_nonzero(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_fi
 	float mn = FLT_MAX, mx = -FLT_MAX;
 	for (auto &p : part) { if (p.x < mn) mn = p.x; if (p.y > mx) mx = p.y; }
 	minmax[0] = mn; minmax[1] = mx;
+	return SGPU_OK;
+}
+
+int sgpu_minmax_nonzero_static(sgpu_ctx *ctx, const float *d_img, size_t n, int skip_first, float minmax[2]) {
+	if (!ctx || !d_img || !minmax) return SGPU_GENERIC_ERROR;
+	if (n > (size_t) SGPU_STATIC_MAX_PIXELS) {
+		return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "sgpu_minmax_nonzero_static: %zu pixels are beyond the static scratch's limit of %zu "
+				"(%d bytes, one 8-byte partial per %d pixels): use sgpu_minmax_nonzero", n, (size_t) SGPU_STATIC_MAX_PIXELS,
+				SGPU_STATIC_SCRATCH_BYTES, SGPU_STATIC_CHUNK);
+	}
+	float2 *scratch = static_scratch_of(ctx);
+	if (!scratch) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t first = skip_first ? 1 : 0;
+	const int nparts = n > first ? (int) ((n - first + SGPU_STATIC_CHUNK - 1) / SGPU_STATIC_CHUNK) : 0;
+	if (nparts) minmax_nonzero_chunk_kernel<<<nparts, 256, 0, ctx->stream>>>(d_img, n, first, scratch);
+	minmax_final_kernel<<<1, 256, 0, ctx->stream>>>(scratch, nparts);
+	ctx->launches += nparts ? 2 : 1;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	float2 r;
+	SGPU_CUDA(ctx, cudaMemcpyAsync(&r, scratch, sizeof r, cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	minmax[0] = r.x; minmax[1] = r.y;
 	return SGPU_OK;
 }
 
