@@ -500,11 +500,14 @@ def main():
     ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's image height")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--rej", default="", help="profiling only: override the workload's rejection (none, sigma, winsorized, ...)")
+    ap.add_argument("--frames", type=int, default=0, help="profiling only: override the workload's stack depth")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
     if args.height:
         wl = wl[:2] + (args.height,) + wl[3:-1] + (wl[-1] + f" [PROFILING SUBSET: {args.height} rows]",)
+    if args.frames:
+        wl = (args.frames,) + wl[1:-1] + (wl[-1] + f" [PROFILING: {args.frames} frames]",)
     if args.rej:
         wl = wl[:6] + (REJ_NAMES.index(args.rej),) + wl[7:-1] + (wl[-1] + f" [PROFILING: rejection {args.rej}]",)
     if args.impl == "reference":

@@ -1,0 +1,17 @@
+#!/bin/bash
+# selection engine check: its parity tests, then the target bench (device-resident only) and variants
+cd "$(dirname "$0")/.."
+TAG=${1:-r2l}
+timeout 1200 python -m pytest tests/test_gpu_psel.py tests/test_gpu_parity.py -x -q -k "psel or auto" > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/${TAG}_pytest.log
+run() { # name, env..., args after --
+  local name=$1; shift
+  env "${ENVV[@]}" timeout 300 python bench.py --steps 4 --warmup 3 --no-e2e --no-cpu "$@" > gpurun_out/${TAG}_$name.json 2> gpurun_out/${TAG}_$name.err
+  echo "$name rc=$? $(python -c "import json,sys; d=json.load(open('gpurun_out/${TAG}_$name.json')); print(d['ms_per_step'], round(d['roofline']['frac'],4), d['detail']['handed_to_exact_engine_px'])")"
+}
+ENVV=(A=1); run target
+ENVV=(SGPU_PSEL_STOP=3); run stop3
+ENVV=(SGPU_PSEL_STOP=2); run stop2
+ENVV=(A=1); run none --rej none
+ENVV=(A=1); run C3 --workload C3
+ENVV=(A=1); run C1 --workload C1
+for extra in $EXTRA_RUNS; do ENVV=($extra); run "x_${extra//[^A-Za-z0-9_=]/}"; done

@@ -305,10 +305,130 @@ struct PartialAcc {
 	SGPU_HD __forceinline__ void set(int, float) const { miss = true; }	// no rejection here compacts in place
 };
 
+// 1 / i: from a table of correctly rounded reciprocals when there is one (device: a load instead of
+// MUFU.RCP64H and its Newton steps), else rcp_d — the same value either way
+SGPU_HD __forceinline__ double psel_rcp(const double *tab, int i) {
+#ifdef __CUDA_ARCH__
+	if (tab) return __ldg(tab + i);
+#endif
+	(void) tab;
+	return rcp_d(i);
+}
+
+// sd_interval (sorted.cuh) for this engine's B2: one square root; the float-mean term of the upper
+// bound (sum (x - m~)^2 = sum (x - m)^2 + n (m - m~)^2) is folded into the relative margin unless it is
+// a noticeable part of the variance (levels thousands of sigmas above zero), which takes a second root
+SGPU_HD __forceinline__ bool psel_sd_bounds(const Sums &S, int nn, double rn, double rn1, float *lo, float *hi) {
+	const double var = (S.S2 - S.S1 * S.S1 * rn) * rn1;
+	if (!(var >= 0.0)) return false;
+	const double e = fabs(S.K + S.S1 * rn) * 5.9604645e-08;	// >= half an ulp of the float mean
+	const double t = e * e * ((double) nn * rn1);
+	const float s = sqrtf((float) var);
+	float sh = s;
+	if (t > var * 1e-7) sh = sqrtf((float) (var + t));
+	*lo = s * (1.f - SGPU_DELTA_SD); *hi = sh * (1.f + (SGPU_DELTA_SD + 1e-7f));
+	return *hi < FLT_MAX;
+}
+
+// one iteration of the reference's loop (rejection_float.c:174-209) from the state "s.a lows and s.bh highs
+// rejected, sums S1 / S2 of the kept": what it rejects, and whether the loop goes on
+enum { SIG_STOP = 0, SIG_LAST = 1, SIG_CONT = 2, SIG_FAIL = 3 };	// nothing rejected (state final) | state after it final | another iteration | hand over
+struct SigState { int status, a, bh; double S1, S2; };
+struct SigCtx {
+	int n, nl, cc, nh, m, cl;
+	float lstand, hstand, s0, s1;
+	double K;
+	const double *rcp_tab;
+};
+
+template <bool U16, class Store>
+SGPU_HD __forceinline__ SigState psel_sigma_step(const Store &col, const SigCtx &x, SigState s) {
+	s.status = SIG_STOP;
+	const int a = s.a, bh = s.bh, nn = x.n - a - bh, r = a + bh;
+	if (nn - r <= 4) return s;		// the guard refuses every rejection of this pass
+	// the next two candidates of each side and the median's rows, all loaded before the arithmetic
+	const float l0 = a < x.nl ? col.get(a) : x.lstand, l1 = a + 1 < x.nl ? col.get(a + 1) : x.lstand;
+	const float h0 = bh < x.nh ? col.get(x.m - 1 - bh) : x.hstand, h1 = bh + 1 < x.nh ? col.get(x.m - 2 - bh) : x.hstand;
+	bool miss = false;
+	auto cen = [&](int rank) { int q = rank - x.cl; if ((unsigned) q >= (unsigned) x.cc) { miss = true; q = 0; } return col.get(x.nl + q); };
+	const float medf = (float) median_sorted<U16>(cen, a, nn);
+	Sums S; S.K = x.K; S.S1 = s.S1; S.S2 = s.S2;
+	float slo, shi;
+	s.status = SIG_FAIL;
+	if (!psel_sd_bounds(S, nn, psel_rcp(x.rcp_tab, nn), psel_rcp(x.rcp_tab, nn - 1), &slo, &shi) || miss) return s;
+	const float tl = shi * x.s0, th = shi * x.s1;	// sigma_clipping_float: `sigma * sigmalow`
+	int a2 = a, b2 = bh;
+	float vl = l0, vh = h0;		// V_low[a2], V_high[b2]
+	while (medf - vl > tl) {
+		if (++a2 > x.nl) return s;	// the stand-in went: samples that were never extracted are in play
+		vl = a2 == a + 1 ? l1 : (a2 < x.nl ? col.get(a2) : x.lstand);
+	}
+	while (vh - medf > th) {
+		if (++b2 > x.nh) return s;
+		vh = b2 == bh + 1 ? h1 : (b2 < x.nh ? col.get(x.m - 1 - b2) : x.hstand);
+	}
+	if (medf - vl > slo * x.s0 || vh - medf > slo * x.s1) return s;	// the low end of the interval rejects more
+	const int K = (a2 - a) + (b2 - bh);
+	if (K == 0) { s.status = SIG_STOP; return s; }
+	if (nn - r - K < 4) return s;	// the guard would cut this pass short: order dependent
+	if (a2 > a) {
+		S.sub(l0);
+		if (a2 > a + 1) {
+			S.sub(l1);
+#pragma unroll 1
+			for (int i = a + 2; i < a2; i++) S.sub(col.get(i));
+		}
+	}
+	if (b2 > bh) {
+		S.sub(h0);
+		if (b2 > bh + 1) {
+			S.sub(h1);
+#pragma unroll 1
+			for (int i = bh + 2; i < b2; i++) S.sub(col.get(x.m - 1 - i));
+		}
+	}
+	s.a = a2; s.bh = b2; s.S1 = S.S1; s.S2 = S.S2;
+	s.status = (x.n - a2 - b2 <= 3) ? SIG_LAST : SIG_CONT;
+	return s;
+}
+
+// Sigma clipping (fast_sigma, sorted.cuh) restated in ROW space, with the dependent chain cut short: B2 is
+// latency bound — its pixels in flight are fixed by the shared memory a tile takes.  The clip walks run over
+// V_low = [lows..., stand-in] and V_high = [highs (descending)..., stand-in] by row index, medians are centre
+// rows, reciprocals come from a table, a rejected stand-in is a hand-over at once.  Decisions and arithmetic
+// are fast_sigma's (same sd interval up to its margin, same float predicates, same down-dated sums);
+// tests/test_psel_host.py runs it against the oracle.  (Running the next pass speculatively on the group's other
+// lanes — one hypothesis per lane about what this pass rejects — was tried: the lanes diverge and it was slower.)
+template <bool U16, class Store>
+SGPU_HD __forceinline__ void psel_sigma(const Store &col, const PselHdr &h, int nl, int cc, int nh, const RejCfg &c, const double *rcp_tab,
+		int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	SigCtx x;
+	x.n = h.n; x.nl = nl; x.cc = cc; x.nh = nh; x.m = nl + cc + nh; x.cl = h.cl;
+	x.lstand = nl ? h.blo : h.mn; x.hstand = nh ? h.bhi : h.mx; x.s0 = c.s0; x.s1 = c.s1; x.K = h.K; x.rcp_tab = rcp_tab;
+	{
+		bool miss = false;
+		auto cen = [&](int rank) { int q = rank - x.cl; if ((unsigned) q >= (unsigned) cc) { miss = true; q = 0; } return col.get(nl + q); };
+		const double median = median_sorted<U16>(cen, 0, x.n);
+		if (miss || (U16 ? ((float) median == 0.f) : (median == 0.0))) return;
+	}
+	SigState s; s.status = SIG_CONT; s.a = 0; s.bh = 0; s.S1 = h.S1; s.S2 = h.S2;
+#pragma unroll 1
+	for (int pass = 0; s.status == SIG_CONT; pass++) {
+		if (pass == 64) return;	// far more passes than a sane stack takes
+		s = psel_sigma_step<U16>(col, x, s);
+	}
+	if (s.status == SIG_FAIL) return;
+	rej[0] += s.a; rej[1] += s.bh;
+	Sums S; S.K = x.K; S.S1 = s.S1; S.S2 = s.S2;
+	o.status = FAST_DONE; o.kept = x.n - s.a - s.bh; o.sum = S.sum(o.kept);
+	o.pmin = s.a < nl ? col.get(s.a) : x.lstand; o.pmax = s.bh < nh ? col.get(x.m - 1 - s.bh) : x.hstand;
+}
+
 // Store: get(row) / set(row, v) on the pixel's column: m + 2 rows, the first m sorted by B1
 template <bool U16, class Store, typename OrigFn>
 SGPU_HD double psel_pixel(const Store &col, const PselHdr &h, int N, int is_mean, const RejCfg &c,
-		const double *wts, OrigFn orig, int rej[2], int *status) {
+		const double *wts, OrigFn orig, int rej[2], int *status, const double *rcp_tab = nullptr) {
 	*status = FAST_FALLBACK;
 	if (h.flags & (PSEL_WEIRD | PSEL_HANDOVER)) return 0.0;
 	const int n = h.n;
@@ -331,6 +451,7 @@ SGPU_HD double psel_pixel(const Store &col, const PselHdr &h, int N, int is_mean
 			o.status = FAST_DONE; o.kept = n; o.sum = 0.0; o.pmin = o.pmax = 0.f;
 			if (n == 1 || c.type == SGPU_NO_REJEC) fast_all(acc, n, &S0, o);
 			else if (c.type == SGPU_PERCENTILE) fast_percentile<U16>(acc, n, c, &S0, rej, o);
+			else if (c.type == SGPU_SIGMA && !acc.trivial) psel_sigma<U16>(col, h, nl, cc, nh, c, rcp_tab, rej, o);
 			else if (c.type == SGPU_SIGMA) fast_sigma<U16>(acc, n, c, &S0, rej, o);
 			else o.status = FAST_FALLBACK;
 			if (o.status != FAST_DONE || o.kept == 0) o.status = FAST_FALLBACK;

@@ -450,7 +450,7 @@ SGPU_HD double fast_combine(const FastRes &o, int nb, const double *w, OrigFn or
 		}
 		return sum / norm;
 	}
-	return o.sum / (double) o.kept;
+	return div_by_int(o.sum, o.kept);	// the correctly rounded quotient, without the division routine
 }
 
 template <bool U16, class Acc, typename OrigFn>

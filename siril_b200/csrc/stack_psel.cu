@@ -2,6 +2,7 @@
 // (lanes per pixel) for the stack depth, sizes shared memory, clears the hand-over list, launches,
 // then lets the exact engine redo the list.
 #include <cstdlib>
+#include <mutex>
 #include "stack_psel.cuh"
 
 using namespace sgpu;
@@ -20,6 +21,26 @@ static const PselVariant *pick(int N) {
 	}
 	for (const PselVariant &v : VARIANTS) if (N >= v.nmin && N <= v.nmax) return &v;
 	return nullptr;
+}
+
+// correctly rounded reciprocals 1 / i for the B2 arithmetic (psel_rcp), filled once per device
+#define PSEL_RCP_N 1282
+static __device__ double g_psel_rcp[PSEL_RCP_N];
+static const double *psel_rcp_table(sgpu_ctx *ctx) {
+	static std::mutex mu;
+	static const double *addr[64];
+	if (ctx->device < 0 || ctx->device >= 64) return nullptr;
+	std::lock_guard<std::mutex> lk(mu);
+	if (!addr[ctx->device]) {
+		static double host[PSEL_RCP_N];
+		host[0] = 0.0;
+		for (int i = 1; i < PSEL_RCP_N; i++) host[i] = 1.0 / (double) i;
+		void *p = nullptr;
+		if (cudaGetSymbolAddress(&p, g_psel_rcp) != cudaSuccess) return nullptr;
+		if (cudaMemcpy(p, host, sizeof host, cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+		addr[ctx->device] = (const double *) p;
+	}
+	return addr[ctx->device];
 }
 
 bool sgpu_psel_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
@@ -46,6 +67,8 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	SGPU_CUDA(ctx, cudaMemsetAsync(p.list_count, 0, sizeof(unsigned), ctx->stream));
 	ctx->list_used = true;
 	p.is_u16 = d.dtype == SGPU_U16;
+	{ const char *e = getenv("SGPU_PSEL_STOP"); p.dbg_stop = e ? atoi(e) : 0; }
+	p.rcp_tab = psel_rcp_table(ctx);	// null: the kernel computes the reciprocals
 	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes
 	CUtensorMap tmap;
 	p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; p.use_tma = 0;
@@ -59,11 +82,13 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	}
 	const int T = 1 << var->lt, nt = var->sub * T * 32, pxc = var->sub * TILE_PX;
 	const int rows8 = (p.tile_rows + 9) & ~7, lcap = psel_list_cap(T);
-	const size_t shm = (size_t) var->sub * TILE_PX * rows8 * sizeof(float) + (size_t) pxc * sizeof(int) + 16
+	const size_t shm = (size_t) var->sub * TILE_PX * rows8 * sizeof(float) + 16
 		+ ((p.use_tma && a->normalize != SGPU_NO_NORM) ? (size_t) d.nb_frames * 16 : 0) + (size_t) lcap * nt * sizeof(float);
-	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the selection engine");
+	size_t shm_pad = 0;
+	if (const char *e = getenv("SGPU_PSEL_PAD")) shm_pad = (size_t) atol(e);	// tuning aid: extra shared memory per CTA (fewer CTAs per SM)
+	if (shm + shm_pad > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the selection engine");
 	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
-	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);
+	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm + shm_pad);
 	if (rv) return rv;
 	return sgpu_launch_exact_list(ctx, blk, p);
 }
