@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SGPU_ABI_VERSION 2
+#define SGPU_ABI_VERSION 3
 
 enum {	/* stacking.h:18-24 */
 	SGPU_OK = 0,
@@ -169,6 +169,8 @@ typedef struct {
 	int create_rejmaps;		/* args->create_rejmaps */
 	int merge_lowhigh_rejmaps;	/* args->merge_lowhigh_rejmaps */
 	int nb_critical;		/* entries critical_value holds; 0: not stated (trusted to be (int) floor((float) nb_frames * sig[0])) */
+	int source_bitpix;		/* seq->bitpix of the frames as they were on disk; only 8 (BYTE_IMG) matters: with a 16-bit output and
+					 * output_norm the result is scaled by 65535/255 (normalize_to16bit, median_and_mean.c:547-555,1729-1733); 0: unknown */
 	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 5: force the lane-sort engine; 6: force the selection engine */
 } sgpu_stack_args;
 

@@ -182,6 +182,7 @@ int gpu_stack_mean_or_median(struct stacking_args *args, gboolean is_mean) {
 	sa.shiftx = any_sx ? shiftx : NULL;
 	sa.output_norm = args->output_norm; sa.use_32bit_output = args->use_32bit_output;
 	sa.create_rejmaps = maps; sa.merge_lowhigh_rejmaps = args->merge_lowhigh_rejmaps;
+	sa.source_bitpix = args->seq->bitpix;	/* normalize_to16bit (:547-555) */
 
 	/* Row blocks (the reference: stack_get_max_number_of_rows :1234 from the RAM budget; here from the
 	 * HBM the device has left): every frame's rows of the block are read into a pinned staging buffer,

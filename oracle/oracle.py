@@ -39,6 +39,7 @@ class _StackParams(C.Structure):
         ("create_rejmaps", C.c_int), ("merge_rejmaps", C.c_int),
         ("nthreads", C.c_int),
         ("max_rows", C.c_long),
+        ("source_bitpix", C.c_int),
     ]
 
 
@@ -175,7 +176,7 @@ class Oracle:
     def stack(self, frames, *, is_mean=True, rejection=NO_REJEC, sig=(3.0, 3.0), crit=None,
               normalize=NO_NORM, scale=None, offset=None, mul=None, weights=None,
               shiftx=None, shifty=None, output_norm=False, use_32bit_output=True,
-              create_rejmaps=False, merge_rejmaps=False, nthreads=None, max_rows=0):
+              create_rejmaps=False, merge_rejmaps=False, nthreads=None, max_rows=0, source_bitpix=0):
         """frames: ndarray [N][C][H][W] float32|uint16 (memory / FITS row order).
         Returns dict(out, rej_low, rej_high, irej[3][2])."""
         frames = np.ascontiguousarray(frames)
@@ -204,6 +205,7 @@ class Oracle:
         p.create_rejmaps, p.merge_rejmaps = int(create_rejmaps), int(merge_rejmaps)
         p.nthreads = nthreads or os.cpu_count() or 1
         p.max_rows = max_rows
+        p.source_bitpix = source_bitpix
         out = np.zeros((Cn, H, W), dtype=np.float32 if use_32bit_output else np.uint16)
         rl = np.zeros((Cn, H, W), dtype=np.uint16) if create_rejmaps else None
         rh = np.zeros((Cn, H, W), dtype=np.uint16) if (create_rejmaps and not merge_rejmaps) else None

@@ -124,6 +124,7 @@ typedef struct {
 	int create_rejmaps, merge_rejmaps;
 	int nthreads;
 	long max_rows;				/* planner budget; <=0: whole image */
+	int source_bitpix;			/* seq->bitpix; 8 (BYTE_IMG): normalize_to16bit */
 } ref_stack_params;
 
 /* Restatement of the block loop of stack_mean_or_median (median_and_mean.c:1552-1760) on
@@ -228,6 +229,8 @@ static void ref_stack_block(int b, int tid, void *vctx) {
 						v = p->output_norm ? (float) result : set_float_in_interval((float) result, 0.f, 1.f);
 					((float *) out)[o] = v;
 				} else {
+					if (p->output_norm && p->source_bitpix == 8)	/* normalize_to16bit (median_and_mean.c:547-555, :1729-1732) */
+						result *= (USHRT_MAX_DOUBLE / UCHAR_MAX_DOUBLE);
 					((WORD *) out)[o] = round_to_WORD(result);
 				}
 			}

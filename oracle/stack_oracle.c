@@ -615,6 +615,7 @@ typedef struct {
 	int create_rejmaps, merge_rejmaps;
 	int nthreads;
 	long max_rows;				/* unused by the restatement (kept for ABI parity with ref_stack) */
+	int source_bitpix;			/* seq->bitpix; 8 (BYTE_IMG): normalize_to16bit */
 } orc_stack_params;
 
 /* src/stacking/median_and_mean.c:557-582; NB the min/max scan starts at index 1 (:566) */
@@ -702,7 +703,10 @@ int orc_stack(const orc_stack_params *p, const void *frames, void *out,
 					float v = p->is_float ? (float) result : (float) result * .000015259022f;
 					if (!p->output_norm) v = clampf(v, 0.f, 1.f);
 					((float *) out)[o] = v;
-				} else ((u16 *) out)[o] = rnd_word(result);					/* :1733 */
+				} else {
+					if (p->output_norm && p->source_bitpix == 8) result *= (65535.0 / 255.0);	/* normalize_to16bit :547-555, :1729-1732 */
+					((u16 *) out)[o] = rnd_word(result);					/* :1733 */
+				}
 			}
 		}
 #pragma omp critical

@@ -1,10 +1,14 @@
-# round-end check on the GPU box: new FITS reader parity, smoke, default bench, then the full parity suite
-set -x
-mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_fitsread.py -x -q > gpurun_out/r1f_pytest_fits.log 2>&1; echo "fits rc=$?"
-tail -5 gpurun_out/r1f_pytest_fits.log
-timeout 300 python __graft_entry__.py smoke > gpurun_out/r1f_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/r1f_smoke.log
-timeout 900 python bench.py > gpurun_out/r1f_bench.json 2> gpurun_out/r1f_bench.err; echo "bench rc=$?"; tail -c 1500 gpurun_out/r1f_bench.json
-timeout 300 python scripts/fits_time.py > gpurun_out/r1f_fits_time.log 2>&1; echo "fits_time rc=$?"; tail -8 gpurun_out/r1f_fits_time.log
-timeout 1500 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_fitsread.py > gpurun_out/r1f_pytest_gpu.log 2>&1; echo "pytest rc=$?"
-tail -5 gpurun_out/r1f_pytest_gpu.log
+#!/bin/bash
+# the round's measurement set: full GPU suite, smoke, default bench (target, with e2e and cpu_baseline), reference arm,
+# device-resident lines of C1-C5, launch list and one full ncu capture of the target's kernel
+cd "$(dirname "$0")/.."
+TAG=${1:-r2z}
+timeout 2400 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest gpu rc=$?"; tail -3 gpurun_out/${TAG}_pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/${TAG}_smoke.log
+timeout 1200 python bench.py > gpurun_out/${TAG}_bench_target.json 2> gpurun_out/${TAG}_bench_target.err; echo "bench rc=$?"; tail -2 gpurun_out/${TAG}_bench_target.err; head -c 600 gpurun_out/${TAG}_bench_target.json; echo
+timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_target_reference_arm.json 2> gpurun_out/${TAG}_bench_ref.err; echo "ref rc=$?"; head -c 400 gpurun_out/${TAG}_bench_target_reference_arm.json; echo
+for wl in C1 C2 C3 C4 C5; do
+  timeout 900 python bench.py --workload $wl --no-e2e > gpurun_out/${TAG}_bench_$wl.json 2> gpurun_out/${TAG}_bench_$wl.err; echo "$wl rc=$? $(python -c "import json; d=json.load(open('gpurun_out/${TAG}_bench_$wl.json')); print(d['ms_per_step'], round(d['roofline']['frac'],4), d['roofline']['kernel'], d['detail'], d['cpu_baseline']['value'])")"
+done
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:stack_ -c 24 --csv --log-file gpurun_out/${TAG}_launches_target.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/${TAG}_ncu_ll.log 2>&1; echo "launch list rc=$?"
+timeout 900 ncu --set full --import-source on --clock-control none -k regex:stack_psel -s 3 -c 1 -o gpurun_out/${TAG}_target_full python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --height 1024 > gpurun_out/${TAG}_ncufull.log 2>&1; echo "ncu full rc=$?"

@@ -27,7 +27,7 @@ class StackArgs(C.Structure):
                 ("weights", C.c_void_p), ("shiftx", C.c_void_p),
                 ("output_norm", C.c_int), ("use_32bit_output", C.c_int),
                 ("create_rejmaps", C.c_int), ("merge_lowhigh_rejmaps", C.c_int), ("nb_critical", C.c_int),
-                ("engine", C.c_int)]
+                ("source_bitpix", C.c_int), ("engine", C.c_int)]
 
 
 class ImStats(C.Structure):

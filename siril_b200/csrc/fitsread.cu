@@ -67,11 +67,13 @@ __global__ void __launch_bounds__(256) fits_decode_byte_kernel(const unsigned ch
 
 // ---- staging -------------------------------------------------------------------------------------
 static int ensure_stage(sgpu_ctx *ctx) {
-	if (ctx->h_stage[0]) return SGPU_OK;
+	if (ctx->h_stage[0] && ctx->h_stage[1] && ctx->d_stage[0] && ctx->d_stage[1] && ctx->stage_ev[0] && ctx->stage_ev[1]) return SGPU_OK;
+	sgpu_free_stage(ctx);	// a half-made set from a failed call: start over
 	for (int k = 0; k < 2; k++) {
-		SGPU_CUDA(ctx, cudaMallocHost(&ctx->h_stage[k], SGPU_STAGE_CHUNK + 16));
-		SGPU_CUDA(ctx, cudaMalloc(&ctx->d_stage[k], SGPU_STAGE_CHUNK + 16));
-		SGPU_CUDA(ctx, cudaEventCreateWithFlags(&ctx->stage_ev[k], cudaEventDisableTiming));
+		cudaError_t e = cudaMallocHost(&ctx->h_stage[k], SGPU_STAGE_CHUNK + 16);
+		if (e == cudaSuccess) e = cudaMalloc(&ctx->d_stage[k], SGPU_STAGE_CHUNK + 16);
+		if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->stage_ev[k], cudaEventDisableTiming);
+		if (e != cudaSuccess) { sgpu_free_stage(ctx); return sgpu_cuda_fail(ctx, e, "staging buffers of the FITS reader"); }
 	}
 	return SGPU_OK;
 }
@@ -320,11 +322,33 @@ int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, cons
 	const sgpu_block_desc desc = { nb_frames, (int) fi[0].naxes[2], (int) fi[0].naxes[0], (int) fi[0].naxes[1],
 			fi[0].bitpix == -32 ? SGPU_F32 : SGPU_U16 };
 	const int H = desc.height;
+	// Float data without a DATAMAX key: the reference guesses the range from three or four samples of
+	// whatever region it has just read (image_format_fits.c:997-1003), so its answer depends on ITS
+	// block plan.  The row blocks here are not the reference's, and a frame must not be scaled in one
+	// block and left alone in another: the guess is made ONCE per file, on the samples the reference
+	// would look at when it reads the first layer whole.
+	std::vector<int> rescale(nb_frames, 0);
+	for (int f = 0; f < nb_frames; f++) {
+		if (fi[f].bitpix != -32) continue;
+		if (fi[f].has_datamax) { rescale[f] = fi[f].datamax > 10.0; continue; }
+		const size_t nbdata = (size_t) desc.width * (size_t) H;
+		if (nbdata <= 3) continue;
+		double data_max = 0.;
+		for (size_t i = 0; i < nbdata; i += nbdata / 3) {
+			unsigned char q[4];
+			if (pread(fds[f], q, 4, (off_t) (fi[f].data_offset + i * 4)) != 4) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d", f));
+			const uint32_t w = ((uint32_t) q[0] << 24) | ((uint32_t) q[1] << 16) | ((uint32_t) q[2] << 8) | q[3];
+			float x; memcpy(&x, &w, 4);
+			data_max = (data_max > x) ? data_max : x;	// the reference's max() macro, NaN included
+		}
+		rescale[f] = data_max > 10.0;
+	}
+	sgpu_stack_args with_bitpix = *args;
+	with_bitpix.source_bitpix = fi[0].bitpix;	// BYTE_IMG sequences: normalize_to16bit
 	const int rv = sgpu_stack_host_impl(ctx, &desc, [&](sgpu_block *b, int f, int row0) {
 		RawSource src; src.fd = fds[f]; src.base = (off_t) fi[f].data_offset;
-		const int rescale = fi[f].has_datamax ? (fi[f].datamax > 10.0) : -1;
-		return upload_raw(b, f, src, fi[f].bitpix, H, row0, shifty ? shifty[f] : 0, rescale);
-	}, args, out, rej_low, rej_high, irej);
+		return upload_raw(b, f, src, fi[f].bitpix, H, row0, shifty ? shifty[f] : 0, rescale[f]);
+	}, &with_bitpix, out, rej_low, rej_high, irej);
 	return close_all(rv);
 }
 

@@ -14,6 +14,7 @@ struct StackParams {
 	const int *shiftx;	// device [N] or null
 	RejCfg rc;
 	int is_mean, output_norm, out32, rejmaps;	// rejmaps: 0 none, 1 merged, 2 low+high
+	int norm16;		// 8-bit frames, 16-bit output, output_norm: the result is scaled by 65535/255 (normalize_to16bit)
 	void *out; u16 *rej_low, *rej_high;
 	unsigned long long *irej;	// [3][2]
 	void *scratch;		// exact engine: global columns when the tile does not fit in shared memory
@@ -66,7 +67,10 @@ __device__ __forceinline__ void store_result(const StackParams &p, size_t o, dou
 		float v = (sizeof(T) == 4) ? (float) result : (float) result * .000015259022f;
 		if (!p.output_norm) { v = v < 0.f ? 0.f : v; v = v > 1.f ? 1.f : v; }
 		((float *) p.out)[o] = v;
-	} else ((u16 *) p.out)[o] = round_to_word(result);
+	} else {
+		if (p.norm16) result *= (65535.0 / 255.0);	// normalize_to16bit (median_and_mean.c:547-555)
+		((u16 *) p.out)[o] = round_to_word(result);
+	}
 }
 
 }  // namespace sgpu

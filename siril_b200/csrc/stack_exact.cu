@@ -108,6 +108,7 @@ void sgpu_fill_stack_params(StackParams &p, sgpu_block *blk, const sgpu_stack_ar
 		p.rc.m_x = mx; p.rc.m_dx2 = 1.f / acc;
 	}
 	p.is_mean = a->is_mean; p.output_norm = a->output_norm; p.out32 = a->use_32bit_output;
+	p.norm16 = a->source_bitpix == 8 && a->output_norm && !a->use_32bit_output;
 	p.rejmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
 	p.out = d_out; p.rej_low = d_rej_low; p.rej_high = d_rej_high; p.irej = (unsigned long long *) d_irej;
 	p.use_aux = a->is_mean && (p.rc.type == SGPU_MAD || p.rc.type == SGPU_GESDT);

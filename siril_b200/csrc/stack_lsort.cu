@@ -59,8 +59,12 @@ int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 	const LsortVariant *var = nullptr;
 	for (const LsortVariant &v : VARIANTS) if ((v.rs << v.lt) >= d.nb_frames) { var = &v; break; }
 	if (const char *e = getenv("SGPU_LSORT_ALT")) {	// alternates follow their primary in the table
-		const LsortVariant *alt = var + atoi(e);
-		if (var && alt < VARIANTS + sizeof VARIANTS / sizeof VARIANTS[0] && alt->lt == var->lt && alt->rs == var->rs && alt->re == var->re) var = alt;
+		const int k = atoi(e);
+		const ptrdiff_t nvar = (ptrdiff_t) (sizeof VARIANTS / sizeof VARIANTS[0]);
+		if (var && k >= 0 && k <= 3 && (var - VARIANTS) + k < nvar) {
+			const LsortVariant *alt = var + k;
+			if (alt->lt == var->lt && alt->rs == var->rs && alt->re == var->re) var = alt;
+		}
 	}
 	if (!var) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "no lane-sort variant for %d frames", d.nb_frames);
 	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes

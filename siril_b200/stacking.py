@@ -84,6 +84,7 @@ class StackingArgs:
     weighting_type: int = NO_WEIGHT
     weights: Optional[np.ndarray] = None
     bgnoise: Optional[np.ndarray] = None  # seq->stats[layer][idx]->bgnoise, filled by do_normalization
+    source_bitpix: int = 0          # seq->bitpix of the frames on disk; 8: normalize_to16bit with a 16-bit output_norm result
     engine: int = 0
     retval: int = ST_OK
     result: StackResult = field(default_factory=StackResult)
@@ -161,6 +162,7 @@ def _fill_cargs(args, n, c, is_mean, keep):
     a.create_rejmaps = int(args.create_rejmaps)
     a.merge_lowhigh_rejmaps = int(args.merge_lowhigh_rejmaps)
     a.engine = args.engine
+    a.source_bitpix = args.source_bitpix
     return a
 
 
@@ -202,15 +204,15 @@ def stack_mean_or_median(args: StackingArgs, is_mean: bool) -> int:
         frames = args.frames.contiguous()
         blk = C.c_void_p()
         shifted = args.shifty is not None and np.any(np.asarray(args.shifty) != 0)
-        if shifted:     # the reference applies the y shift when it loads the block (:407-448)
-            ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
-            es = frames.element_size()
-            for f in range(n):
-                ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0,
-                                                    int(args.shifty[f])))
-        else:
-            ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
         try:
+            if shifted:     # the reference applies the y shift when it loads the block (:407-448)
+                ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
+                es = frames.element_size()
+                for f in range(n):
+                    ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0,
+                                                        int(args.shifty[f])))
+            else:
+                ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
             out = torch.empty((c, h, w), dtype=torch.float32 if out32 else torch.uint16, device=dev)
             rl = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if nmaps >= 1 else None
             rh = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if nmaps == 2 else None
@@ -232,7 +234,8 @@ def stack_mean_or_median(args: StackingArgs, is_mean: bool) -> int:
             res.irej = irej.cpu().numpy().astype(np.uint64).reshape(3, 2)
         finally:
             ctx.synchronize()
-            L.sgpu_block_destroy(blk)
+            if blk:
+                L.sgpu_block_destroy(blk)
     else:
         frames = [np.ascontiguousarray(f) for f in args.frames]
         ptrs = (C.c_void_p * n)(*[f.ctypes.data_as(C.c_void_p) for f in frames])
@@ -294,15 +297,15 @@ def _stack_simple(args: StackingArgs, op: int) -> int:
     sx = None if args.shiftx is None else np.ascontiguousarray(args.shiftx, dtype=np.int32)
     sy = None if args.shifty is None else np.ascontiguousarray(args.shifty, dtype=np.int32)
     blk = C.c_void_p()
-    if sy is not None and np.any(sy != 0):
-        ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
-        es = frames.element_size()
-        for f in range(n):
-            ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0, int(sy[f])))
-    else:
-        ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
     ptr = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
     try:
+        if sy is not None and np.any(sy != 0):
+            ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
+            es = frames.element_size()
+            for f in range(n):
+                ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0, int(sy[f])))
+        else:
+            ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
         if op == _lib.SIMPLE_SUM:
             acc = torch.empty((c, h, w), dtype=torch.float64 if is_float else torch.int64, device=dev)
             mx = C.c_double(0.0)
@@ -321,7 +324,8 @@ def _stack_simple(args: StackingArgs, op: int) -> int:
             return rv
     finally:
         ctx.synchronize()
-        L.sgpu_block_destroy(blk)
+        if blk:
+            L.sgpu_block_destroy(blk)
     res = StackResult()
     if host:
         o = out.cpu()

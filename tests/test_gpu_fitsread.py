@@ -145,6 +145,63 @@ def test_stack_fits_files(tmp_path, orc, monkeypatch, dtype, nblk):
     assert rel.max() <= 1e-6
 
 
+@pytest.mark.parametrize("nblk", [1, 3])
+def test_stack_fits_byte_images_normalize_to16bit(tmp_path, orc, monkeypatch, nblk):
+    """8-bit sequences with a 16-bit output and output_norm: the reference scales the result by 65535/255
+    before rounding (normalize_to16bit, median_and_mean.c:547-555, 1729-1733); without output_norm it does not"""
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    monkeypatch.setenv("SGPU_HOST_BLOCKS", str(nblk))
+    rng = np.random.default_rng(77)
+    N, C, H, W = 12, 1, 21, 64
+    fr = np.clip(np.round(40 + 6 * rng.standard_normal((N, C, H, W))), 1, 255).astype(np.uint8)
+    fr[rng.random(fr.shape) < 0.01] = 250
+    paths = []
+    for f in range(N):
+        p = str(tmp_path / f"b_{f:05d}.fit")
+        fits_ref.write_fits(p, fr[f])
+        paths.append(p)
+    wide = fr.astype(np.uint16)      # BYTE_IMG is read into WORD buffers as it is (image_format_fits.c: convert_data_ushort)
+    for output_norm in (True, False):
+        args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.SIGMA, sig=(3.0, 3.0),
+                               use_32bit_output=False, output_norm=output_norm)
+        assert fitsread.stack_fits(args, paths) == 0, getattr(args, "error", "")
+        ref = orc.stack(wide, rejection=sb.SIGMA, sig=(3.0, 3.0), use_32bit_output=False, output_norm=output_norm, source_bitpix=8)
+        assert np.array_equal(args.result.irej, ref["irej"])
+        assert np.array_equal(args.result.data, ref["out"]), output_norm
+        assert (args.result.data.max() > 255) == output_norm
+
+
+def test_stack_fits_float_range_guess_is_per_file(tmp_path, orc, monkeypatch):
+    """float files without DATAMAX whose samples exceed 10 only in some rows: the 1/65535 rescale is decided
+    once per file (the samples the reference looks at when it reads the first layer whole), not per row block"""
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    rng = np.random.default_rng(78)
+    N, H, W = 6, 24, 48
+    fr = (3000.0 + 300 * rng.standard_normal((N, 1, H, W))).astype(np.float32)     # ADU-like floats
+    fr[:, :, :8, :] = 5.0          # a dark band: a block made of these rows alone would guess "already in [0, 1]"
+    paths = []
+    for f in range(N):
+        p = str(tmp_path / f"g_{f:05d}.fit")
+        fits_ref.write_fits(p, fr[f])      # no DATAMAX
+        paths.append(p)
+    outs = []
+    for nblk in (1, 3):
+        monkeypatch.setenv("SGPU_HOST_BLOCKS", str(nblk))
+        args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.NO_REJEC, output_norm=True)
+        assert fitsread.stack_fits(args, paths) == 0, getattr(args, "error", "")
+        outs.append(args.result.data.copy())
+    assert np.array_equal(outs[0], outs[1])
+    # whole-layer sampling: indices 0, n/3, 2n/3 (, n - n%3): sample 0 is 5.0, the others ~3000 -> rescaled everywhere
+    scaled = fr * np.float32(1.0 / 65535.0)
+    ref = orc.stack(scaled.astype(np.float32), rejection=sb.NO_REJEC, output_norm=True)
+    rel = np.abs(outs[0] - ref["out"]) / np.maximum(np.abs(ref["out"]), 1e-30)
+    assert rel.max() <= 1e-6
+
+
 def test_stack_fits_rejects_mixed_sequences(tmp_path):
     import siril_b200 as sb
     from siril_b200 import fitsread
