@@ -25,6 +25,9 @@ struct StackParams {
 	int is_u16;		// sorted engine: sample type is a run-time switch there (fewer kernel variants)
 	int use_tma, tile_rows, box_rows;	// sorted engine: TMA tile load (f32, no x shift, plane a multiple of 16 bytes); rows held / rows per TMA box
 	int need_sums;		// sorted engine: phase A leaves sum(x-K), sum((x-K)^2) beside each sorted stack
+	// selection engine, split form: the stack kernel ends after the extraction and leaves one record per pixel
+	// (PSEL_REC_WORDS words: header + unsorted entries) for psel_finish_kernel; a launch covers pixels [pix_base, ...) of layer layer_base
+	float *records; int split; int layer_base; size_t pix_base;
 	const double *rcp_tab;	// selection engine: correctly rounded 1 / i, i <= 1280 (device)
 	int dbg_stop;		// selection engine, SGPU_PSEL_STOP (timing breakdowns only, results are wrong): 1 return after the tile load, 2 after phase A, 3 after B1
 };

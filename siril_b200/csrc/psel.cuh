@@ -28,7 +28,7 @@
 
 namespace sgpu {
 
-enum { PSEL_WEIRD = 1, PSEL_TRIVIAL = 2, PSEL_HANDOVER = 4 };
+enum { PSEL_WEIRD = 1, PSEL_TRIVIAL = 2, PSEL_HANDOVER = 4, PSEL_DONE = 8 };	// DONE (split form): the stack kernel finished the pixel itself
 
 #define PSEL_NAN __int_as_float_hd(0x7fffffff)
 SGPU_HD __forceinline__ float __int_as_float_hd(int i) {
@@ -51,6 +51,11 @@ struct PselHdr {
 	int tid0;		// CTA thread of the group's first lane (its lists follow at tid0 + t)
 	int flags;
 };
+
+// split form (stack_psel.cu): record of one pixel in global memory between the two kernels
+#define PSEL_REC_HDR 16		// S1, S2, K (doubles), mn, mx, blo, bhi, n, cl, nl, cc, m, flags
+#define PSEL_REC_ENTRIES 64	// more entries than this: hand-over
+#define PSEL_REC_WORDS (PSEL_REC_HDR + PSEL_REC_ENTRIES)
 
 #define PSEL_CAP 64	// longest centre / tail list phase B sorts by insertion (ties can make a class arbitrarily long)
 #define PSEL_CAPT 48

@@ -7,6 +7,7 @@
 
 using namespace sgpu;
 
+int sgpu_launch_psel_finish(sgpu_ctx *ctx, const sgpu::StackParams &p, unsigned chunk_px);
 int sgpu_make_tile_tmap(sgpu_ctx *ctx, CUtensorMap *tm, void *base, size_t npix, int layers, int frames, int box_px, int box_rows);
 
 // 2^lt lanes per pixel; serves nmin <= N <= nmax (about 40 to 80 samples per lane); sub sub-tiles of 32 px per CTA
@@ -87,6 +88,44 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	size_t shm_pad = 0;
 	if (const char *e = getenv("SGPU_PSEL_PAD")) shm_pad = (size_t) atol(e);	// tuning aid: extra shared memory per CTA (fewer CTAs per SM)
 	if (shm + shm_pad > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the selection engine");
+	// Split form (default; SGPU_PSEL_SPLIT=0 keeps everything in the stack kernel): the stack kernel stops after the
+	// extraction and psel_finish_kernel sorts and rejects, one thread per pixel.  The records between the two take
+	// PSEL_REC_WORDS * 4 bytes per pixel of scratch; a block that needs more than half of the free memory is
+	// processed in chunks of pixels.
+	const char *se = getenv("SGPU_PSEL_SPLIT");
+	p.split = !(se && se[0] == '0') && var->lt <= 2;	// deeper stacks extract more entries than a record holds
+	p.layer_base = 0; p.pix_base = 0;
+	if (p.split) {
+		const size_t rec_bytes = (size_t) PSEL_REC_WORDS * sizeof(float);
+		size_t freeb = 0, totalb = 0;
+		SGPU_CUDA(ctx, cudaMemGetInfo(&freeb, &totalb));
+		size_t chunk_px = npix;
+		if (npix * rec_bytes > ctx->d_scratch_cap) {
+			const size_t budget = ctx->d_scratch_cap + freeb / 2;
+			if (chunk_px * rec_bytes > budget) chunk_px = budget / rec_bytes;
+		}
+		if (const char *ce = getenv("SGPU_PSEL_CHUNK")) { const size_t c = (size_t) atol(ce); if (c > 0 && c < chunk_px) chunk_px = c; }	// tests: force chunks
+		chunk_px = chunk_px / pxc * pxc;
+		if (chunk_px < (size_t) pxc) p.split = 0;	// no room for records: the one-kernel form
+		else {
+			rv = sgpu_ensure_scratch(ctx, chunk_px * rec_bytes);
+			if (rv) return rv;
+			p.records = (float *) ctx->d_scratch;
+			for (int layer = 0; layer < d.nb_layers; layer++) {
+				for (size_t base = 0; base < npix; base += chunk_px) {
+					const size_t n = npix - base < chunk_px ? npix - base : chunk_px;
+					p.layer_base = layer; p.pix_base = base;
+					dim3 grid((unsigned) ((n + pxc - 1) / pxc), 1);
+					rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm + shm_pad);
+					if (rv) return rv;
+					rv = sgpu_launch_psel_finish(ctx, p, (unsigned) n);
+					if (rv) return rv;
+				}
+			}
+			p.layer_base = 0; p.pix_base = 0;
+			return sgpu_launch_exact_list(ctx, blk, p);
+		}
+	}
 	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
 	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm + shm_pad);
 	if (rv) return rv;

@@ -220,7 +220,13 @@ __device__ __forceinline__ void psel_finish(const StackParams &p, const Store &c
 		__syncwarp();
 		unsigned lo = rej[0], hi = rej[1];
 		lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
-		if (lane == 0 && (lo | hi)) { atomicAdd(&cta_rej[0], lo); atomicAdd(&cta_rej[1], hi); }
+		if (lane == 0 && (lo | hi)) {
+			if (cta_rej) { atomicAdd(&cta_rej[0], lo); atomicAdd(&cta_rej[1], hi); }
+			else {	// (split form: the few warps that finish their pixels here; the CTA's other warps have left)
+				atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
+				atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+			}
+		}
 	}
 }
 
@@ -259,8 +265,8 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 	const bool raw_norm = p.use_tma && p.normalize != SGPU_NO_NORM;
 	constexpr int LCAP = psel_list_cap(T);
 	float *lists = (float *) (coef + (raw_norm ? N : 0));	// [LCAP][NT]
-	const int layer = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t npix = (size_t) p.H * p.W, pix0 = (size_t) blockIdx.x * PXC;
+	const int layer = (int) blockIdx.y + p.layer_base, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const size_t npix = (size_t) p.H * p.W, pix0 = p.pix_base + (size_t) blockIdx.x * PXC;
 
 	if (threadIdx.x == 0) { cta_rej[0] = 0; cta_rej[1] = 0; }
 	if (p.use_tma) {
@@ -311,6 +317,34 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 		psel_group(ln, p.is_mean, rt == SGPU_SIGMA || rt == SGPU_PERCENTILE, rt == SGPU_PERCENTILE, p.rc.s0, p.rc.s1, h);
 		h.tid0 = (int) threadIdx.x - t;
 		if (p.dbg_stop == 2) return;
+		if (p.split) {
+			// ---- split form: the pixel's header and its (unsorted) entries go to global memory; psel_finish_kernel
+			// sorts them and runs the rejection with one thread per pixel at full occupancy, which this kernel,
+			// whose CTAs are sized by the tile they hold, cannot offer to the scalar tail of a pixel ----
+			const size_t pix = pix0 + (size_t) (sb * TILE_PX + px);
+			const bool valid = pix < npix;
+			if (!ln.any(valid)) return;	// (a warp past the image's last pixel)
+			const bool live = !(h.flags & (PSEL_WEIRD | PSEL_HANDOVER | PSEL_TRIVIAL));
+			// a pixel with more entries than a record holds: its whole warp stays here and finishes below (B1, B2)
+			const bool stay = ln.any(live && h.m > PSEL_REC_ENTRIES);
+			float *rec = p.records + (pix - p.pix_base) * PSEL_REC_WORDS;
+			const int mine = (live && !stay && valid) ? ln.cnt : 0;
+			int pre = mine;		// entries of the lanes before this one
+#pragma unroll
+			for (int d = 1; d < T; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, pre, d, T); if (t >= d) pre += o; }
+			pre -= mine;
+			const uint4 q0 = make_uint4((unsigned) __double2loint(h.S1), (unsigned) __double2hiint(h.S1), (unsigned) __double2loint(h.S2), (unsigned) __double2hiint(h.S2));
+			const uint4 q1 = make_uint4((unsigned) __double2loint(h.K), (unsigned) __double2hiint(h.K), __float_as_uint(h.mn), __float_as_uint(h.mx));
+			const uint4 q2 = make_uint4(__float_as_uint(h.blo), __float_as_uint(h.bhi), (unsigned) h.n, (unsigned) h.cl);
+			const uint4 q3 = make_uint4((unsigned) h.nl, (unsigned) h.cc, (unsigned) h.m, (unsigned) (h.flags | (stay ? PSEL_DONE : 0)));
+			uint4 *rq = (uint4 *) rec;
+			if (!valid) { }
+			else if (T >= 4) { if (t == 0) rq[0] = q0; else if (t == 1) rq[1] = q1; else if (t == 2) rq[2] = q2; else if (t == 3) rq[3] = q3; }
+			else if (T == 2) { if (t == 0) { rq[0] = q0; rq[2] = q2; } else { rq[1] = q1; rq[3] = q3; } }
+			else { rq[0] = q0; rq[1] = q1; rq[2] = q2; rq[3] = q3; }
+			for (int k = 0; k < mine; k++) rec[PSEL_REC_HDR + pre + k] = lds_f32(ln.list0 + (unsigned) k * ln.lstride);
+			if (!stay) return;
+		}
 		// ---- B1: the group's entries, dealt out evenly over its lanes, sorted in registers (the
 		// lane-sort engine's networks) and written over the first rows of the pixel's (now dead) column ----
 		constexpr int RB = psel_sort_slots(T), RB2 = psel_sort_slots2(T);
@@ -333,9 +367,9 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 		// instructions for all T lanes: no barrier, the header never leaves the registers); lane 0 stores.
 		// (One thread per pixel after a CTA barrier issues a quarter of the instructions on a quarter of the
 		// warps: measured the same, 46.8 against 47.8 ms.) ----
-		psel_finish(p, col, h, layer, pix0 + (size_t) (sb * TILE_PX + px), npix, N, t == 0, lane, cta_rej);
+		psel_finish(p, col, h, layer, pix0 + (size_t) (sb * TILE_PX + px), npix, N, t == 0, lane, p.split ? nullptr : cta_rej);
 	}
-	if (p.is_mean && p.rc.type != SGPU_NO_REJEC) {
+	if (!p.split && p.is_mean && p.rc.type != SGPU_NO_REJEC) {
 		__syncthreads();
 		if (threadIdx.x == 0 && (cta_rej[0] | cta_rej[1])) {
 			atomicAdd(&p.irej[layer * 2], (unsigned long long) cta_rej[0]);
