@@ -1,0 +1,16 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+TAG=${1:-r3e}
+timeout 1500 python -m pytest tests/test_gpu_psel.py tests/test_gpu_parity.py tests/test_gpu_stats.py tests/test_gpu_integration.py -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/${TAG}_pytest.log
+SGPU_PSEL_CHUNK=1000 timeout 1200 python -m pytest tests/test_gpu_psel.py -x -q > gpurun_out/${TAG}_pytest_chunk.log 2>&1; echo "pytest chunked rc=$?"; tail -2 gpurun_out/${TAG}_pytest_chunk.log
+run() { local name=$1; shift
+  env "${ENVV[@]}" timeout 300 python bench.py --steps 4 --warmup 3 --no-e2e --no-cpu "$@" > gpurun_out/${TAG}_$name.json 2> gpurun_out/${TAG}_$name.err
+  echo "$name rc=$? $(python -c "import json,sys; d=json.load(open('gpurun_out/${TAG}_$name.json')); print(d['ms_per_step'], round(d['roofline']['frac'],4), d['roofline']['kernel'], d['detail']['handed_to_exact_engine_px'])")"
+}
+ENVV=(A=1); run target
+ENVV=(A=1); run C2 --workload C2
+ENVV=(A=1); run C3 --workload C3
+ENVV=(A=1); run C1 --workload C1
+ENVV=(A=1); run percentile --rej percentile
+bash scripts/gpu_launchlist.sh ${TAG}_target
+bash scripts/gpu_launchlist.sh ${TAG}_C2 --workload C2

@@ -8,7 +8,7 @@
 // the kernel (phase A, stack_psel.cuh) keeps the N samples of a pixel in the registers of a small
 // lane group and makes three streaming passes over them:
 //   sums     n, sum x, sum x^2 in double, min, max;
-//   count    how many samples lie below the (trimmed) mean and how many within 0.45 sd of it:
+//   count    how many samples lie below the (trimmed) mean and how many within one sd of it:
 //            the first locates the median, the second gives a scale no outlier can inflate;
 //   extract  every sample inside a narrow window around the predicted median ("centre", a few
 //            dozen ranks wide) or beyond a radius the clipping thresholds cannot fall inside
@@ -104,37 +104,63 @@ SGPU_HD inline bool psel_plan_count(int n, double S1, double S2, double K, float
 	const double m = T1 * rnt, ss = T2 - T1 * m;		// sum of squares about the trimmed mean
 	if (!(ss > 0.0) || !(ss * 1e9 > T2)) return false;
 	*mean = (float) (K + m);
-	*hw = 0.45f * PSEL_SQRT(PSEL_DIV((float) ss, (float) (n - 3)));
+	*hw = PSEL_SQRT(PSEL_DIV((float) ss, (float) (n - 3)));	// one sd either side: two thirds of a clean stack, the bulk's scale to ~1 / sqrt(n)
 	return *hw > 0.f && *hw < FLT_MAX;
+}
+
+// the window's half-width in units of the bulk's sd, u = hw / sigma, when the window is NOT centred on the bulk:
+// its centre sits at the q-quantile (zq = ndtri(q)) and it holds the fraction f:  Phi(zq + u) - Phi(zq - u) = f.
+// Newton from the centred answer; only reached when outliers have dragged the mean off the bulk (|zq| > 0.4).
+SGPU_HD inline float psel_offcentre_u(float zq, float f, float u) {
+	for (int it = 0; it < 4; it++) {
+		const float a = zq + u, b = zq - u;
+		const float g = 0.5f * (erfcf(-a * 0.70710678f) - erfcf(-b * 0.70710678f)) - f;
+		const float dg = 0.39894228f * (expf(-0.5f * a * a) + expf(-0.5f * b * b));
+		if (!(dg > 1e-6f)) break;
+		u -= g / dg;
+		if (!(u > 0.05f)) u = 0.05f;
+	}
+	return u;
 }
 
 // after the count pass (c_neg samples below `mean`, c_in within hw of it): the windows.
 // 0: plan filled; 1: the count window swallowed nearly everything (scale still inflated) — count
 // again with the smaller *hw; 2: degenerate
-SGPU_HD inline int psel_plan_window(int n, float *meanp, float *hw, int c_neg, int c_in, bool tails, bool percentile,
+SGPU_HD inline int psel_plan_window(int n, float *meanp, float *hw, int c_neg, int c_in, bool tails, int mode,
 		float s0, float s1, int attempt, PselPlan *pl) {
 	const float fn = (float) n, mean = *meanp;
 	const float rfn = PSEL_DIV(1.f, fn);
 	float f = (float) c_in * rfn;
 	float q = ((float) c_neg + 0.5f) * rfn;
 	q = q < 0.03f ? 0.03f : (q > 0.97f ? 0.97f : q);
-	if (f >= 0.80f && attempt < 2) {	// several outliers: the bulk is a fraction of the window, and the mean sits off its middle
-		*hw *= 0.25f;
-		*meanp = mean - *hw * psel_ndtri(q);
+	const float zq = psel_ndtri(q);
+	if (f >= 0.93f && attempt < 3) {	// several outliers inflated the sd: the bulk is a fraction of the window (too little of it outside
+						// to tell its scale) and the mean sits off its middle: count again, about one bulk sd either side
+		if (f > 0.97f) {	// scale unknown: a quarter of the window, and a cautious step towards the median
+			*hw *= 0.25f;
+			*meanp = mean - 0.5f * *hw * zq;
+		} else {
+			float u = psel_ndtri(0.5f + 0.5f * f);
+			if (fabsf(zq) > 0.4f) u = psel_offcentre_u(zq, f, u);
+			*hw = PSEL_DIV(*hw, u);
+			*meanp = mean - *hw * zq;
+		}
 		return 1;
 	}
 	f = f < 0.05f ? 0.05f : (f > 0.95f ? 0.95f : f);
-	const float srob = PSEL_DIV(*hw, psel_ndtri(0.5f + 0.5f * f));	// scale of the bulk
-	const float p1 = mean - srob * psel_ndtri(q);		// where half of the samples are below
+	float u = psel_ndtri(0.5f + 0.5f * f);
+	if (fabsf(zq) > 0.4f) u = psel_offcentre_u(zq, f, u);
+	const float srob = PSEL_DIV(*hw, u);			// scale of the bulk
+	const float p1 = mean - srob * zq;			// where half of the samples are below
 	const float sq = PSEL_SQRT(fn);
 	const float wr = fmaxf(6.f, 3.0f * PSEL_SQRT(sq));	// half-width of the centre window in ranks
 	const float w = wr * srob * 2.5066283f * rfn;
 	float rlo = FLT_MAX, rhi = FLT_MAX;
 	if (tails) {
-		if (percentile) {	// thresholds median * sig (rejection_float.c:31-44), the median within w of p1
+		if (mode == 1) {	// percentile: thresholds median * sig (rejection_float.c:31-44), the median within w of p1
 			rlo = fabsf(p1) * s0 - 2.f * w; rhi = fabsf(p1) * s1 - 2.f * w;
 		} else {		// thresholds sig * sigma; the bulk's sigma is known to ~1.7 / sqrt(n) relative (1 sd)
-			const float mf = PSEL_DIV(sq, sq + 8.f);
+			const float mf = PSEL_DIV(sq, sq + 6.f);
 			rlo = mf * s0 * srob; rhi = mf * s1 * srob;
 		}
 		rlo = rlo > w ? rlo : w; rhi = rhi > w ? rhi : w;
@@ -191,7 +217,7 @@ SGPU_HD inline void psel_replan(int n, int cl, int cc, PselPlan *pl) {
 //   extract(on, plan, &below, &over)  fills the lane lists (nothing when !on); kept samples below plan.p1; lists overflowed
 //   classify(plan, &cc, &ccb, &nl, &m)  list entries inside the centre window / of those, below plan.p1 / entries below the window / all
 template <class P>
-SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool percentile, float s0, float s1, PselHdr &h) {
+SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, int mode, float s0, float s1, PselHdr &h) {	// mode: 0 sigma, 1 percentile
 	double S1, S2; float mn, mx; int n;
 	ps.sums(is_mean, &n, &S1, &S2, &mn, &mx);
 	h.n = n; h.S1 = S1; h.S2 = S2; h.K = 0.0; h.mn = mn; h.mx = mx; h.flags = 0; h.cl = 0; h.nl = 0; h.cc = 0; h.m = 0;
@@ -213,12 +239,12 @@ SGPU_HD __forceinline__ void psel_group(P &ps, int is_mean, bool tails, bool per
 	bool want = live && psel_plan_count(n, S1, S2, h.K, mn, mx, &mean, &hw);
 	bool all_centre = live && !want;
 #pragma unroll 1
-	for (int attempt = 0; attempt < 3; attempt++) {
+	for (int attempt = 0; attempt < 4; attempt++) {
 		if (!ps.any(want)) break;
 		int c_neg, c_in;
 		ps.count(mean, hw, &c_neg, &c_in);
 		if (want) {
-			const int r = psel_plan_window(n, &mean, &hw, c_neg, c_in, tails, percentile, s0, s1, attempt, &pl);
+			const int r = psel_plan_window(n, &mean, &hw, c_neg, c_in, tails, mode, s0, s1, attempt, &pl);
 			if (r == 0) want = false;
 			else if (r == 2) { want = false; all_centre = true; }
 		}

@@ -97,10 +97,10 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	p.layer_base = 0; p.pix_base = 0;
 	if (p.split) {
 		const size_t rec_bytes = (size_t) PSEL_REC_WORDS * sizeof(float);
-		size_t freeb = 0, totalb = 0;
-		SGPU_CUDA(ctx, cudaMemGetInfo(&freeb, &totalb));
 		size_t chunk_px = npix;
-		if (npix * rec_bytes > ctx->d_scratch_cap) {
+		if (npix * rec_bytes > ctx->d_scratch_cap) {	// (only then: cudaMemGetInfo under load can hold the launches up for milliseconds)
+			size_t freeb = 0, totalb = 0;
+			SGPU_CUDA(ctx, cudaMemGetInfo(&freeb, &totalb));
 			const size_t budget = ctx->d_scratch_cap + freeb / 2;
 			if (chunk_px * rec_bytes > budget) chunk_px = budget / rec_bytes;
 		}
@@ -111,15 +111,26 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 			rv = sgpu_ensure_scratch(ctx, chunk_px * rec_bytes);
 			if (rv) return rv;
 			p.records = (float *) ctx->d_scratch;
+			const char *te = getenv("SGPU_PSEL_TIMING");
+			const bool timing = te && te[0] == '1';
 			for (int layer = 0; layer < d.nb_layers; layer++) {
 				for (size_t base = 0; base < npix; base += chunk_px) {
 					const size_t n = npix - base < chunk_px ? npix - base : chunk_px;
 					p.layer_base = layer; p.pix_base = base;
 					dim3 grid((unsigned) ((n + pxc - 1) / pxc), 1);
+					cudaEvent_t ev[3] = { nullptr, nullptr, nullptr };
+					if (timing) { for (auto &e : ev) cudaEventCreate(&e); cudaEventRecord(ev[0], ctx->stream); }
 					rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm + shm_pad);
 					if (rv) return rv;
+					if (timing) cudaEventRecord(ev[1], ctx->stream);
 					rv = sgpu_launch_psel_finish(ctx, p, (unsigned) n);
 					if (rv) return rv;
+					if (timing) {	// SGPU_PSEL_TIMING=1: the two kernels' durations, on stderr (serializes the stream)
+						cudaEventRecord(ev[2], ctx->stream); cudaEventSynchronize(ev[2]);
+						float a = 0.f, b = 0.f; cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]);
+						fprintf(stderr, "psel layer %d pixels [%zu, +%zu): stack kernel %.3f ms, finish kernel %.3f ms\n", layer, base, n, a, b);
+						for (auto &e : ev) cudaEventDestroy(e);
+					}
 				}
 			}
 			p.layer_base = 0; p.pix_base = 0;

@@ -39,6 +39,7 @@ struct PselLane {
 	unsigned lcap;		// slots
 	int cnt;		// entries after the last extraction
 	unsigned pk;		// of which: centre | centre below p1 << 10 | low tail << 20 (classify)
+	float *rec;		// split form: where this pixel's entries go (global memory), or null
 	const double2 *coef;	// per-frame {scale, offset | mul} when the tile holds raw samples, else null
 	int norm_mode;		// 1 additive family, 2 multiplicative family (with coef)
 
@@ -160,11 +161,19 @@ struct PselLane {
 
 	__device__ __forceinline__ void classify(const PselPlan &pl, int *cc, int *ccb, int *nl, int *m) {
 		pk = 0;
+		int pre = cnt;		// entries of the lanes before this one (split form: the entries go to the pixel's record on the way;
+					// an extraction that is repeated simply writes them again)
+#pragma unroll
+		for (int d = 1; d < T; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, pre, d, T); if (t >= d) pre += o; }
+		pre -= cnt;
+		float *out = rec ? rec + PSEL_REC_HDR + pre : nullptr;
+		const int room = PSEL_REC_ENTRIES - pre;
 		for (int k = 0; k < cnt; k++) {
 			const float x = lds_f32(list0 + (unsigned) k * lstride);
 			const float d = x - pl.p1;
 			const bool in = fabsf(d) < pl.w, neg = d < 0.f;
 			pk += in ? (neg ? 1u + (1u << 10) : 1u) : (neg ? (1u << 20) : 0u);
+			if (out && k < room) out[k] = x;
 		}
 		// fields of 10 bits: a class with more than 1023 entries is far past what phase B sorts
 		const unsigned a = gsum(pk & 0x3ffu), b = gsum((pk >> 10) & 0x3ffu), l = gsum(pk >> 20);
@@ -312,9 +321,13 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 		ln.coef = raw_norm ? coef : nullptr;
 		ln.norm_mode = (p.normalize == SGPU_ADDITIVE || p.normalize == SGPU_ADDITIVE_SCALING) ? 1 : 2;
 		ln.list0 = smem_u32(lists + threadIdx.x); ln.lstride = NT * 4; ln.lcap = LCAP; ln.cnt = 0;
+		{
+			const size_t pixg = pix0 + (size_t) (sb * TILE_PX + px);
+			ln.rec = (p.split && pixg < npix) ? p.records + (pixg - p.pix_base) * PSEL_REC_WORDS : nullptr;
+		}
 		const int rt = p.is_mean ? p.rc.type : SGPU_NO_REJEC;
 		PselHdr h;
-		psel_group(ln, p.is_mean, rt == SGPU_SIGMA || rt == SGPU_PERCENTILE, rt == SGPU_PERCENTILE, p.rc.s0, p.rc.s1, h);
+		psel_group(ln, p.is_mean, rt == SGPU_SIGMA || rt == SGPU_PERCENTILE, rt == SGPU_PERCENTILE ? 1 : 0, p.rc.s0, p.rc.s1, h);
 		h.tid0 = (int) threadIdx.x - t;
 		if (p.dbg_stop == 2) return;
 		if (p.split) {
@@ -328,11 +341,6 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 			// a pixel with more entries than a record holds: its whole warp stays here and finishes below (B1, B2)
 			const bool stay = ln.any(live && h.m > PSEL_REC_ENTRIES);
 			float *rec = p.records + (pix - p.pix_base) * PSEL_REC_WORDS;
-			const int mine = (live && !stay && valid) ? ln.cnt : 0;
-			int pre = mine;		// entries of the lanes before this one
-#pragma unroll
-			for (int d = 1; d < T; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, pre, d, T); if (t >= d) pre += o; }
-			pre -= mine;
 			const uint4 q0 = make_uint4((unsigned) __double2loint(h.S1), (unsigned) __double2hiint(h.S1), (unsigned) __double2loint(h.S2), (unsigned) __double2hiint(h.S2));
 			const uint4 q1 = make_uint4((unsigned) __double2loint(h.K), (unsigned) __double2hiint(h.K), __float_as_uint(h.mn), __float_as_uint(h.mx));
 			const uint4 q2 = make_uint4(__float_as_uint(h.blo), __float_as_uint(h.bhi), (unsigned) h.n, (unsigned) h.cl);
@@ -342,8 +350,7 @@ stack_psel_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap)
 			else if (T >= 4) { if (t == 0) rq[0] = q0; else if (t == 1) rq[1] = q1; else if (t == 2) rq[2] = q2; else if (t == 3) rq[3] = q3; }
 			else if (T == 2) { if (t == 0) { rq[0] = q0; rq[2] = q2; } else { rq[1] = q1; rq[3] = q3; } }
 			else { rq[0] = q0; rq[1] = q1; rq[2] = q2; rq[3] = q3; }
-			for (int k = 0; k < mine; k++) rec[PSEL_REC_HDR + pre + k] = lds_f32(ln.list0 + (unsigned) k * ln.lstride);
-			if (!stay) return;
+			if (!stay) return;	// (the entries went to the record while they were classified)
 		}
 		// ---- B1: the group's entries, dealt out evenly over its lanes, sorted in registers (the
 		// lane-sort engine's networks) and written over the first rows of the pixel's (now dead) column ----

@@ -47,11 +47,12 @@ __global__ void __launch_bounds__(FIN_THREADS) stack_psel_finish_kernel(const St
 			float e[PSEL_REC_ENTRIES];
 #pragma unroll
 			for (int k = 0; k < PSEL_REC_ENTRIES / 4; k++) {
-				const uint4 v = __ldg(rq + PSEL_REC_HDR / 4 + k);
+				uint4 v = make_uint4(0u, 0u, 0u, 0u);
+				if (4 * k < h.m) v = __ldg(rq + PSEL_REC_HDR / 4 + k);	// nothing was written past entry m
 				e[4 * k] = 4 * k < h.m ? __uint_as_float(v.x) : SGPU_INF; e[4 * k + 1] = 4 * k + 1 < h.m ? __uint_as_float(v.y) : SGPU_INF;
 				e[4 * k + 2] = 4 * k + 2 < h.m ? __uint_as_float(v.z) : SGPU_INF; e[4 * k + 3] = 4 * k + 3 < h.m ? __uint_as_float(v.w) : SGPU_INF;
 			}
-			LocalNet<64>::template run<64>(e);
+			LocalNet<64>::template run<64>(e);	// (a 48-input network for the warps without a longer list was tried: the second copy of the code cost more than its 159 comparators saved)
 #pragma unroll
 			for (int k = 0; k < PSEL_REC_ENTRIES; k++) col.set(k, e[k]);
 		}

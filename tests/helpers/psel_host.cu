@@ -121,7 +121,7 @@ extern "C" int psel_host_pixel(int is_float, const void *stack, int N, int T, in
 	for (int i = 0; i < N; i++) hp.v[i % T][i / T] = o[i];
 	PselHdr h{};
 	const bool tails = is_mean && (rejtype == SGPU_SIGMA || rejtype == SGPU_PERCENTILE);
-	psel_group(hp, is_mean, tails, rejtype == SGPU_PERCENTILE, s0, s1, h);
+	psel_group(hp, is_mean, tails, rejtype == SGPU_PERCENTILE ? 1 : 0, s0, s1, h);
 	std::vector<float> colbuf(std::max(N, (int) PSEL_ROWS) + 3, -12345.f);
 	HostCol col{ colbuf.data() };
 	HostLists ls{ hp };

@@ -101,7 +101,8 @@ def synth_fill(n, c, h, w, dtype, seed, row0=0, full_h=None):
     ("C3", 200, 3, 6000, 4000, np.float32, 1003, dict(is_mean=False)),
     ("C2-sigma", 100, 1, 6248, 4176, np.float32, 1002, dict(rejection=O.SIGMA, sig=(3, 3), create_rejmaps=True)),
     ("C5-sigma", 500, 1, 9576, 6388, np.uint16, 1005, dict(rejection=O.SIGMA, sig=(3, 3), create_rejmaps=True)),
-], ids=["target", "C3", "C2-sigma", "C5-sigma"])
+    ("C2-norm-sigma", 100, 1, 6248, 4176, np.float32, 1002, dict(rejection=O.SIGMA, sig=(3, 3), create_rejmaps=True, normalize=O.ADDITIVE_SCALING)),
+], ids=["target", "C3", "C2-sigma", "C5-sigma", "C2-norm-sigma"])
 def test_config_strips(ref, name, n, c, w, full_h, dtype, seed, kw):
     """the frames the benchmark stacks (sgpu_synth_fill), full width, real depth, 16 rows from the
     middle of the image, against the reference's own code"""
@@ -109,10 +110,17 @@ def test_config_strips(ref, name, n, c, w, full_h, dtype, seed, kw):
     rows = 16
     fr = synth_fill(n, c, rows, w, dtype, seed, row0=full_h // 2, full_h=full_h)
     host = tp.to_np(fr)
+    kw = dict(kw)
     args = sb.StackingArgs(method=sb.stack_median if kw.get("is_mean") is False else sb.stack_mean_with_rejection, frames=fr,
                            type_of_rejection=kw.get("rejection", O.NO_REJEC), sig=kw.get("sig", (3, 3)),
                            create_rejmaps=kw.get("create_rejmaps", False), engine=PSEL)
-    assert sb.main_stack(args) == 0, getattr(args, "error", "")
+    if kw.get("normalize"):     # the configuration's real coefficients: do_normalization on the strip's own statistics
+        args.normalize = kw["normalize"]
+        assert sb.do_normalization(args) == 0
+        kw.update(scale=args.coeff.scale.copy(), offset=args.coeff.offset.copy(), mul=args.coeff.mul.copy())
+        assert args.method(args) == 0, getattr(args, "error", "")
+    else:
+        assert sb.main_stack(args) == 0, getattr(args, "error", "")
     assert args.ctx.last_engine == "stack_psel_kernel"
     handed = args.ctx.handovers
     r = args.result
