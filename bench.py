@@ -477,7 +477,11 @@ def run_ours(args, wl):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": kernel_name, "kernel_ms": kernel_ms_max,
                          "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0,
-                         "note": "per GPU: the stack kernel of rank 0's rows (slowest rank's time)" if world > 1 else "the stack kernel"},
+                         "note": ("per GPU: the stack call of rank 0's rows (slowest rank's time)" if world > 1 else "the stack call")
+                                 + ("; stack_psel_kernel (streaming passes, leaves a record per pixel) + stack_psel_finish_kernel (sort + rejection, "
+                                    "one thread per pixel) + the exact engine on the hand-over list: `achieved` is the algorithmic bytes over the time of "
+                                    "all three, `traffic` the DRAM bytes of the first two (the records' round trip is on top of the samples)"
+                                    if kernel_name == "stack_psel_kernel" else "")},
             "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line))

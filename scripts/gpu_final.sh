@@ -11,4 +11,5 @@ for wl in C1 C2 C3 C4 C5; do
   timeout 900 python bench.py --workload $wl --no-e2e > gpurun_out/${TAG}_bench_$wl.json 2> gpurun_out/${TAG}_bench_$wl.err; echo "$wl rc=$? $(python -c "import json; d=json.load(open('gpurun_out/${TAG}_bench_$wl.json')); print(d['ms_per_step'], round(d['roofline']['frac'],4), d['roofline']['kernel'], d['detail'], d['cpu_baseline']['value'])")"
 done
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:stack_ -c 24 --csv --log-file gpurun_out/${TAG}_launches_target.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/${TAG}_ncu_ll.log 2>&1; echo "launch list rc=$?"
-timeout 900 ncu --set full --import-source on --clock-control none -k regex:stack_psel -s 3 -c 1 -o gpurun_out/${TAG}_target_full python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --height 1024 > gpurun_out/${TAG}_ncufull.log 2>&1; echo "ncu full rc=$?"
+timeout 900 ncu --set full --import-source on --clock-control none -k regex:stack_psel_kernel -s 3 -c 1 -o gpurun_out/${TAG}_target_full python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --height 1024 > gpurun_out/${TAG}_ncufull.log 2>&1; echo "ncu full rc=$?"
+timeout 900 ncu --set full --import-source on --clock-control none -k regex:stack_psel_finish -s 3 -c 1 -o gpurun_out/${TAG}_target_finish_full python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --height 1024 > gpurun_out/${TAG}_ncufull2.log 2>&1; echo "ncu full (finish kernel) rc=$?"
