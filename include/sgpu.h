@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SGPU_ABI_VERSION 3
+#define SGPU_ABI_VERSION 4
 
 enum {	/* stacking.h:18-24 */
 	SGPU_OK = 0,
@@ -122,6 +122,26 @@ void *sgpu_block_device_ptr(sgpu_block *blk);
  * `host_frame` should be pinned for the copy to overlap. */
 int sgpu_block_upload_frame(sgpu_block *blk, int frame, const void *host_frame, int frame_height,
 		int row0, int shifty);
+
+/* ---- feather masks and drizzle weights ---------------------------------------
+ * Two optional float plane sets of a block, what data->mask[frame] and data->drizz[frame] are in the reference
+ * (stack_read_block_data, median_and_mean.c:483-542): the feather mask of every frame, [nb_frames][height][width]
+ * (one plane per frame, shared by the layers: the reference reads the same mask file for each channel block), and
+ * the drizzle weights, [nb_frames][nb_layers][height][width].  With either present a mean stack takes the weighted
+ * combine with n = drizzle * mask * weight per sample (mean_and_reject, :1043-1070, :1060-1066; gathered at the
+ * sample's shifted column, :1687-1692), and samples with a zero drizzle weight are dropped with the null samples
+ * before the rejection (rejection_float.c:116-126, median_and_mean.c:716-726).  Median stacks ignore them. */
+enum { SGPU_PLANE_MASK = 0, SGPU_PLANE_DRIZZLE = 1 };
+/* rows of one host plane set of one frame ([frame_height][width] mask, [nb_layers][frame_height][width] drizzle
+ * weights) into the block, geometry as sgpu_block_upload_frame; the plane set is allocated (zeroed) on first use */
+int sgpu_block_upload_weight_plane(sgpu_block *blk, int which, int frame, const float *host_planes,
+		int frame_height, int row0, int shifty);
+/* or: use caller-owned device memory of exactly those shapes (NULL: none) */
+int sgpu_block_set_weight_planes(sgpu_block *blk, float *d_mask, float *d_drizzle);
+/* the mask normalization of :513-521 on the block's mask planes, in place: a distance above feather_dist becomes
+ * 1, one below it the smoothstep ramp of blending.c:34-50 (get_ramped_value, 1001-point table by truncation),
+ * zero stays zero.  Upload the up-scaled distance masks (cvUpscaleBlendMask's output), then call this once. */
+int sgpu_block_mask_ramp(sgpu_block *blk, int feather_dist);
 
 /* ---- raw FITS data units ----------------------------------------------------
  * Replaces, for uncompressed primary-HDU images, the read leg of stack_read_block_data

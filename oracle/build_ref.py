@@ -48,6 +48,8 @@ RANGES = {
     "mm_rejection_u16":  ("src/stacking/median_and_mean.c", 590, 1101, None),
     "mm_noise_weights":  ("src/stacking/median_and_mean.c", 1111, 1135, None),
     "mm_linfit_precalc": ("src/stacking/median_and_mean.c", 1491, 1499, None),
+    "mm_mask_ramp":      ("src/stacking/median_and_mean.c", 513, 521, None),
+    "blend_ramp":        ("src/stacking/blending.c", 30, 50, None),
     "stats_u16_sd_mad":  ("src/algos/statistics.c", 100, 154, None),
     "statsf_mad_bwmv":   ("src/algos/statistics_float.c", 79, 127, None),
     "statsf_ikss":       ("src/algos/statistics_float.c", 199, 229, None),

@@ -40,6 +40,8 @@ class _StackParams(C.Structure):
         ("nthreads", C.c_int),
         ("max_rows", C.c_long),
         ("source_bitpix", C.c_int),
+        ("mask", C.c_void_p), ("drizz", C.c_void_p),
+        ("feather_dist", C.c_int), ("drizzle", C.c_int),
     ]
 
 
@@ -176,7 +178,8 @@ class Oracle:
     def stack(self, frames, *, is_mean=True, rejection=NO_REJEC, sig=(3.0, 3.0), crit=None,
               normalize=NO_NORM, scale=None, offset=None, mul=None, weights=None,
               shiftx=None, shifty=None, output_norm=False, use_32bit_output=True,
-              create_rejmaps=False, merge_rejmaps=False, nthreads=None, max_rows=0, source_bitpix=0):
+              create_rejmaps=False, merge_rejmaps=False, nthreads=None, max_rows=0, source_bitpix=0,
+              masks=None, feather_dist=0, drizzle_weights=None):
         """frames: ndarray [N][C][H][W] float32|uint16 (memory / FITS row order).
         Returns dict(out, rej_low, rej_high, irej[3][2])."""
         frames = np.ascontiguousarray(frames)
@@ -206,6 +209,9 @@ class Oracle:
         p.nthreads = nthreads or os.cpu_count() or 1
         p.max_rows = max_rows
         p.source_bitpix = source_bitpix
+        # feather masks [N][H][W] (distances, before the ramp) / drizzle weights [N][C][H][W] (median_and_mean.c:483-542)
+        p.mask, p.feather_dist = arr(masks, np.float32), int(feather_dist if masks is not None else 0)
+        p.drizz, p.drizzle = arr(drizzle_weights, np.float32), int(drizzle_weights is not None)
         out = np.zeros((Cn, H, W), dtype=np.float32 if use_32bit_output else np.uint16)
         rl = np.zeros((Cn, H, W), dtype=np.uint16) if create_rejmaps else None
         rh = np.zeros((Cn, H, W), dtype=np.uint16) if (create_rejmaps and not merge_rejmaps) else None

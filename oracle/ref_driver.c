@@ -54,6 +54,7 @@ static int FnCompare_double(const void *, const void *);
 #include "gen/quant_diffmeansigma.inc" /* FnDiffMeanSigma_int, FnDiffMeanSigma_float */
 #include "gen/quant_noise1.inc"      /* FnNoise1_ushort, FnNoise1_float, FnCompare_double */
 #include "gen/norm_factors.inc"      /* compute_factors_from_estimators */
+#include "gen/blend_ramp.inc"        /* RAMP_PACE, init_ramp, get_ramped_value */
 
 /* dead helper symbols sorting.c's strcompare() references */
 void g_free(void *p) { free(p); }
@@ -71,6 +72,8 @@ static void setup_block(struct _data_block *blk, int is_float, int N, int rejtyp
 	blk->rejected = calloc(N + 1, sizeof(int));
 	blk->xf = calloc(N + 1, sizeof(float));
 	blk->yf = calloc(N + 1, sizeof(float));
+	blk->mstack = calloc(N + 1, sizeof(float));
+	blk->dstack = calloc(N + 1, sizeof(float));
 	if (rejtype == LINEARFIT) {
 		struct _data_block *data_pool = blk;
 		int i = 0, nb_frames = N;
@@ -80,7 +83,7 @@ static void setup_block(struct _data_block *blk, int is_float, int N, int rejtyp
 
 static void free_block(struct _data_block *blk) {
 	free(blk->stack); free(blk->o_stack); free(blk->w_stack);
-	free(blk->rejected); free(blk->xf); free(blk->yf);
+	free(blk->rejected); free(blk->xf); free(blk->yf); free(blk->mstack); free(blk->dstack);
 }
 
 static void setup_args(struct stacking_args *args, int N, int rejtype, float s0, float s1,
@@ -125,7 +128,24 @@ typedef struct {
 	int nthreads;
 	long max_rows;				/* planner budget; <=0: whole image */
 	int source_bitpix;			/* seq->bitpix; 8 (BYTE_IMG): normalize_to16bit */
+	const float *mask;			/* [N][H][W] up-scaled distance masks (data->mask[frame] before :513-521) or NULL */
+	const float *drizz;			/* [N][C][H][W] drizzle weights (data->drizz[frame]) or NULL */
+	int feather_dist, drizzle;		/* args->feather_dist (> 0: masking), args->drizzle */
 } ref_stack_params;
+
+/* the mask normalization stack_read_block_data applies to a block it has just read
+ * (median_and_mean.c:513-521, the reference's own lines), here on whole planes */
+static void ref_normalize_masks(float **planes, int N, long H, long W, int feather_dist) {
+	struct stacking_args a_, *args = &a_;
+	struct _image_block b_, *my_block = &b_;
+	struct _data_block d_, *data = &d_;
+	long naxes[3] = { W, H, 1 };
+	a_.feather_dist = feather_dist; b_.height = H; d_.mask = planes;
+	init_ramp();
+	for (int frame = 0; frame < N; frame++) {
+#include "gen/mm_mask_ramp.inc"
+	}
+}
 
 /* Restatement of the block loop of stack_mean_or_median (median_and_mean.c:1552-1760) on
  * in-RAM frames laid out [N][C][H][W] in memory (FITS, bottom-up) row order; `out` is
@@ -136,6 +156,7 @@ typedef struct {
 	const ref_stack_params *p; const void *frames; void *out; WORD *rej_low, *rej_high;
 	struct _image_block *blocks; struct _data_block *pool; struct stacking_args *args;
 	uint64_t *brej;	/* [nb_blocks][2] */
+	float **mask;	/* [N] normalized mask planes, or NULL */
 } ref_stack_ctx;
 
 /* provided by ref_omp.c (the only TU of the pinned build compiled with -fopenmp): the
@@ -172,6 +193,9 @@ static void ref_stack_block(int b, int tid, void *vctx) {
 						size_t idx = ((size_t) f * C + layer) * plane + (size_t) sr * W + sx;
 						if (p->is_float) fpixel = ((const float *) frames)[idx];
 						else pixel = ((const WORD *) frames)[idx];
+						/* median_and_mean.c:1687-1692 (outside the frame the reference `continue`s before these lines) */
+						if (cx->mask) data->mstack[f] = cx->mask[f][(size_t) sr * W + sx];
+						if (args->drizzle) data->dstack[f] = p->drizz[idx];
 					}
 					double tmp;
 					const double sc = p->scale ? p->scale[layer * N + f] : 1.0;
@@ -254,9 +278,20 @@ int ref_stack(const ref_stack_params *p, const void *frames, void *out,
 	for (int t = 0; t < nthreads; t++) setup_block(&pool[t], p->is_float, N, p->rejtype);
 	struct stacking_args args;
 	setup_args(&args, N, p->rejtype, p->sig[0], p->sig[1], p->crit, p->weights);
+	float **mask = NULL;
+	if (p->is_mean && p->feather_dist > 0 && p->mask) {
+		args.feather_dist = p->feather_dist;
+		mask = calloc(N, sizeof(float *));
+		for (int f = 0; f < N; f++) {
+			mask[f] = malloc((size_t) H * W * sizeof(float));
+			memcpy(mask[f], p->mask + (size_t) f * H * W, (size_t) H * W * sizeof(float));
+		}
+		ref_normalize_masks(mask, N, H, W, p->feather_dist);
+	}
+	args.drizzle = p->is_mean && p->drizzle && p->drizz;
 	memset(irej, 0, 6 * sizeof(uint64_t));
 	ref_stack_ctx cx = { p, frames, out, rej_low, rej_high, blocks, pool, &args,
-		calloc(2 * (size_t) nb_blocks, sizeof(uint64_t)) };
+		calloc(2 * (size_t) nb_blocks, sizeof(uint64_t)), mask };
 	ref_parallel_for(nb_blocks, nthreads, ref_stack_block, &cx);
 	if (p->is_mean && p->rejtype != NO_REJEC)
 		for (int b = 0; b < nb_blocks; b++) {
@@ -271,6 +306,7 @@ int ref_stack(const ref_stack_params *p, const void *frames, void *out,
 	}
 	for (int t = 0; t < nthreads; t++) free_block(&pool[t]);
 	free(pool); free(blocks);
+	if (mask) { for (int f = 0; f < N; f++) free(mask[f]); free(mask); }
 	return 0;
 }
 

@@ -285,10 +285,11 @@ static void confirm(float *ox, int *oi, int *oo, int n, double median, int *flag
 
 /* src/stacking/rejection_float.c:100-354 apply_rejection_float.  `stack` is modified in place
  * exactly as the reference leaves it (callers use that state). */
-static int reject_f32(float *stack, int nb, const rej_cfg *c, int *flag, int rej[2]) {
+static int reject_f32(float *stack, int nb, const rej_cfg *c, int *flag, int rej[2], const float *ds) {
 	int N = nb, kept = 0, r = 0, first = 1, changed;
 	double median = 0.0;
-	for (int f = 0; f < N; f++) if (stack[f] != 0.f) { if (f != kept) stack[kept] = stack[f]; kept++; }	/* :128-135 */
+	/* null pixels, and with drizzle the samples of null drizzle weight as well (:116-135) */
+	for (int f = 0; f < N; f++) if (stack[f] != 0.f && (!ds || ds[f] != 0.f)) { if (f != kept) stack[kept] = stack[f]; kept++; }
 	if (kept <= 1) return kept;								/* :140 */
 	const int removed = N - kept;
 	N = kept;
@@ -409,10 +410,11 @@ static int sclip_w(u16 px, float lo, float hi, float sigma, float med, int rej[2
 }
 
 /* src/stacking/median_and_mean.c:703-954 apply_rejection_ushort */
-static int reject_u16(u16 *stack, int nb, const rej_cfg *c, int *flag, int rej[2]) {
+static int reject_u16(u16 *stack, int nb, const rej_cfg *c, int *flag, int rej[2], const float *ds) {
 	int N = nb, kept = 0, r = 0, first = 1, changed;
 	float median = 0.f;
-	for (int f = 0; f < N; f++) if (stack[f] != 0) { if (f != kept) stack[kept] = stack[f]; kept++; }	/* :728-735 */
+	/* :716-735 (null pixels; with drizzle also the samples of null drizzle weight) */
+	for (int f = 0; f < N; f++) if (stack[f] != 0 && (!ds || ds[f] != 0.f)) { if (f != kept) stack[kept] = stack[f]; kept++; }
 	if (kept <= 1) return kept;
 	const int removed = N - kept;
 	N = kept;
@@ -526,19 +528,28 @@ static int reject_u16(u16 *stack, int nb, const rej_cfg *c, int *flag, int rej[2
 }
 
 /* ------------------------------------------------------------------ combine */
+/* the weight of one sample in the weighted combine: n = 1 * drizzle * mask * frame weight, in this
+ * order (median_and_mean.c:998-1004, :1060-1066); ms / ds: the pixel's gathered mask / drizzle stacks */
+static double sample_weight(const double *w, const float *ms, const float *ds, int f) {
+	double n = 1.;
+	if (ds) n *= ds[f];
+	if (ms) n *= ms[f];
+	if (w) n *= w[f];
+	return n;
+}
 /* src/stacking/median_and_mean.c:956-1101 mean_and_reject.  `orig` is the untouched copy of the
  * stack (o_stack, rejection_float.c:114); weights == NULL means NO_WEIGHT. */
 static double combine_f32(float *stack, const float *orig, int nb, const rej_cfg *c,
-		const double *w, int *flag, int rej[2]) {
-	int kept = reject_f32(stack, nb, c, flag, rej);
+		const double *w, int *flag, int rej[2], const float *ms, const float *ds) {
+	int kept = reject_f32(stack, nb, c, flag, rej, ds);
 	if (kept == 0) return orc_quickmedian_float(stack, nb);					/* :1040-1041 */
-	if (w) {										/* :1043-1082 */
+	if (w || ms || ds) {									/* :1043-1082 */
 		float pmin = FLT_MAX, pmax = -FLT_MAX;
 		for (int f = 0; f < kept; f++) { if (pmin > stack[f]) pmin = stack[f]; if (pmax < stack[f]) pmax = stack[f]; }
 		double sum = 0.0, norm = 0.0;
 		for (int f = 0; f < nb; f++) {
 			float v = orig[f];
-			if (v >= pmin && v <= pmax && v != 0.f) { sum += (double) v * w[f]; norm += w[f]; }
+			if (v >= pmin && v <= pmax && v != 0.f) { const double n = sample_weight(w, ms, ds, f); sum += (double) v * n; norm += n; }
 		}
 		if (norm == 0. || sum == 0.) {
 			sum = 0.;
@@ -552,16 +563,16 @@ static double combine_f32(float *stack, const float *orig, int nb, const rej_cfg
 	return sum / (double) kept;
 }
 static double combine_u16(u16 *stack, const u16 *orig, int nb, const rej_cfg *c,
-		const double *w, int *flag, int rej[2]) {
-	int kept = reject_u16(stack, nb, c, flag, rej);
+		const double *w, int *flag, int rej[2], const float *ms, const float *ds) {
+	int kept = reject_u16(stack, nb, c, flag, rej, ds);
 	if (kept == 0) return orc_quickmedian(stack, nb);					/* :964-965 */
-	if (w) {										/* :967-1021 */
+	if (w || ms || ds) {									/* :967-1021 */
 		u16 pmin = 65535, pmax = 0;
 		for (int f = 0; f < kept; f++) { if (pmin > stack[f]) pmin = stack[f]; if (pmax < stack[f]) pmax = stack[f]; }
 		double sum = 0.0, norm = 0.0;
 		for (int f = 0; f < nb; f++) {
 			u16 v = orig[f];
-			if (v >= pmin && v <= pmax && v > 0) { sum += (double) v * w[f]; norm += w[f]; }
+			if (v >= pmin && v <= pmax && v > 0) { const double n = sample_weight(w, ms, ds, f); sum += (double) v * n; norm += n; }
 		}
 		if (norm == 0. || sum == 0.) {
 			sum = 0.;
@@ -586,7 +597,7 @@ double orc_mean_and_reject(int is_float, const void *stack, int N, int rejtype, 
 	void *s = malloc((N + 1) * es), *o = malloc((N + 1) * es);
 	memcpy(s, stack, N * es); memcpy(o, stack, N * es);
 	rej[0] = rej[1] = 0;
-	double m = is_float ? combine_f32(s, o, N, &c, w, flag, rej) : combine_u16(s, o, N, &c, w, flag, rej);
+	double m = is_float ? combine_f32(s, o, N, &c, w, flag, rej, NULL, NULL) : combine_u16(s, o, N, &c, w, flag, rej, NULL, NULL);
 	free(s); free(o); free(flag);
 	return m;
 }
@@ -596,7 +607,7 @@ int orc_apply_rejection_float(float *stack, int N, int rejtype, float s0, float 
 	if (rejtype == R_LINEARFIT) orc_linfit_consts(N, &c.m_x, &c.m_dx2);
 	int *flag = calloc(N + 1, sizeof(int));
 	rej[0] = rej[1] = 0;
-	int kept = reject_f32(stack, N, &c, flag, rej);
+	int kept = reject_f32(stack, N, &c, flag, rej, NULL);
 	free(flag);
 	return kept;
 }
@@ -616,7 +627,21 @@ typedef struct {
 	int nthreads;
 	long max_rows;				/* unused by the restatement (kept for ABI parity with ref_stack) */
 	int source_bitpix;			/* seq->bitpix; 8 (BYTE_IMG): normalize_to16bit */
+	const float *mask;			/* [N][H][W] up-scaled distance masks (data->mask[frame] before :513-521) or NULL */
+	const float *drizz;			/* [N][C][H][W] drizzle weights (data->drizz[frame]) or NULL */
+	int feather_dist, drizzle;		/* args->feather_dist (> 0: masking), args->drizzle */
 } orc_stack_params;
+
+/* the mask normalization of stack_read_block_data (median_and_mean.c:513-521) with the ramp table of
+ * blending.c:34-50 (r^3 (6 r^2 - 15 r + 10) at 1001 points, looked up by truncation) */
+static float orc_mask_ramp(float v, float distf, float invdistf) {
+	if (!v) return v;
+	if (v > distf) return 1.f;
+	const int index = (int) ((v * invdistf) * 1000);
+	const float norm = 1.f / (float) 1000;
+	const float r = (float) index * norm;
+	return r * r * r * (6.f * r * r - 15.f * r + 10.f);
+}
 
 /* src/stacking/median_and_mean.c:557-582; NB the min/max scan starts at index 1 (:566) */
 void orc_norm_to_0_1(float *d, long W, long H, long C) {
@@ -649,6 +674,9 @@ int orc_stack(const orc_stack_params *p, const void *frames, void *out,
 		size_t es = p->is_float ? 4 : 2;
 		void *stack = malloc((N + 1) * es), *orig = malloc((N + 1) * es);
 		int *flag = calloc(N + 1, sizeof(int));
+		const int masking = p->is_mean && p->feather_dist > 0 && p->mask, drizzle = p->is_mean && p->drizzle && p->drizz;
+		float *ms = masking ? calloc(N + 1, sizeof(float)) : NULL, *ds = drizzle ? calloc(N + 1, sizeof(float)) : NULL;
+		const float distf = (float) p->feather_dist, invdistf = 1.f / distf;
 		uint64_t loc[6] = { 0, 0, 0, 0, 0, 0 };
 #pragma omp for schedule(dynamic, 4) collapse(2)
 		for (int layer = 0; layer < C; layer++) for (long r = 0; r < H; r++) {
@@ -661,6 +689,10 @@ int orc_stack(const orc_stack_params *p, const void *frames, void *out,
 					if (inside) {
 						size_t idx = ((size_t) f * C + layer) * plane + (size_t) sr * W + sx;
 						if (p->is_float) fpx = ((const float *) frames)[idx]; else px = ((const u16 *) frames)[idx];
+						/* :1687-1692: the mask / drizzle samples are gathered at the same (shifted) place; outside the
+						 * frame the reference leaves stale values, which nothing reads (the sample is null) */
+						if (ms) ms[f] = orc_mask_ramp(p->mask[(size_t) f * plane + (size_t) sr * W + sx], distf, invdistf);
+						if (ds) ds[f] = p->drizz[idx];
 					}
 					const double sc = p->scale ? p->scale[layer * N + f] : 1.0;
 					double tmp;
@@ -689,8 +721,8 @@ int orc_stack(const orc_stack_params *p, const void *frames, void *out,
 					int rej[2] = { 0, 0 };
 					memcpy(orig, stack, N * es);
 					const double *w = p->weights ? p->weights + (size_t) layer * N : NULL;
-					result = p->is_float ? combine_f32(stack, orig, N, &c, w, flag, rej)
-							     : combine_u16(stack, orig, N, &c, w, flag, rej);
+					result = p->is_float ? combine_f32(stack, orig, N, &c, w, flag, rej, ms, ds)
+							     : combine_u16(stack, orig, N, &c, w, flag, rej, ms, ds);
 					loc[layer * 2] += rej[0]; loc[layer * 2 + 1] += rej[1];
 					if (p->create_rejmaps) {
 						if (p->merge_rejmaps) rej_low[o] = trunc_word(rej[0] + rej[1]);
@@ -711,7 +743,7 @@ int orc_stack(const orc_stack_params *p, const void *frames, void *out,
 		}
 #pragma omp critical
 		for (int i = 0; i < 6; i++) tot[i] += loc[i];
-		free(stack); free(orig); free(flag);
+		free(stack); free(orig); free(flag); free(ms); free(ds);
 	}
 	for (int i = 0; i < 6; i++) irej[i] = (p->is_mean && p->rejtype != R_NONE) ? tot[i] : 0;	/* :1748 */
 	if (p->use_32bit_output && p->output_norm) orc_norm_to_0_1(out, W, H, C);			/* :1774-1775 */

@@ -7,6 +7,7 @@ LIB_PATH = os.environ.get("SGPU_LIB") or os.path.join(HERE, "libsgpu.so")
 
 
 SIMPLE_SUM, SIMPLE_MAX, SIMPLE_MIN = 0, 1, 2      # include/sgpu.h SGPU_SIMPLE_*
+PLANE_MASK, PLANE_DRIZZLE = 0, 1                  # include/sgpu.h SGPU_PLANE_*
 
 
 class SgpuError(RuntimeError):
@@ -78,6 +79,9 @@ SIGNATURES = {
     "sgpu_block_destroy": (None, [P]),
     "sgpu_block_device_ptr": (P, [P]),
     "sgpu_block_upload_frame": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int]),
+    "sgpu_block_upload_weight_plane": (C.c_int, [P, C.c_int, C.c_int, P, C.c_int, C.c_int, C.c_int]),
+    "sgpu_block_set_weight_planes": (C.c_int, [P, P, P]),
+    "sgpu_block_mask_ramp": (C.c_int, [P, C.c_int]),
     "sgpu_fits_probe": (C.c_int, [C.c_char_p, C.POINTER(FitsInfo)]),
     "sgpu_block_upload_fits": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "sgpu_block_upload_fits_fd": (C.c_int, [P, C.c_int, C.c_int, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -185,7 +185,11 @@ int sgpu_block_wrap(sgpu_ctx *ctx, const sgpu_block_desc *desc, void *dev, sgpu_
 
 void sgpu_block_destroy(sgpu_block *b) {
 	if (!b) return;
-	if (b->owned && b->dev) { cudaStreamSynchronize(b->ctx->stream); cudaFree(b->dev); }
+	const bool own = (b->owned && b->dev) || (b->mask_owned && b->mask) || (b->drizz_owned && b->drizz);
+	if (own) cudaStreamSynchronize(b->ctx->stream);
+	if (b->owned && b->dev) cudaFree(b->dev);
+	if (b->mask_owned && b->mask) cudaFree(b->mask);
+	if (b->drizz_owned && b->drizz) cudaFree(b->drizz);
 	delete b;
 }
 
@@ -210,6 +214,59 @@ int sgpu_block_upload_frame(sgpu_block *b, int frame, const void *host, int fram
 				(size_t) (hi - lo) * rowb, cudaMemcpyDefault, ctx->stream));
 	}
 	return SGPU_OK;
+}
+
+/* ---- feather masks / drizzle weights: two more float plane sets of the block (median_and_mean.c:483-542) ---- */
+static size_t weight_plane_floats(const sgpu_block *b, int which) {
+	return (size_t) b->d.nb_frames * (which == SGPU_PLANE_DRIZZLE ? b->d.nb_layers : 1) * b->plane();
+}
+
+int sgpu_block_set_weight_planes(sgpu_block *b, float *d_mask, float *d_drizzle) {
+	if (!b) return SGPU_GENERIC_ERROR;
+	if ((b->mask_owned && b->mask) || (b->drizz_owned && b->drizz)) cudaStreamSynchronize(b->ctx->stream);
+	if (b->mask_owned && b->mask) cudaFree(b->mask);
+	if (b->drizz_owned && b->drizz) cudaFree(b->drizz);
+	b->mask = d_mask; b->drizz = d_drizzle; b->mask_owned = b->drizz_owned = false;
+	return SGPU_OK;
+}
+
+int sgpu_block_upload_weight_plane(sgpu_block *b, int which, int frame, const float *host, int frame_height, int row0, int shifty) {
+	if (!b || !host) return SGPU_GENERIC_ERROR;
+	sgpu_ctx *ctx = b->ctx;
+	const sgpu_block_desc &d = b->d;
+	if (which != SGPU_PLANE_MASK && which != SGPU_PLANE_DRIZZLE) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "unknown weight plane kind %d", which);
+	if (frame < 0 || frame >= d.nb_frames) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d out of range", frame);
+	float *&set = which == SGPU_PLANE_MASK ? b->mask : b->drizz;
+	bool &owned = which == SGPU_PLANE_MASK ? b->mask_owned : b->drizz_owned;
+	if (!set) {	// first upload: the plane set comes into being zeroed (the reference callocs its pool, :1402-1462)
+		SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+		const size_t bytes = weight_plane_floats(b, which) * 4;
+		cudaError_t e = cudaMalloc(&set, bytes ? bytes : 16);
+		if (e != cudaSuccess) { set = nullptr; return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "cannot allocate %zu bytes of HBM for the %s planes: %s", bytes, which == SGPU_PLANE_MASK ? "mask" : "drizzle weight", cudaGetErrorString(e)); }
+		owned = true;
+		SGPU_CUDA(ctx, cudaMemsetAsync(set, 0, bytes ? bytes : 16, ctx->stream));
+	}
+	const int layers = which == SGPU_PLANE_DRIZZLE ? d.nb_layers : 1;
+	const size_t rowb = (size_t) d.width * 4;
+	long lo = (long) shifty - row0; if (lo < 0) lo = 0;
+	long hi = (long) frame_height + shifty - row0; if (hi > d.height) hi = d.height;
+	for (int l = 0; l < layers; l++) {
+		char *dst = (char *) (set + ((size_t) frame * layers + l) * b->plane());
+		const char *src = (const char *) host + (size_t) l * frame_height * rowb;
+		if (hi <= lo) { SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) d.height * rowb, ctx->stream)); continue; }
+		if (lo > 0) SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) lo * rowb, ctx->stream));
+		if (hi < d.height) SGPU_CUDA(ctx, cudaMemsetAsync(dst + (size_t) hi * rowb, 0, (size_t) (d.height - hi) * rowb, ctx->stream));
+		SGPU_CUDA(ctx, cudaMemcpyAsync(dst + (size_t) lo * rowb, src + (size_t) (row0 + lo - shifty) * rowb,
+				(size_t) (hi - lo) * rowb, cudaMemcpyDefault, ctx->stream));
+	}
+	return SGPU_OK;
+}
+
+int sgpu_block_mask_ramp(sgpu_block *b, int feather_dist) {
+	if (!b) return SGPU_GENERIC_ERROR;
+	if (!b->mask) return sgpu_fail(b->ctx, SGPU_GENERIC_ERROR, "the block has no mask planes");
+	if (feather_dist <= 0) return sgpu_fail(b->ctx, SGPU_GENERIC_ERROR, "feather distance must be positive");
+	return sgpu_launch_mask_ramp(b->ctx, b->mask, weight_plane_floats(b, SGPU_PLANE_MASK), feather_dist);
 }
 
 /* ---- stacking ---- */
@@ -278,6 +335,12 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
 	ctx->list_used = false;
 	sgpu_stack_args forced;
+	if (a->is_mean && (blk->mask || blk->drizz)) {
+		// feather masks / drizzle weights: per-sample weights in the combine and, for drizzle, in what counts as a null
+		// sample.  Served by the exact engine (the others have no plane loads); asking for another one is an error.
+		if (a->engine != 0 && a->engine != 1) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "mask / drizzle weight planes are served by the exact engine only");
+		forced = *a; forced.engine = 1; a = &forced;
+	} else
 	if (a->engine == 0) if (const char *e = getenv("SGPU_ENGINE")) {	// tuning aid: force an engine from the environment
 		forced = *a; forced.engine = atoi(e);
 		if ((forced.engine == 2 && sgpu_sorted_supports(blk->d, a)) || (forced.engine == 5 && sgpu_lsort_supports(blk->d, a)) ||

@@ -37,6 +37,9 @@ struct sgpu_block {
 	sgpu_block_desc d{};
 	void *dev = nullptr;
 	bool owned = false;
+	// optional per-sample weight planes (data->mask[frame] / data->drizz[frame], median_and_mean.c:483-542)
+	float *mask = nullptr, *drizz = nullptr;	// [N][H][W] / [N][C][H][W]
+	bool mask_owned = false, drizz_owned = false;
 	size_t elem() const { return d.dtype == SGPU_F32 ? 4 : 2; }
 	size_t plane() const { return (size_t) d.width * d.height; }
 	size_t frame_elems() const { return plane() * d.nb_layers; }
@@ -48,6 +51,7 @@ int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what);
 int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes);
 int sgpu_ensure_list(sgpu_ctx *ctx, size_t bytes);
 void sgpu_free_stage(sgpu_ctx *ctx);
+int sgpu_launch_mask_ramp(sgpu_ctx *ctx, float *d_mask, size_t n, int feather_dist);
 
 #define SGPU_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return sgpu_cuda_fail((ctx), e__, #call); } while (0)
 

@@ -246,12 +246,35 @@ template <typename T> struct Pre { };
 template <> struct Pre<float> { static SGPU_HD __forceinline__ bool need(int t) { return t == 1 || t == 2 || t == 3; } };	// rejection_float.c:147-157
 template <> struct Pre<u16> { static SGPU_HD __forceinline__ bool need(int t) { return t >= 1 && t <= 5; } };		// median_and_mean.c:747-759
 
+// Per-sample weights of the weighted combine (median_and_mean.c:1043-1070).  The combine takes any type with
+// `bool(w)` and `w[f]`: a plain `const double *` is the per-frame weight alone (args->weights + layer * N);
+// PixWeights adds the feather mask and the drizzle weight of the sample (data->mstack / data->dstack, gathered at
+// the pixel's shifted column like the sample itself, :1687-1692): n = 1 * d * m * w in the reference's order.
+struct PixWeights {
+	const double *w;	// frame weights of this layer, or null (NO_WEIGHT)
+	const float *m, *d;	// frame 0's mask / drizzle sample of this pixel, or null
+	size_t ms, ds;		// frame strides of the two plane sets, in floats
+	const int *shiftx;	// per-frame x shift, or null
+	SGPU_HD explicit operator bool() const { return w || m || d; }
+	SGPU_HD float dval(int f) const { return d[(size_t) f * ds - (shiftx ? shiftx[f] : 0)]; }
+	SGPU_HD double operator[](int f) const {	// only asked for samples inside their frame (non-zero ones)
+		double n = 1.;
+		if (d) n *= dval(f);
+		if (m) n *= m[(size_t) f * ms - (shiftx ? shiftx[f] : 0)];
+		if (w) n *= w[f];
+		return n;
+	}
+};
+// "remove null pixels (or null drizzle weights or both)" (rejection_float.c:116-126, median_and_mean.c:716-726)
+SGPU_HD __forceinline__ bool drizzle_null(const double *, int) { return false; }
+SGPU_HD __forceinline__ bool drizzle_null(const PixWeights &w, int f) { return w.d && w.dval(f) == 0.f; }
+
 // apply_rejection_float / apply_rejection_ushort.  Returns the kept count; `st` holds the kept
 // samples in front exactly as the reference leaves them.
-template <typename T>
-SGPU_HD int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux, int rej[2]) {
+template <typename T, typename W = const double *>
+SGPU_HD int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux, int rej[2], const W &w = W()) {
 	int N = nb, kept = 0, r = 0, first = 1, changed;
-	for (int f = 0; f < N; f++) { const T v = st.get(f); if (v != (T) 0) { if (f != kept) st.set(kept, v); kept++; } }
+	for (int f = 0; f < N; f++) { const T v = st.get(f); if (v != (T) 0 && !drizzle_null(w, f)) { if (f != kept) st.set(kept, v); kept++; } }
 	if (kept <= 1) return kept;
 	const int removed = N - kept;
 	N = kept;
@@ -417,10 +440,10 @@ SGPU_HD int apply_rejection(Col<T> st, int nb, const RejCfg &c, Col<u16> aux, in
 
 // mean_and_reject (median_and_mean.c:956-1101).  `orig(f)` re-reads the normalized sample of
 // frame f (the reference's o_stack copy); w == nullptr is NO_WEIGHT.
-template <typename T, typename OrigFn>
-SGPU_HD double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const double *w, Col<u16> aux,
+template <typename T, typename OrigFn, typename W>
+SGPU_HD double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const W &w, Col<u16> aux,
 		OrigFn orig, int rej[2]) {
-	const int kept = apply_rejection(st, nb, c, aux, rej);
+	const int kept = apply_rejection(st, nb, c, aux, rej, w);
 	if (kept == 0) return quickmedian_col(st, nb);
 	if (w) {
 		if (sizeof(T) == 4) {
@@ -429,7 +452,7 @@ SGPU_HD double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const double 
 			double sum = 0.0, norm = 0.0;
 			for (int f = 0; f < nb; f++) {
 				const float v = to_f(orig(f));
-				if (v >= pmin && v <= pmax && v != 0.f) { sum += (double) v * w[f]; norm += w[f]; }
+				if (v >= pmin && v <= pmax && v != 0.f) { const double n = w[f]; sum += (double) v * n; norm += n; }
 			}
 			if (norm == 0. || sum == 0.) {
 				sum = 0.;
@@ -443,7 +466,7 @@ SGPU_HD double mean_and_reject(Col<T> st, int nb, const RejCfg &c, const double 
 			double sum = 0.0, norm = 0.0;
 			for (int f = 0; f < nb; f++) {
 				const unsigned v = (unsigned) orig(f);
-				if (v >= pmin && v <= pmax && v > 0) { sum += (double) v * w[f]; norm += w[f]; }
+				if (v >= pmin && v <= pmax && v > 0) { const double n = w[f]; sum += (double) v * n; norm += n; }
 			}
 			if (norm == 0. || sum == 0.) {
 				sum = 0.;

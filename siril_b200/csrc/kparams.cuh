@@ -12,6 +12,7 @@ struct StackParams {
 	int normalize;
 	const double *scale, *offset, *mul, *weights;	// device, [C*N]
 	const int *shiftx;	// device [N] or null
+	const float *mask, *drizz;	// feather masks [N][H][W] / drizzle weights [N][C][H][W] of the block, or null (mean stacking only)
 	RejCfg rc;
 	int is_mean, output_norm, out32, rejmaps;	// rejmaps: 0 none, 1 merged, 2 low+high
 	int norm16;		// 8-bit frames, 16-bit output, output_norm: the result is scaled by 65535/255 (normalize_to16bit)

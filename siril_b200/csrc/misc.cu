@@ -140,9 +140,35 @@ __global__ void synth_kernel(T *dst, int N, int C, int H, int W, uint64_t seed, 
 	}
 }
 
+// feather-mask normalization (median_and_mean.c:513-521): distances above feather_dist become 1, the others go
+// through the smoothstep table of blending.c:34-50 (1001 points, looked up by truncation) — the table entry is
+// recomputed here with the same float operations instead of being stored; zeros stay zero
+__global__ void mask_ramp_kernel(float *mask, size_t n, float distf, float invdistf) {
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+		const float v = mask[i];
+		if (v == 0.f) continue;	// `if (data->mask[frame][i])`: NaN is true and takes the ramp like any value
+		float o = 1.f;
+		if (!(v > distf)) {
+			const int index = (int) ((v * invdistf) * 1000);	// get_ramped_value: (int)(val * RAMP_PACE)
+			const float r = (float) index * (1.f / (float) 1000);
+			o = r * r * r * (6.f * r * r - 15.f * r + 10.f);
+		}
+		mask[i] = o;
+	}
+}
+
 }  // namespace sgpu
 
 using namespace sgpu;
+
+int sgpu_launch_mask_ramp(sgpu_ctx *ctx, float *d_mask, size_t n, int feather_dist) {
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const float distf = (float) feather_dist, invdistf = 1.f / distf;
+	mask_ramp_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d_mask, n, distf, invdistf);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	return SGPU_OK;
+}
 
 extern "C" {
 

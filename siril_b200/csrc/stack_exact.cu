@@ -30,7 +30,12 @@ __device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, siz
 	if (p.is_mean) {
 		const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
 		auto orig = [&](int ff) { return load_norm<T>(p, ff, layer, pix, x); };
-		result = mean_and_reject<T>(st, N, p.rc, w, aux, orig, rej);
+		if (p.mask || p.drizz) {	// feather masks / drizzle weights ride along as per-sample weights (median_and_mean.c:1687-1692)
+			const PixWeights pw = { w, p.mask ? p.mask + pix : nullptr, p.drizz ? p.drizz + (size_t) layer * npix + pix : nullptr,
+				npix, (size_t) p.C * npix, p.shiftx };
+			result = mean_and_reject<T>(st, N, p.rc, pw, aux, orig, rej);
+		} else
+			result = mean_and_reject<T>(st, N, p.rc, w, aux, orig, rej);
 	} else {
 		result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
 	}
@@ -92,6 +97,7 @@ void sgpu_fill_stack_params(StackParams &p, sgpu_block *blk, const sgpu_stack_ar
 	p.normalize = a->normalize; p.scale = dp.scale; p.offset = dp.offset; p.mul = dp.mul;
 	p.weights = a->is_mean ? dp.weights : nullptr;
 	p.shiftx = dp.shiftx;
+	p.mask = a->is_mean ? blk->mask : nullptr; p.drizz = a->is_mean ? blk->drizz : nullptr;
 	p.rc.type = a->is_mean ? a->type_of_rejection : SGPU_NO_REJEC;
 	p.rc.s0 = a->sig[0]; p.rc.s1 = a->sig[1]; p.rc.crit = dp.crit; p.rc.nb_frames = d.nb_frames;
 	p.rc.m_x = 0.f; p.rc.m_dx2 = 0.f; p.rc.xf = nullptr;

@@ -84,6 +84,10 @@ class StackingArgs:
     weighting_type: int = NO_WEIGHT
     weights: Optional[np.ndarray] = None
     bgnoise: Optional[np.ndarray] = None  # seq->stats[layer][idx]->bgnoise, filled by do_normalization
+    feather_dist: int = 0           # > 0: masking (stacking.h:112); `masks` then holds the up-scaled distance masks
+    masks: Any = None               # [N][H][W] float32 (torch CUDA tensor or numpy), data->mask[frame] before the ramp (:483-521)
+    drizzle: bool = False           # args->drizzle; `drizzle_weights` [N][C][H][W] float32 = data->drizz[frame] (:523-541)
+    drizzle_weights: Any = None
     source_bitpix: int = 0          # seq->bitpix of the frames on disk; 8: normalize_to16bit with a 16-bit output_norm result
     engine: int = 0
     retval: int = ST_OK
@@ -204,13 +208,33 @@ def stack_mean_or_median(args: StackingArgs, is_mean: bool) -> int:
         frames = args.frames.contiguous()
         blk = C.c_void_p()
         shifted = args.shifty is not None and np.any(np.asarray(args.shifty) != 0)
+        masking = is_mean and args.feather_dist > 0
+        drizzle = is_mean and bool(args.drizzle)
+        if (masking and args.masks is None) or (drizzle and args.drizzle_weights is None):
+            args.retval = ST_SEQUENCE_ERROR     # the reference fails reading the mask / weight areas (:497-501, :529-532)
+            return ST_SEQUENCE_ERROR
         try:
-            if shifted:     # the reference applies the y shift when it loads the block (:407-448)
+            if shifted or masking or drizzle:     # the reference applies the y shift when it loads the block (:407-448)
                 ctx.check(L.sgpu_block_create(ctx.h, C.byref(desc), C.byref(blk)))
                 es = frames.element_size()
                 for f in range(n):
                     ctx.check(L.sgpu_block_upload_frame(blk, f, C.c_void_p(frames.data_ptr() + f * c * h * w * es), h, 0,
-                                                        int(args.shifty[f])))
+                                                        int(args.shifty[f]) if shifted else 0))
+                for on, planes, kind, per in ((masking, args.masks, _lib.PLANE_MASK, 1),
+                                              (drizzle, args.drizzle_weights, _lib.PLANE_DRIZZLE, c)):
+                    if not on:
+                        continue    # the planes travel like the frames: same rows, same y shift (:483-541)
+                    pl = planes if _is_torch_cuda(planes) else torch.from_numpy(np.ascontiguousarray(planes, dtype=np.float32)).to(dev)
+                    pl = pl.contiguous().float()
+                    if pl.numel() != n * per * h * w:
+                        raise ValueError(f"weight planes have {pl.numel()} samples, expected {n * per * h * w}")
+                    keep.append(pl)
+                    torch.cuda.current_stream(dev).synchronize()
+                    for f in range(n):
+                        ctx.check(L.sgpu_block_upload_weight_plane(blk, kind, f, C.c_void_p(pl.data_ptr() + f * per * h * w * 4), h, 0,
+                                                                   int(args.shifty[f]) if shifted else 0))
+                if masking:
+                    ctx.check(L.sgpu_block_mask_ramp(blk, int(args.feather_dist)))
             else:
                 ctx.check(L.sgpu_block_wrap(ctx.h, C.byref(desc), C.c_void_p(frames.data_ptr()), C.byref(blk)))
             out = torch.empty((c, h, w), dtype=torch.float32 if out32 else torch.uint16, device=dev)
@@ -237,6 +261,8 @@ def stack_mean_or_median(args: StackingArgs, is_mean: bool) -> int:
             if blk:
                 L.sgpu_block_destroy(blk)
     else:
+        if is_mean and (args.feather_dist > 0 or args.drizzle):
+            raise _lib.SgpuError(ST_GENERIC_ERROR, "mask / drizzle weight planes go with device-resident frames (sgpu_stack_block)")
         frames = [np.ascontiguousarray(f) for f in args.frames]
         ptrs = (C.c_void_p * n)(*[f.ctypes.data_as(C.c_void_p) for f in frames])
         out = np.empty((c, h, w), dtype=np.float32 if out32 else np.uint16)
