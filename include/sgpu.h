@@ -299,6 +299,14 @@ int sgpu_compute_factors(int normalize, int nb_layers, int nb_frames, int ref_in
 int sgpu_noise_weights(int nb_layers, int nb_frames, const double *scale, const double *bgnoise,
 		double *weights);
 
+/* the other weightingTypes (stacking.h:46-52), from registration data / FITS keywords of the SELECTED frames, in stack order:
+ * compute_wfwhm_weights (median_and_mean.c:1137-1183; regdata.weighted_fwhm, frames with 0 get weight 0; fails when the
+ * weights sum to 0), compute_nbstars_weights (:1185-1230; regdata.number_of_stars), and NBSTACK_WEIGHT (:150-159: the
+ * STACKCNT keyword of each frame, not normalized) */
+int sgpu_wfwhm_weights(int nb_layers, int nb_frames, const float *weighted_fwhm, double *weights);
+int sgpu_nbstars_weights(int nb_layers, int nb_frames, const int *number_of_stars, double *weights);
+int sgpu_nbstack_weights(int nb_layers, int nb_frames, const int *stack_count, double *weights);
+
 /* ---- row-block planner (stack_compute_parallel_blocks, median_and_mean.c:295-356) ------------- */
 typedef struct { long channel, start_row, end_row, height; } sgpu_image_block;	/* stacking.h:167-169 */
 int sgpu_compute_parallel_blocks(sgpu_image_block *blocks, int max_blocks, long max_number_of_rows,

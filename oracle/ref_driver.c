@@ -45,6 +45,8 @@ static int processing_should_continue(void) { return 1; }
 #include "gen/mm_rejection_u16.inc"  /* u16 clippers, check_G_values, confirm_outliers,
                                         apply_rejection_ushort, mean_and_reject */
 #include "gen/mm_noise_weights.inc"  /* compute_noise_weights */
+static int layer_has_registration(const sequence *seq, int layer) { return seq->regparam && layer >= 0 && seq->regparam[layer]; }
+#include "gen/mm_other_weights.inc"  /* compute_wfwhm_weights, compute_nbstars_weights */
 #include "gen/stats_u16_sd_mad.inc"  /* siril_stats_ushort_sd_64/_32/_mad */
 #include "gen/statsf_mad_bwmv.inc"   /* siril_stats_float_mad, siril_stats_float_bwmv */
 #include "gen/statsf_ikss.inc"       /* IKSSlite */
@@ -403,6 +405,21 @@ void ref_noise_weights(int nb_layers, int N, const double *scale, const double *
 	compute_noise_weights(&args);
 	memcpy(weights, args.weights, (size_t) nb_layers * N * sizeof(double));
 	free(args.weights); free(idx); free(st); free(pst);
+}
+
+/* median_and_mean.c:1137-1230 on the selected frames' registration data; returns the reference's ST_* code */
+int ref_reg_weights(int use_nbstars, int nb_layers, int N, const float *wfwhm, const int *nbstars, double *weights) {
+	struct stacking_args args; sequence seq;
+	memset(&args, 0, sizeof(args)); memset(&seq, 0, sizeof(seq));
+	regdata *rd = calloc(N, sizeof(regdata)), *layers[1] = { rd };
+	int *idx = malloc(N * sizeof(int));
+	for (int i = 0; i < N; i++) { idx[i] = i; rd[i].weighted_fwhm = wfwhm ? wfwhm[i] : 0.f; rd[i].number_of_stars = nbstars ? nbstars[i] : 0; }
+	seq.nb_layers = nb_layers; seq.regparam = layers; args.seq = &seq; args.reglayer = 0;
+	args.nb_images_to_stack = N; args.image_indices = idx;
+	int rv = use_nbstars ? compute_nbstars_weights(&args) : compute_wfwhm_weights(&args);
+	if (args.weights) memcpy(weights, args.weights, (size_t) nb_layers * N * sizeof(double));
+	free(args.weights); free(idx); free(rd);
+	return rv;
 }
 
 /* blocks_out: 4 longs per block (channel, start_row, end_row, height) */

@@ -64,7 +64,9 @@ typedef unsigned char BYTE;
 typedef enum { DATA_USHORT, DATA_FLOAT, DATA_UNSUPPORTED } data_type;
 
 /* opaque stand-ins: the compiled code only passes these around */
-typedef struct shim_sequence { int nb_layers; int number; imstats ***stats; } sequence;
+/* regdata: only the two members compute_wfwhm_weights / compute_nbstars_weights read (core/siril.h:438,442) */
+typedef struct shim_regdata { float weighted_fwhm; int number_of_stars; } regdata;
+typedef struct shim_sequence { int nb_layers; int number; imstats ***stats; regdata **regparam; } sequence;
 typedef struct shim_fits { long naxes[3]; float *fdata; } fits;
 
 void g_free(void *p);

@@ -99,6 +99,9 @@ SIGNATURES = {
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "sgpu_compute_factors": (C.c_int, [C.c_int] * 6 + [P, P, P]),
     "sgpu_noise_weights": (C.c_int, [C.c_int, C.c_int, P, P, P]),
+    "sgpu_wfwhm_weights": (C.c_int, [C.c_int, C.c_int, P, P]),
+    "sgpu_nbstars_weights": (C.c_int, [C.c_int, C.c_int, P, P]),
+    "sgpu_nbstack_weights": (C.c_int, [C.c_int, C.c_int, P, P]),
     "sgpu_compute_parallel_blocks": (C.c_int, [P, C.c_int, C.c_long, C.POINTER(C.c_long), C.c_int,
                                                C.POINTER(C.c_long), C.POINTER(C.c_int)]),
     "sgpu_synth_fill": (C.c_int, [P, P, C.c_uint64, C.c_int, C.c_int]),

@@ -5,6 +5,8 @@
 #include <new>
 #include <cstdlib>
 #include <functional>
+#include <cfloat>
+#include <climits>
 #include "common.cuh"
 
 int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::function<int(sgpu_block *, int, int)> &upload_one,
@@ -557,6 +559,63 @@ int sgpu_noise_weights(int nb_layers, int N, const double *scale, const double *
 		norm /= (double) N;
 		for (int i = 0; i < N; i++) weights[l * N + i] /= norm;
 	}
+	return SGPU_OK;
+}
+
+/* compute_wfwhm_weights (median_and_mean.c:1137-1183): weighted_fwhm of the selected frames (regdata's float) */
+int sgpu_wfwhm_weights(int nb_layers, int N, const float *weighted_fwhm, double *weights) {
+	if (!weighted_fwhm || !weights || N < 1) return SGPU_GENERIC_ERROR;
+	double fwhmmin = DBL_MAX, fwhmmax = -DBL_MAX;
+	for (int i = 0; i < N; i++) {
+		if (weighted_fwhm[i] < fwhmmin && weighted_fwhm[i] > 0) fwhmmin = weighted_fwhm[i];
+		if (weighted_fwhm[i] > fwhmmax) fwhmmax = weighted_fwhm[i];
+	}
+	const double invdenom = 1. / (1. / (fwhmmin * fwhmmin) - 1. / (fwhmmax * fwhmmax));
+	const double invfwhmax2 = 1. / (fwhmmax * fwhmmax);
+	for (int l = 0; l < nb_layers; l++) {
+		double norm = 0.0;
+		double *pw = weights + (size_t) l * N;
+		for (int i = 0; i < N; i++) {
+			if (weighted_fwhm[i] > 0) {
+				pw[i] = (1. / (weighted_fwhm[i] * weighted_fwhm[i]) - invfwhmax2) * invdenom;	// the square is a float product, as in the reference
+				norm += pw[i];
+			} else pw[i] = 0.;
+		}
+		norm /= (double) N;
+		if (!norm) return SGPU_GENERIC_ERROR;	// NaN is "true" here too: the reference goes on with NaN weights
+		for (int i = 0; i < N; i++) pw[i] /= norm;
+	}
+	return SGPU_OK;
+}
+
+/* compute_nbstars_weights (median_and_mean.c:1185-1230): number_of_stars of the selected frames */
+int sgpu_nbstars_weights(int nb_layers, int N, const int *number_of_stars, double *weights) {
+	if (!number_of_stars || !weights || N < 1) return SGPU_GENERIC_ERROR;
+	int starmin = INT_MAX, starmax = 0;
+	for (int i = 0; i < N; i++) {
+		if (number_of_stars[i] < starmin) starmin = number_of_stars[i];
+		if (number_of_stars[i] > starmax) starmax = number_of_stars[i];
+	}
+	const double invdenom = starmax == starmin ? 1.0 : 1. / (double) (starmax - starmin);
+	for (int l = 0; l < nb_layers; l++) {
+		double norm = 0.0;
+		double *pw = weights + (size_t) l * N;
+		for (int i = 0; i < N; i++) {
+			if (starmax == starmin) pw[i] = 1.;
+			else pw[i] = (double) (number_of_stars[i] - starmin) * (double) (number_of_stars[i] - starmin) * invdenom * invdenom;
+			norm += pw[i];
+		}
+		norm /= (double) N;
+		for (int i = 0; i < N; i++) pw[i] /= norm;
+	}
+	return SGPU_OK;
+}
+
+/* NBSTACK_WEIGHT (median_and_mean.c:150-159): the frame's STACKCNT keyword as its weight on every layer, not normalized */
+int sgpu_nbstack_weights(int nb_layers, int N, const int *stack_count, double *weights) {
+	if (!stack_count || !weights || N < 1) return SGPU_GENERIC_ERROR;
+	for (int l = 0; l < nb_layers; l++)
+		for (int i = 0; i < N; i++) weights[(size_t) l * N + i] = (double) stack_count[i];
 	return SGPU_OK;
 }
 

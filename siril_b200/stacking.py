@@ -83,6 +83,9 @@ class StackingArgs:
     merge_lowhigh_rejmaps: bool = False
     weighting_type: int = NO_WEIGHT
     weights: Optional[np.ndarray] = None
+    weighted_fwhm: Optional[np.ndarray] = None    # regparam[reglayer][idx].weighted_fwhm of the selected frames (WFWHM_WEIGHT)
+    number_of_stars: Optional[np.ndarray] = None  # regparam[reglayer][idx].number_of_stars (NBSTARS_WEIGHT)
+    stack_count: Optional[np.ndarray] = None      # STACKCNT keyword of each frame (NBSTACK_WEIGHT, median_and_mean.c:150-159)
     bgnoise: Optional[np.ndarray] = None  # seq->stats[layer][idx]->bgnoise, filled by do_normalization
     feather_dist: int = 0           # > 0: masking (stacking.h:112); `masks` then holds the up-scaled distance masks
     masks: Any = None               # [N][H][W] float32 (torch CUDA tensor or numpy), data->mask[frame] before the ramp (:483-521)
@@ -171,9 +174,26 @@ def _fill_cargs(args, n, c, is_mean, keep):
 
 
 def _compute_weights(args, n, c):
-    """median_and_mean.c:1519-1539; only NOISE_WEIGHT can be derived from the frames themselves"""
+    """median_and_mean.c:1519-1539: NOISE_WEIGHT from the normalization statistics, the others from the
+    registration data / STACKCNT keywords the caller holds for the selected frames"""
+    L = _lib.lib()
+    w = np.zeros((c, n), dtype=np.float64)
+    for kind, src, dt, fn, what in ((WFWHM_WEIGHT, args.weighted_fwhm, np.float32, L.sgpu_wfwhm_weights, "wFWHM"),
+                                    (NBSTARS_WEIGHT, args.number_of_stars, np.int32, L.sgpu_nbstars_weights, "number of stars"),
+                                    (NBSTACK_WEIGHT, args.stack_count, np.int32, L.sgpu_nbstack_weights, "stack count")):
+        if args.weighting_type == kind:
+            if src is None:    # :1144-1147 / :1192-1195
+                raise _lib.SgpuError(ST_GENERIC_ERROR, f"Sequence does not have registration info, cannot use weighing by {what}, aborting")
+            a = np.ascontiguousarray(src, dtype=dt)
+            if a.size != n:
+                raise ValueError(f"{what}: {a.size} entries for {n} frames")
+            rv = fn(c, n, a.ctypes.data_as(C.c_void_p), w.ctypes.data_as(C.c_void_p))
+            if rv:
+                raise _lib.SgpuError(rv, f"weights by {what}")
+            args.weights = w
+            return
     if args.weighting_type != NOISE_WEIGHT:
-        raise _lib.SgpuError(ST_GENERIC_ERROR, "weights for this weighting type come from registration data: pass args.weights")
+        raise _lib.SgpuError(ST_GENERIC_ERROR, f"unknown weighting type {args.weighting_type}")
     if args.normalize == NO_NORM or args.bgnoise is None:
         # src/core/command.c:11700-11703: noise weighting needs normalization statistics
         raise _lib.SgpuError(ST_GENERIC_ERROR, "Weighting by noise requires normalization")

@@ -86,6 +86,40 @@ def test_factors_and_weights_match_oracle(orc):
         assert np.array_equal(w, orc.noise_weights(s, bg))
 
 
+def test_registration_weights_match_the_reference(ref):
+    """WFWHM / NBSTARS / NBSTACK weights (median_and_mean.c:1137-1230, :150-159): host scalar code of the C ABI against the
+    reference's own functions (oracle/_ref, ref_reg_weights), bit for bit"""
+    from siril_b200 import _lib
+    L = _lib.lib()
+    R = ref.lib
+    R.ref_reg_weights.restype = C.c_int
+    R.ref_reg_weights.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    rng = np.random.default_rng(8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for N, Cn in [(2, 1), (7, 3), (40, 1), (300, 3)]:
+        for case in range(4):
+            fw = rng.uniform(1.5, 6.0, N).astype(np.float32)
+            ns = rng.integers(5, 4000, N).astype(np.int32)
+            if case == 1:
+                fw[rng.integers(0, N)] = 0          # a frame without a measurement gets weight 0
+                ns[:] = ns[0]                       # all alike: weights 1
+            if case == 2:
+                fw[:] = 0                           # nothing measured: the reference fails (norm == 0)
+            if case == 3:
+                fw[:] = fw[0]                       # all alike: 1 / 0 in invdenom, the reference's inf / NaN weights
+            for nbstars in (0, 1):
+                got, exp = np.full((Cn, N), -1.0), np.full((Cn, N), -1.0)
+                rv = (L.sgpu_nbstars_weights(Cn, N, p(ns), p(got)) if nbstars else L.sgpu_wfwhm_weights(Cn, N, p(fw), p(got)))
+                rr = R.ref_reg_weights(nbstars, Cn, N, p(fw), p(ns), p(exp))
+                assert rv == rr, (N, Cn, case, nbstars, rv, rr)
+                if rv == 0:
+                    assert np.array_equal(got, exp, equal_nan=True), (N, Cn, case, nbstars)
+            cnt = rng.integers(1, 50, N).astype(np.int32)
+            got = np.zeros((Cn, N))
+            assert L.sgpu_nbstack_weights(Cn, N, p(cnt), p(got)) == 0
+            assert np.array_equal(got, np.broadcast_to(cnt.astype(np.float64), (Cn, N)))
+
+
 def test_siril_glue_builds_against_the_reference_header_and_keeps_its_symbols():
     """integration/siril/src/gpu/gpu_stack.c compiles against the reference's stacking.h; the harness
     library carries the reference's own symbol names around it (no compute without a GPU)"""
