@@ -299,6 +299,30 @@ int sgpu_compute_factors(int normalize, int nb_layers, int nb_frames, int ref_in
 int sgpu_noise_weights(int nb_layers, int nb_frames, const double *scale, const double *bgnoise,
 		double *weights);
 
+/* ---- overlap normalization (compute_normalization_overlaps, normalization.c:666-938; used with -maximize framing) ----
+ * Frames that only partly overlap are levelled pair by pair: for every pair (i, j) the statistics of the pixels both
+ * frames have (non-zero in both) over their common rectangle, then one small linear system per layer. */
+typedef struct { int x, y, w, h; } sgpu_rect;	/* rectangle (core/settings.h:24-26): y counts from the TOP row of the image */
+/* compute_overlap (normalization.c:420-456): rx / ry the two frame sizes, dx / dy their translation_from_H
+ * (registration.c:301-304); returns the number of pixels of the common area (0: none) and the two rectangles */
+size_t sgpu_compute_overlap(int rxi, int ryi, int rxj, int ryj, double dxi, double dyi, double dxj, double dyj,
+		sgpu_rect *areai, sgpu_rect *areaj);
+/* overlap_stats_t's numbers (core/siril.h:416-424): Xij is frame i's statistic over its overlap with j */
+typedef struct { size_t Nij; float medij, medji, madij, madji, locij, locji, scaij, scaji; } sgpu_overlap_stats;
+/* one pair on one layer (_compute_estimators_for_images, normalization.c:549-593): plane_i / plane_j are whole planes
+ * [ry][rx] in memory order (device pointers when on_device != 0, else host memory: only the rectangle's rows are
+ * uploaded); WORD samples are converted to [0,1] floats first, as the reference does.  Nij stays 0 (and the statistics
+ * with it) when 3 pixels or fewer are non-zero in both; lite != 0 stops after median / MAD (args->lite_norm). */
+int sgpu_overlap_stats_pair(sgpu_ctx *ctx, const void *plane_i, int rxi, int ryi, const void *plane_j, int rxj, int ryj,
+		int on_device, int dtype, const sgpu_rect *areai, const sgpu_rect *areaj, int lite, sgpu_overlap_stats *out);
+/* the solves of compute_normalization_overlaps (:875-906) for ONE layer: Nij / Mij / Sij are nb_frames x nb_frames
+ * row-major (pair counts, locations — median or IKSS location — and scales — MAD or IKSS scale; Mij is modified as the
+ * reference modifies it); offset / mul / scale ([nb_frames], initialized 0 / 1 / 1 by init_coeffs) get the coefficients
+ * of every frame but the reference one.  solve_overlap_coeffs (:296-355) builds the system; the LU solve behind it is
+ * GSL's in the reference (gsl_linalg_LU_decomp / _solve), partial-pivoting Gaussian elimination here. */
+int sgpu_overlap_solve(int normalize, int nb_frames, int ref_index, const size_t *Nij, double *Mij, const double *Sij,
+		double *offset, double *mul, double *scale);
+
 /* the other weightingTypes (stacking.h:46-52), from registration data / FITS keywords of the SELECTED frames, in stack order:
  * compute_wfwhm_weights (median_and_mean.c:1137-1183; regdata.weighted_fwhm, frames with 0 get weight 0; fails when the
  * weights sum to 0), compute_nbstars_weights (:1185-1230; regdata.number_of_stars), and NBSTACK_WEIGHT (:150-159: the

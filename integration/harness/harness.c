@@ -91,6 +91,7 @@ typedef struct {
 	int output_norm, use_32bit_output, create_rejmaps, merge_rejmaps;
 	int cancel_after;		/* processing_should_continue() turns false after this many polls; < 0: never */
 	int runs;			/* stack this many times on the same sequence (the statistics cache serves from the second) */
+	const float *wfwhm; const int *nbstars;	/* regdata.weighted_fwhm / number_of_stars per frame (WFWHM_WEIGHT / NBSTARS_WEIGHT), or NULL */
 } harness_params;
 
 /* out: [C][H][W] float or WORD; rej_low / rej_high: WORD or NULL; coeff_out: 3 * C * N doubles (offset, mul, scale) or NULL.
@@ -103,10 +104,16 @@ int harness_stack(const harness_params *p, const void *frames, void *out, WORD *
 	seq.number = seq.selnum = p->N; seq.nb_layers = p->C; seq.rx = p->W; seq.ry = p->H;
 	seq.bitpix = p->is_float ? FLOAT_IMG : USHORT_IMG; seq.reference_image = p->ref_image; seq.harness = &store;
 	regdata *rp = NULL;
-	if (p->dx) {
+	const int has_reg = p->dx || p->wfwhm || p->nbstars;
+	if (has_reg) {
 		seq.regparam = calloc(3, sizeof(regdata *));
 		rp = calloc(p->N, sizeof(regdata));
-		for (int i = 0; i < p->N; i++) { rp[i].H.h00 = rp[i].H.h11 = rp[i].H.h22 = 1.0; rp[i].H.h02 = p->dx[i]; rp[i].H.h12 = -p->dy[i]; }
+		for (int i = 0; i < p->N; i++) {
+			rp[i].H.h00 = rp[i].H.h11 = rp[i].H.h22 = 1.0;
+			if (p->dx) { rp[i].H.h02 = p->dx[i]; rp[i].H.h12 = -p->dy[i]; }
+			if (p->wfwhm) rp[i].weighted_fwhm = p->wfwhm[i];
+			if (p->nbstars) rp[i].number_of_stars = p->nbstars[i];
+		}
 		seq.regparam[p->reglayer < 0 ? 0 : p->reglayer] = rp;
 	}
 	int *indices = malloc(p->N * sizeof(int));
@@ -122,7 +129,7 @@ int harness_stack(const harness_params *p, const void *frames, void *out, WORD *
 		args.type_of_rejection = p->rejection; args.sig[0] = p->sig[0]; args.sig[1] = p->sig[1];
 		args.create_rejmaps = p->create_rejmaps; args.merge_lowhigh_rejmaps = p->merge_rejmaps;
 		args.weighting_type = p->weighting; args.output_norm = p->output_norm; args.use_32bit_output = p->use_32bit_output;
-		args.reglayer = p->dx ? (p->reglayer < 0 ? 0 : p->reglayer) : -1;
+		args.reglayer = has_reg ? (p->reglayer < 0 ? 0 : p->reglayer) : -1;
 		cancel_after = p->cancel_after; polls = 0; store.reads = 0;
 		/* main_stack (stacking.c:76-108): 1. normalization, 3. the method, through its pointer */
 		args.retval = do_normalization(&args);

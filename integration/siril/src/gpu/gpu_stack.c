@@ -143,10 +143,29 @@ int gpu_stack_mean_or_median(struct stacking_args *args, gboolean is_mean) {
 	/* weights (:1519-1539).  Noise weighting: compute_noise_weights (:1111-1135) from the scale factors and
 	 * the noise estimates do_normalization left in the sequence's statistics cache */
 	if (is_mean && args->weighting_type != NO_WEIGHT) {
-		if (args->weighting_type != NOISE_WEIGHT) {
-			siril_log_message(_("GPU stacking: only noise weighting is available yet\n"));
+		if (args->weighting_type == WFWHM_WEIGHT || args->weighting_type == NBSTARS_WEIGHT) {
+			/* compute_wfwhm_weights / compute_nbstars_weights (:1137-1230) from the registration data of the selected frames */
+			const gboolean stars = args->weighting_type == NBSTARS_WEIGHT;
+			if (args->reglayer < 0 || !args->seq->regparam || !args->seq->regparam[args->reglayer]) {
+				siril_log_error(_("Sequence does not have registration info, cannot use weighing by %s, aborting\n"), stars ? _("number of stars") : "wFWHM");
+				retval = ST_GENERIC_ERROR; goto free_and_close;
+			}
+			const regdata *rd = args->seq->regparam[args->reglayer];
+			float *fw = malloc(nb_frames * sizeof(float)); int *ns = malloc(nb_frames * sizeof(int));
+			args->weights = malloc((size_t) naxes[2] * nb_frames * sizeof(double));
+			if (!fw || !ns || !args->weights) { free(fw); free(ns); retval = ST_ALLOC_ERROR; goto free_and_close; }
+			for (int f = 0; f < nb_frames; f++) { fw[f] = rd[args->image_indices[f]].weighted_fwhm; ns[f] = rd[args->image_indices[f]].number_of_stars; }
+			siril_log_message(stars ? _("Computing weights based on number of stars...\n") : _("Computing weights based on wFWHM...\n"));
+			retval = stars ? sgpu_nbstars_weights((int) naxes[2], nb_frames, ns, args->weights)
+				       : sgpu_wfwhm_weights((int) naxes[2], nb_frames, fw, args->weights);
+			free(fw); free(ns);
+			if (retval) { retval = ST_GENERIC_ERROR; goto free_and_close; }
+		} else if (args->weighting_type != NOISE_WEIGHT) {
+			/* NBSTACK_WEIGHT reads the STACKCNT keyword of every frame while the files are opened (:150-159): with the
+			 * keyword reader of the host build, sgpu_nbstack_weights(nb_layers, nb_frames, stack_count, weights) */
+			siril_log_message(_("GPU stacking: weighting by the number of stacked images needs the frames' STACKCNT keywords\n"));
 			retval = ST_GENERIC_ERROR; goto free_and_close;
-		}
+		} else {
 		if (args->normalize == NO_NORM || !args->coeff.scale || !args->seq->stats) {
 			siril_log_message(_("Weighting by noise requires normalization\n"));	/* command.c:11700-11703 */
 			retval = ST_GENERIC_ERROR; goto free_and_close;
@@ -163,6 +182,7 @@ int gpu_stack_mean_or_median(struct stacking_args *args, gboolean is_mean) {
 		retval = sgpu_noise_weights((int) naxes[2], nb_frames, args->coeff.scale, bg, args->weights);
 		free(bg);
 		if (retval) goto free_and_close;
+		}
 	}
 
 	shiftx = calloc(nb_frames, sizeof(int)); shifty = calloc(nb_frames, sizeof(int));

@@ -59,6 +59,12 @@ RANGES = {
     "quant_diffmeansigma": ("src/algos/quantize.c", 327, 422, None),
     "quant_noise1":      ("src/algos/quantize.c", 1202, 1501, None),
     "norm_factors":      ("src/stacking/normalization.c", 144, 181, None),
+    # --- overlap normalization ---
+    "norm_solve_overlap":   ("src/stacking/normalization.c", 296, 355, None),
+    "norm_compute_overlap": ("src/stacking/normalization.c", 420, 456, None),
+    "norm_overlap_layers":  ("src/stacking/normalization.c", 549, 593, None),
+    "norm_overlap_solves":  ("src/stacking/normalization.c", 875, 906, None),
+    "reg_translation_from_H": ("src/registration/registration.c", 301, 304, None),
     # --- sum / min / max stackers (ref_simple.c) ---
     "sum_pixel_loop":    ("src/stacking/sum.c", 186, 231, None),
     "sum_find_max":      ("src/stacking/sum.c", 257, 279, None),

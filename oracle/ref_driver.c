@@ -23,6 +23,8 @@
 #include "core/processing.h"
 #include <gsl/gsl_statistics_float.h>
 #include <gsl/gsl_statistics_ushort.h>
+#include <gsl/gsl_linalg.h>
+#include <limits.h>
 
 /* the shim fits/sequence are opaque in core/siril.h; the few members the extracted ranges
  * touch are provided by these layouts (same first members as the shim structs). */
@@ -420,6 +422,76 @@ int ref_reg_weights(int use_nbstars, int nb_layers, int N, const float *wfwhm, c
 	if (args.weights) memcpy(weights, args.weights, (size_t) nb_layers * N * sizeof(double));
 	free(args.weights); free(idx); free(rd);
 	return rv;
+}
+
+/* ---- overlap normalization: the reference's own lines around in-RAM data ---- */
+#include "gen/reg_translation_from_H.inc"  /* translation_from_H */
+#include "gen/norm_solve_overlap.inc"      /* solve_overlap_coeffs (LU through oracle/shim/gsl/gsl_linalg.h) */
+#include "gen/norm_compute_overlap.inc"    /* compute_overlap */
+
+/* normalization.c:420-456 for two frames of sizes (rxi, ryi), (rxj, ryj) shifted by (dx, dy) = translation_from_H */
+size_t ref_compute_overlap(int rxi, int ryi, int rxj, int ryj, double dxi, double dyi, double dxj, double dyj,
+		int areai_out[4], int areaj_out[4]) {
+	struct stacking_args args; sequence seq; regdata rd[2]; imgdata im[2] = { { rxi, ryi }, { rxj, ryj } };
+	memset(&args, 0, sizeof args); memset(&seq, 0, sizeof seq); memset(rd, 0, sizeof rd);
+	rd[0].H.h02 = dxi; rd[0].H.h12 = -dyi; rd[1].H.h02 = dxj; rd[1].H.h12 = -dyj;
+	regdata *layers[1] = { rd };
+	seq.regparam = layers; seq.is_variable = TRUE; seq.imgparam = im; seq.number = 2; seq.nb_layers = 1;
+	args.seq = &seq; args.reglayer = 0;
+	rectangle ai = { 0 }, aj = { 0 };
+	size_t n = compute_overlap(&args, 0, 1, &ai, &aj);
+	areai_out[0] = ai.x; areai_out[1] = ai.y; areai_out[2] = ai.w; areai_out[3] = ai.h;
+	areaj_out[0] = aj.x; areaj_out[1] = aj.y; areaj_out[2] = aj.w; areaj_out[3] = aj.h;
+	return n;
+}
+
+/* the per-layer statistics of one pair (normalization.c:549-593) on the two overlap regions as
+ * readfits_partial_all_layers delivers them ([h][w], nbdata samples each); out[0] = Nij, then
+ * medij, medji, madij, madji, locij, locji, scaij, scaji */
+int ref_overlap_pair(int is_float, const void *region_i, const void *region_j, size_t nbdata, int lite, double out[9]) {
+	struct stacking_args a_, *args = &a_; sequence seq_, *seq = &seq_;
+	memset(&a_, 0, sizeof a_); memset(&seq_, 0, sizeof seq_);
+	a_.lite_norm = lite; a_.seq = seq;
+	overlap_stats_t os; memset(&os, 0, sizeof os);
+	overlap_stats_t *ol[1] = { &os };
+	seq_.ostats = ol;
+	const int nb_layers = 1, ijth = 0, i = 0, j = 1;
+	gboolean needs_recalc_lite[3] = { TRUE, 0, 0 }, needs_recalc_detailed[3] = { !lite, 0, 0 };
+	fits fiti, fitj; memset(&fiti, 0, sizeof fiti); memset(&fitj, 0, sizeof fitj);
+	fiti.type = fitj.type = is_float ? DATA_FLOAT : DATA_USHORT;
+	fiti.fpdata[0] = (float *) region_i; fitj.fpdata[0] = (float *) region_j;
+	fiti.pdata[0] = (WORD *) region_i; fitj.pdata[0] = (WORD *) region_j;
+	float invnorm = 1. / USHRT_MAX;
+	float *datai = malloc(nbdata * sizeof(float)), *dataj = malloc(nbdata * sizeof(float));
+	size_t Nij = 0;
+	(void) i; (void) j;
+#include "gen/norm_overlap_layers.inc"
+	free(datai); free(dataj);
+	out[0] = (double) os.Nij; out[1] = os.medij; out[2] = os.medji; out[3] = os.madij; out[4] = os.madji;
+	out[5] = os.locij; out[6] = os.locji; out[7] = os.scaij; out[8] = os.scaji;
+	return 0;
+}
+
+/* the three solves of compute_normalization_overlaps (normalization.c:875-906) for one layer; Nij_in / Mij_in / Sij_in
+ * nb_frames x nb_frames row-major; offset / mul / scale [nb_frames] come in initialized (0 / 1 / 1, init_coeffs) */
+int ref_overlap_solve(int normalize, int nb_frames, int index_ref, const size_t *Nij_in, const double *Mij_in, const double *Sij_in,
+		double *offset, double *mul, double *scale) {
+	struct stacking_args a_, *args = &a_;
+	memset(&a_, 0, sizeof a_);
+	a_.normalize = (normalization) normalize;
+	norm_coeff *coeff = &a_.coeff;
+	coeff->poffset[0] = offset; coeff->pmul[0] = mul; coeff->pscale[0] = scale;
+	const int nb_layers = 1, N = nb_frames - 1;
+	size_t **rowsN = malloc(nb_frames * sizeof(size_t *)); double **rowsM = malloc(nb_frames * sizeof(double *)), **rowsS = malloc(nb_frames * sizeof(double *));
+	size_t *nn = malloc((size_t) nb_frames * nb_frames * sizeof(size_t)); double *mm = malloc((size_t) nb_frames * nb_frames * sizeof(double)), *ss = malloc((size_t) nb_frames * nb_frames * sizeof(double));
+	memcpy(nn, Nij_in, (size_t) nb_frames * nb_frames * sizeof(size_t)); memcpy(mm, Mij_in, (size_t) nb_frames * nb_frames * sizeof(double)); memcpy(ss, Sij_in, (size_t) nb_frames * nb_frames * sizeof(double));
+	for (int k = 0; k < nb_frames; k++) { rowsN[k] = nn + (size_t) k * nb_frames; rowsM[k] = mm + (size_t) k * nb_frames; rowsS[k] = ss + (size_t) k * nb_frames; }
+	size_t **Nij[1] = { rowsN }; double **Mij[1] = { rowsM }, **Sij[1] = { rowsS };
+	int *index = malloc(nb_frames * sizeof(int)); double *coeffs = calloc(N > 0 ? N : 1, sizeof(double));
+	for (int k = 0, c = 0; k < nb_frames; k++) if (k != index_ref) index[c++] = k;	/* :779-782 */
+#include "gen/norm_overlap_solves.inc"
+	free(rowsN); free(rowsM); free(rowsS); free(nn); free(mm); free(ss); free(index); free(coeffs);
+	return 0;
 }
 
 /* blocks_out: 4 longs per block (channel, start_row, end_row, height) */

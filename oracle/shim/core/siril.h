@@ -65,9 +65,13 @@ typedef enum { DATA_USHORT, DATA_FLOAT, DATA_UNSUPPORTED } data_type;
 
 /* opaque stand-ins: the compiled code only passes these around */
 /* regdata: only the two members compute_wfwhm_weights / compute_nbstars_weights read (core/siril.h:438,442) */
-typedef struct shim_regdata { float weighted_fwhm; int number_of_stars; } regdata;
-typedef struct shim_sequence { int nb_layers; int number; imstats ***stats; regdata **regparam; } sequence;
-typedef struct shim_fits { long naxes[3]; float *fdata; } fits;
+/* and the homography compute_overlap reads through translation_from_H (core/siril.h:426-436) */
+typedef struct { double h00, h01, h02, h10, h11, h12, h20, h21, h22; int pair_matched, Inliers; } Homography;
+typedef struct shim_regdata { float weighted_fwhm; int number_of_stars; Homography H; } regdata;
+typedef struct shim_imgdata { int rx, ry; } imgdata;
+typedef struct shim_sequence { int nb_layers; int number; imstats ***stats; regdata **regparam;
+	unsigned int rx, ry; gboolean is_variable; imgdata *imgparam; overlap_stats_t **ostats; } sequence;
+typedef struct shim_fits { long naxes[3]; float *fdata; data_type type; float *fpdata[3]; WORD *pdata[3]; } fits;
 
 void g_free(void *p);
 int g_strcmp0(const char *a, const char *b);

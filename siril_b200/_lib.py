@@ -48,6 +48,15 @@ class FitsInfo(C.Structure):
                 ("device_readable", C.c_int)]
 
 
+class Rect(C.Structure):
+    _fields_ = [("x", C.c_int), ("y", C.c_int), ("w", C.c_int), ("h", C.c_int)]
+
+
+class OverlapStats(C.Structure):
+    _fields_ = [("Nij", C.c_size_t)] + [(n, C.c_float) for n in ("medij", "medji", "madij", "madji", "locij", "locji",
+                                                                   "scaij", "scaji")]
+
+
 class ImageBlock(C.Structure):
     _fields_ = [("channel", C.c_long), ("start_row", C.c_long), ("end_row", C.c_long), ("height", C.c_long)]
 
@@ -99,6 +108,10 @@ SIGNATURES = {
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "sgpu_compute_factors": (C.c_int, [C.c_int] * 6 + [P, P, P]),
     "sgpu_noise_weights": (C.c_int, [C.c_int, C.c_int, P, P, P]),
+    "sgpu_compute_overlap": (C.c_size_t, [C.c_int] * 4 + [C.c_double] * 4 + [C.POINTER(Rect), C.POINTER(Rect)]),
+    "sgpu_overlap_stats_pair": (C.c_int, [P, P, C.c_int, C.c_int, P, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Rect),
+                                          C.POINTER(Rect), C.c_int, C.POINTER(OverlapStats)]),
+    "sgpu_overlap_solve": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, P, P]),
     "sgpu_wfwhm_weights": (C.c_int, [C.c_int, C.c_int, P, P]),
     "sgpu_nbstars_weights": (C.c_int, [C.c_int, C.c_int, P, P]),
     "sgpu_nbstack_weights": (C.c_int, [C.c_int, C.c_int, P, P]),

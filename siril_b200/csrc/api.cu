@@ -562,6 +562,70 @@ int sgpu_noise_weights(int nb_layers, int N, const double *scale, const double *
 	return SGPU_OK;
 }
 
+/* solve_overlap_coeffs (normalization.c:296-355): the (nb_frames - 1)^2 system of one layer, then LU with partial pivoting */
+static int solve_overlap_coeffs(int nb_frames, const int *index, int index_ref, const size_t *Nij, const double *Mij, bool additive, double *coeffs) {
+	const int N = nb_frames - 1;
+	std::vector<double> A((size_t) N * N, 0.0), B(N, 0.0);
+	auto n_ = [&](int a, int b) { return (double) Nij[(size_t) a * nb_frames + b]; };
+	auto m_ = [&](int a, int b) { return Mij[(size_t) a * nb_frames + b]; };
+	int c = 0;
+	for (int i = 0; i < N; i++) {
+		const int ii = index[i];
+		B[i] = additive ? n_(ii, index_ref) * (m_(index_ref, ii) - m_(ii, index_ref)) : n_(ii, index_ref) * m_(index_ref, ii) * m_(ii, index_ref);
+		for (int j = 0; j < N; j++) {
+			const int ij = index[j];
+			if (ii == ij) {
+				for (int k = 0; k < nb_frames; k++)
+					if (k != ii) A[c] += additive ? n_(ii, k) : n_(ii, k) * m_(ii, k) * m_(ii, k);
+			} else {
+				A[c] = additive ? -n_(ii, ij) : -n_(ii, ij) * m_(ii, ij) * m_(ij, ii);
+				if (additive) B[i] += Nij[(size_t) ii * nb_frames + ij] * (m_(ij, ii) - m_(ii, ij));
+			}
+			c++;
+		}
+	}
+	// LU decomposition with partial (row) pivoting, then forward / back substitution
+	std::vector<int> perm(N);
+	for (int i = 0; i < N; i++) perm[i] = i;
+	for (int j = 0; j < N; j++) {
+		int piv = j; double best = fabs(A[(size_t) j * N + j]);
+		for (int i = j + 1; i < N; i++) if (fabs(A[(size_t) i * N + j]) > best) { best = fabs(A[(size_t) i * N + j]); piv = i; }
+		if (piv != j) { for (int k = 0; k < N; k++) std::swap(A[(size_t) j * N + k], A[(size_t) piv * N + k]); std::swap(perm[j], perm[piv]); }
+		const double ajj = A[(size_t) j * N + j];
+		if (ajj == 0.0) return 1;	// singular: frames that overlap nothing
+		for (int i = j + 1; i < N; i++) {
+			const double l = A[(size_t) i * N + j] / ajj;
+			A[(size_t) i * N + j] = l;
+			for (int k = j + 1; k < N; k++) A[(size_t) i * N + k] -= l * A[(size_t) j * N + k];
+		}
+	}
+	for (int i = 0; i < N; i++) { double v = B[perm[i]]; for (int k = 0; k < i; k++) v -= A[(size_t) i * N + k] * coeffs[k]; coeffs[i] = v; }
+	for (int i = N - 1; i >= 0; i--) { double v = coeffs[i]; for (int k = i + 1; k < N; k++) v -= A[(size_t) i * N + k] * coeffs[k]; coeffs[i] = v / A[(size_t) i * N + i]; }
+	return 0;
+}
+
+int sgpu_overlap_solve(int normalize, int nb_frames, int ref_index, const size_t *Nij, double *Mij, const double *Sij,
+		double *offset, double *mul, double *scale) {
+	if (!Nij || !Mij || !Sij || !offset || !mul || !scale || nb_frames < 2 || ref_index < 0 || ref_index >= nb_frames) return SGPU_GENERIC_ERROR;
+	const int N = nb_frames - 1;
+	std::vector<int> index; std::vector<double> coeffs(N, 0.0);
+	for (int i = 0; i < nb_frames; i++) if (i != ref_index) index.push_back(i);
+	if (normalize == SGPU_MULTIPLICATIVE_SCALING || normalize == SGPU_ADDITIVE_SCALING) {	// :875-888
+		if (solve_overlap_coeffs(nb_frames, index.data(), ref_index, Nij, Sij, false, coeffs.data())) return SGPU_GENERIC_ERROR;
+		for (int i = 0; i < N; i++) scale[index[i]] = coeffs[i];
+		for (int ii = 0; ii < nb_frames; ii++) for (int jj = 0; jj < nb_frames; jj++) Mij[(size_t) ii * nb_frames + jj] *= scale[ii];
+	}
+	if (normalize == SGPU_ADDITIVE || normalize == SGPU_ADDITIVE_SCALING) {	// :890-897
+		if (solve_overlap_coeffs(nb_frames, index.data(), ref_index, Nij, Mij, true, coeffs.data())) return SGPU_GENERIC_ERROR;
+		for (int i = 0; i < N; i++) offset[index[i]] = -coeffs[i];
+	}
+	if (normalize == SGPU_MULTIPLICATIVE) {	// :899-906
+		if (solve_overlap_coeffs(nb_frames, index.data(), ref_index, Nij, Mij, false, coeffs.data())) return SGPU_GENERIC_ERROR;
+		for (int i = 0; i < N; i++) mul[index[i]] = coeffs[i];
+	}
+	return SGPU_OK;
+}
+
 /* compute_wfwhm_weights (median_and_mean.c:1137-1183): weighted_fwhm of the selected frames (regdata's float) */
 int sgpu_wfwhm_weights(int nb_layers, int N, const float *weighted_fwhm, double *weights) {
 	if (!weighted_fwhm || !weights || N < 1) return SGPU_GENERIC_ERROR;

@@ -313,7 +313,22 @@ __global__ void __launch_bounds__(NT) noise_rows_kernel(const T *d, long nx, lon
 	}
 }
 
+// overlap normalization (normalization.c:549-565): the two images' samples over their common rectangle, kept where
+// BOTH are non-zero (zero elsewhere, which the statistics sweeps skip like the reference's compaction does), WORD data
+// converted with (float) v * invnorm
+template <typename T>
+__global__ void overlap_pair_kernel(const T *pi, const T *pj, long pitch_i, long pitch_j, long w, size_t n, float inv, float *oi, float *oj) {
+	for (size_t k = (size_t) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (size_t) gridDim.x * blockDim.x) {
+		const long r = (long) (k / (size_t) w), c = (long) (k - (size_t) r * w);
+		const T a = pi[(size_t) r * pitch_i + c], b = pj[(size_t) r * pitch_j + c];
+		const bool keep = !(a == (T) 0) && !(b == (T) 0);	// `!x` of a NaN is false: NaN pairs are kept, as in the reference
+		oi[k] = keep ? cvf(a, inv) : 0.f;
+		oj[k] = keep ? cvf(b, inv) : 0.f;
+	}
+}
+
 }  // namespace sgpu
+
 
 using namespace sgpu;
 
@@ -624,7 +639,106 @@ int image_stats_impl(sgpu_ctx *ctx, const T *d, long nx, long ny, int lite, sgpu
 	return SGPU_OK;
 }
 
+// one side of a pair (normalization.c:566-586): median, MAD and — unless lite — IKSSlite location / scale of the `cnt`
+// non-zero samples of d[0..n); IKSSlite's failures are ignored by the reference, which then keeps location 0 / scale 1
+// (or the location it had reached)
+int overlap_side(sgpu_ctx *ctx, const float *d, size_t n, int lite, size_t &cnt, float &med, float &mad, float &loc, float &sca) {
+	const size_t part_bytes = NB * 64;
+	Sweep w{ ctx, d, SGPU_F32, n, (unsigned *) ctx->d_scratch, (char *) ctx->d_scratch + 65536 * sizeof(unsigned), nullptr };
+	w.h_part = (char *) ctx->h_params + 512 * 1024;
+	(void) part_bytes;
+	basic_kernel<float><<<NB, NT, 0, ctx->stream>>>(d, n, (BasicPartial *) w.d_part);
+	ctx->launches++;
+	SGPU_CUDA(ctx, cudaGetLastError());
+	SGPU_CUDA(ctx, cudaMemcpyAsync(w.h_part, w.d_part, NB * sizeof(BasicPartial), cudaMemcpyDeviceToHost, ctx->stream));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	const BasicPartial *bp = (const BasicPartial *) w.h_part;
+	double sum = 0, sum2 = 0; unsigned long long ngood = 0; float nzmn = FLT_MAX, nzmx = -FLT_MAX;
+	for (int i = 0; i < NB; i++) { sum += bp[i].sum; sum2 += bp[i].sum2; ngood += bp[i].ngood; nzmn = std::min(nzmn, bp[i].nzmn); nzmx = std::max(nzmx, bp[i].nzmx); }
+	cnt = (size_t) ngood;
+	med = mad = loc = sca = 0.f;
+	if (cnt <= 3) return SGPU_OK;	// "we want at least 3 pixels with non-zero data to compute stats" (:565)
+	const double mean = sum / ngood, sigma = sqrt(std::max(0.0, sum2 / ngood - mean * mean));
+	Sel s{ 0, 0.f, 0.f, 0, 0.f, 1.f };
+	int rv = hist_median_float<float>(w, s, nzmn, nzmx, cnt, (float) mean, med); if (rv) return rv;
+	Sel sa{ 0, 0.f, 0.f, 1, med, 1.f };
+	float amn, amx; size_t c;
+	rv = minmax_sel<float>(w, sa, amn, amx, c); if (rv) return rv;
+	rv = hist_median_float<float>(w, sa, amn, amx, cnt, (float) (0.6745 * sigma), mad); if (rv) return rv;
+	if (!lite) {
+		double location = 0., scale = 1.;	// `double li = 0., lj = 0., si = 1., sj = 1.;` (:574)
+		if (ikss<float>(w, 1.f, med, mad, location, scale)) ctx->err.clear();
+		loc = (float) location; sca = (float) scale;
+	}
+	return SGPU_OK;
+}
+
 }  // namespace
+
+/* compute_overlap (normalization.c:420-456): dx* / dy* are translation_from_H of the two frames' homographies */
+extern "C" size_t sgpu_compute_overlap(int rxi, int ryi, int rxj, int ryj, double dxi, double dyi, double dxj, double dyj,
+		sgpu_rect *areai, sgpu_rect *areaj) {
+	auto rnd = [](double x) { x = x > 2147483646.5 ? 2147483646.5 : x; x = x < -2147483647.5 ? -2147483647.5 : x; return (int) (x + (x >= 0.0 ? 0.5 : -0.5)); };	// round_to_int, proto.h:208-213
+	int dx = rnd(dxj - dxi), dy = rnd(dyi - dyj);
+	const int x_tli = std::max(0, dx), y_tli = std::max(0, dy);
+	const int x_bri = std::min(rxi, dx + rxj), y_bri = std::min(ryi, dy + ryj);
+	const int x_tlj = std::max(0, -dx), y_tlj = std::max(0, -dy);
+	const int x_brj = std::min(rxj, -dx + rxi), y_brj = std::min(ryj, -dy + ryi);
+	if (x_tli < x_bri && y_tli < y_bri) {
+		if (areai) *areai = sgpu_rect{ x_tli, y_tli, x_bri - x_tli, y_bri - y_tli };
+		if (areaj) *areaj = sgpu_rect{ x_tlj, y_tlj, x_brj - x_tlj, y_brj - y_tlj };
+		return (size_t) ((x_bri - x_tli) * (y_bri - y_tli));	// an int product, as in the reference
+	}
+	return 0;
+}
+
+/* the statistics of one pair of frames on one layer (_compute_estimators_for_images, normalization.c:549-593) */
+extern "C" int sgpu_overlap_stats_pair(sgpu_ctx *ctx, const void *plane_i, int rxi, int ryi, const void *plane_j, int rxj, int ryj,
+		int on_device, int dtype, const sgpu_rect *areai, const sgpu_rect *areaj, int lite, sgpu_overlap_stats *out) {
+	if (!ctx || !plane_i || !plane_j || !areai || !areaj || !out) return SGPU_GENERIC_ERROR;
+	if (dtype != SGPU_F32 && dtype != SGPU_U16) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "bad dtype");
+	memset(out, 0, sizeof *out);
+	const long w = areai->w, h = areai->h;
+	if (w != areaj->w || h != areaj->h || w < 1 || h < 1 || areai->x < 0 || areai->y < 0 || areaj->x < 0 || areaj->y < 0 ||
+	    areai->x + w > rxi || areai->y + h > ryi || areaj->x + w > rxj || areaj->y + h > ryj)
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "overlap rectangles do not fit the frames");
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t es = dtype == SGPU_F32 ? 4 : 2, n = (size_t) w * h;
+	void *staged[2] = { nullptr, nullptr };
+	const void *src[2] = { plane_i, plane_j };
+	const int rx[2] = { rxi, rxj }, ry[2] = { ryi, ryj };
+	const sgpu_rect *ar[2] = { areai, areaj };
+	const char *first[2];	// the rectangle's first sample in memory order: rows are bottom-up, area.y counts from the top
+	long pitch[2];
+	for (int k = 0; k < 2; k++) {
+		const long row0 = ry[k] - ar[k]->y - h;
+		if (on_device) { first[k] = (const char *) src[k] + ((size_t) row0 * rx[k] + ar[k]->x) * es; pitch[k] = rx[k]; continue; }
+		// host planes: only the rows of the rectangle travel (readfits_partial_all_layers reads just that region too)
+		cudaError_t e = cudaMalloc(&staged[k], (size_t) h * rx[k] * es);
+		if (e == cudaSuccess) e = cudaMemcpyAsync(staged[k], (const char *) src[k] + (size_t) row0 * rx[k] * es, (size_t) h * rx[k] * es, cudaMemcpyHostToDevice, ctx->stream);
+		if (e != cudaSuccess) { cudaFree(staged[0]); cudaFree(staged[1]); return sgpu_cuda_fail(ctx, e, "upload overlap rows"); }
+		first[k] = (const char *) staged[k] + (size_t) ar[k]->x * es; pitch[k] = rx[k];
+	}
+	// scratch: [histogram | partials | pair arrays]
+	const size_t head = 65536 * sizeof(unsigned) + NB * 64 + 256;
+	int rv = sgpu_ensure_scratch(ctx, head + 2 * n * sizeof(float));
+	if (!rv) {
+		float *oi = (float *) ((char *) ctx->d_scratch + head), *oj = oi + n;
+		const float inv = 1. / 65535.0;	// `float invnorm = 1. / USHRT_MAX;` (:471)
+		const unsigned grid = (unsigned) std::min<size_t>((n + 255) / 256, (size_t) ctx->sm_count * 16);
+		if (dtype == SGPU_F32) overlap_pair_kernel<float><<<grid, 256, 0, ctx->stream>>>((const float *) first[0], (const float *) first[1], pitch[0], pitch[1], w, n, 1.f, oi, oj);
+		else overlap_pair_kernel<u16><<<grid, 256, 0, ctx->stream>>>((const u16 *) first[0], (const u16 *) first[1], pitch[0], pitch[1], w, n, inv, oi, oj);
+		ctx->launches++;
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) rv = sgpu_cuda_fail(ctx, e, "overlap_pair_kernel");
+		size_t ci = 0, cj = 0;
+		if (!rv) rv = overlap_side(ctx, oi, n, lite, ci, out->medij, out->madij, out->locij, out->scaij);
+		if (!rv) rv = overlap_side(ctx, oj, n, lite, cj, out->medji, out->madji, out->locji, out->scaji);
+		if (!rv) out->Nij = ci > 3 ? ci : 0;	// seq->ostats[n][ijth].Nij is only set when there are more than 3 pairs
+	}
+	if (staged[0] || staged[1]) { cudaStreamSynchronize(ctx->stream); cudaFree(staged[0]); cudaFree(staged[1]); }
+	return rv;
+}
 
 static int image_stats_any(sgpu_ctx *ctx, const void *plane, int on_device, int dtype, long nx, long ny, int lite, sgpu_imstats *out,
 		sgpu_reduce_fn reduce, void *user, long row0, long full_ny);

@@ -17,14 +17,15 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "integration", "_build", "libgpu_stack_harness.so")
 ST_OK, ST_GENERIC_ERROR, ST_CANCEL = 0, -1, -9
-NO_WEIGHT, NOISE_WEIGHT = 0, 3
+NO_WEIGHT, NBSTARS_WEIGHT, WFWHM_WEIGHT, NOISE_WEIGHT = 0, 1, 2, 3
 
 
 class Params(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("N", "C", "H", "W", "is_float", "is_mean", "rejection")] + [("sig", C.c_float * 2)] + \
                [(n, C.c_int) for n in ("normalize", "lite_norm", "weighting", "ref_image", "reglayer", "equalizeRGB")] + \
                [("dx", C.c_void_p), ("dy", C.c_void_p)] + \
-               [(n, C.c_int) for n in ("output_norm", "use_32bit_output", "create_rejmaps", "merge_rejmaps", "cancel_after", "runs")]
+               [(n, C.c_int) for n in ("output_norm", "use_32bit_output", "create_rejmaps", "merge_rejmaps", "cancel_after", "runs")] + \
+               [("wfwhm", C.c_void_p), ("nbstars", C.c_void_p)]
 
 
 @pytest.fixture(scope="module")
@@ -56,7 +57,7 @@ def synth(rng, N, Cn, H, W, dtype):
 
 def run(L, fr, *, is_mean=True, rejection=O.NO_REJEC, sig=(3, 3), normalize=O.NO_NORM, lite_norm=False, weighting=NO_WEIGHT,
         ref_image=0, reglayer=-1, equalizeRGB=False, dx=None, dy=None, output_norm=False, use_32bit_output=True,
-        create_rejmaps=False, merge_rejmaps=False, cancel_after=-1, runs=1):
+        create_rejmaps=False, merge_rejmaps=False, cancel_after=-1, runs=1, wfwhm=None, nbstars=None):
     N, Cn, H, W = fr.shape
     p = Params(N=N, C=Cn, H=H, W=W, is_float=int(fr.dtype == np.float32), is_mean=int(is_mean), rejection=rejection,
                normalize=normalize, lite_norm=int(lite_norm), weighting=weighting, ref_image=ref_image, reglayer=reglayer,
@@ -68,6 +69,12 @@ def run(L, fr, *, is_mean=True, rejection=O.NO_REJEC, sig=(3, 3), normalize=O.NO
         dxa, dya = np.ascontiguousarray(dx, dtype=np.float64), np.ascontiguousarray(dy, dtype=np.float64)
         keep += [dxa, dya]
         p.dx, p.dy = dxa.ctypes.data, dya.ctypes.data
+    if wfwhm is not None:
+        keep.append(np.ascontiguousarray(wfwhm, dtype=np.float32))
+        p.wfwhm = keep[-1].ctypes.data
+    if nbstars is not None:
+        keep.append(np.ascontiguousarray(nbstars, dtype=np.int32))
+        p.nbstars = keep[-1].ctypes.data
     out = np.zeros((Cn, H, W), dtype=np.float32 if use_32bit_output else np.uint16)
     lo = np.zeros((Cn, H, W), dtype=np.uint16)
     hi = np.zeros((Cn, H, W), dtype=np.uint16)
@@ -126,6 +133,8 @@ CASES = [
          shifts=True, create_rejmaps=True),
     dict(rejection=O.PERCENTILE, sig=(0.2, 0.3), dtype=np.float32, Cn=1, normalize=O.ADDITIVE, output_norm=True, shifts=True),
     dict(is_mean=False, dtype=np.float32, Cn=3, normalize=O.ADDITIVE_SCALING, ref_image=1),
+    dict(rejection=O.SIGMA, sig=(3, 3), dtype=np.float32, Cn=1, weighting=WFWHM_WEIGHT, create_rejmaps=True),
+    dict(rejection=O.WINSORIZED, sig=(3, 3), dtype=np.uint16, Cn=3, weighting=NBSTARS_WEIGHT, shifts=True),
     dict(is_mean=False, dtype=np.uint16, Cn=1, use_32bit_output=False, shifts=True),
 ]
 
@@ -142,6 +151,15 @@ def test_method_pointer_matches_oracle(harness, orc, case, max_rows, monkeypatch
     fr = synth(rng, N, Cn, H, W, dtype)
     fr *= (1 + 0.2 * rng.random((N, 1, 1, 1))).astype(fr.dtype) if dtype == np.float32 else 1
     kw = dict(cs)
+    reg_w = None
+    if cs.get("weighting") in (WFWHM_WEIGHT, NBSTARS_WEIGHT):   # registration data of the frames (median_and_mean.c:1137-1230)
+        from oracle.oracle import Oracle
+        fw, ns = rng.uniform(1.5, 6.0, N).astype(np.float32), rng.integers(20, 3000, N).astype(np.int32)
+        kw.update(wfwhm=fw, nbstars=ns)
+        R = Oracle("reference").lib
+        R.ref_reg_weights.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        reg_w = np.zeros((Cn, N))
+        assert R.ref_reg_weights(int(cs["weighting"] == NBSTARS_WEIGHT), Cn, N, fw.ctypes.data, ns.ctypes.data, reg_w.ctypes.data) == 0
     if shifts:
         kw["reglayer"] = kw.get("reglayer", 0) if kw.get("reglayer", -1) >= 0 else 0
         kw.update(dx=rng.integers(-6, 7, N) + rng.uniform(-0.4, 0.4, N), dy=rng.integers(-9, 10, N) + rng.uniform(-0.4, 0.4, N))
@@ -163,6 +181,8 @@ def test_method_pointer_matches_oracle(harness, orc, case, max_rows, monkeypatch
         assert g["cached"] == N * Cn           # add_stats_to_seq: one record per frame and layer
         if cs.get("weighting") == NOISE_WEIGHT and is_mean:
             okw["weights"] = orc.noise_weights(g["scale"], bg)
+    if reg_w is not None:
+        okw["weights"] = reg_w
     if shifts:
         okw.update(shiftx=np.rint(kw["dx"]).astype(np.int32), shifty=np.rint(kw["dy"]).astype(np.int32))
     o = orc.stack(fr, **okw)
