@@ -87,6 +87,10 @@ class StackingArgs:
     number_of_stars: Optional[np.ndarray] = None  # regparam[reglayer][idx].number_of_stars (NBSTARS_WEIGHT)
     stack_count: Optional[np.ndarray] = None      # STACKCNT keyword of each frame (NBSTACK_WEIGHT, median_and_mean.c:150-159)
     bgnoise: Optional[np.ndarray] = None  # seq->stats[layer][idx]->bgnoise, filled by do_normalization
+    overlap_norm: bool = False      # args->overlap_norm (with maximize_framing): normalization by the frames' overlaps (normalization.c:64-67)
+    reg_dx: Optional[np.ndarray] = None   # translation_from_H of every frame (registration.c:301-304), unrounded: the overlaps
+    reg_dy: Optional[np.ndarray] = None
+    overlap_stats: Any = None       # filled by compute_normalization_overlaps: {(layer, i, j): OverlapStats} (seq->ostats)
     feather_dist: int = 0           # > 0: masking (stacking.h:112); `masks` then holds the up-scaled distance masks
     masks: Any = None               # [N][H][W] float32 (torch CUDA tensor or numpy), data->mask[frame] before the ramp (:483-521)
     drizzle: bool = False           # args->drizzle; `drizzle_weights` [N][C][H][W] float32 = data->drizz[frame] (:523-541)
@@ -529,11 +533,62 @@ def finalize_factors(args: StackingArgs, off, mul, sc):
     args.coeff = NormCoeff(offset=off, mul=mul, scale=sc)
 
 
+def compute_normalization_overlaps(args: StackingArgs) -> int:
+    """compute_normalization_overlaps (normalization.c:666-938) on device-resident frames [N][C][H][W]: every pair of
+    frames is levelled on the pixels both have (sgpu_compute_overlap + sgpu_overlap_stats_pair per layer, the
+    reference's `_compute_estimators_for_images`), then one linear system per layer (sgpu_overlap_solve)."""
+    L = _lib.lib()
+    ctx = _context(args)
+    if not _is_torch_cuda(args.frames):
+        raise _lib.SgpuError(ST_GENERIC_ERROR, "overlap normalization takes device-resident frames")
+    frames = args.frames.contiguous()
+    n, c, h, w, dt = _shape_dtype(frames)
+    if not 0 <= args.ref_image < n:     # :690-695
+        raise _lib.SgpuError(ST_GENERIC_ERROR, "The reference image is not in the selected set of images.")
+    dx = np.zeros(n) if args.reg_dx is None else np.asarray(args.reg_dx, dtype=np.float64)
+    dy = np.zeros(n) if args.reg_dy is None else np.asarray(args.reg_dy, dtype=np.float64)
+    es = frames.element_size()
+    Nij = np.zeros((c, n, n), dtype=np.uint64)
+    Mij, Sij = np.zeros((c, n, n)), np.zeros((c, n, n))
+    args.overlap_stats = {}
+    for i in range(n):
+        for j in range(i + 1, n):
+            ai, aj = _lib.Rect(), _lib.Rect()
+            if not L.sgpu_compute_overlap(w, h, w, h, dx[i], dy[i], dx[j], dy[j], C.byref(ai), C.byref(aj)):
+                continue    # "No overlap between image %d and %d"
+            for layer in range(c):
+                st = _lib.OverlapStats()
+                ctx.check(L.sgpu_overlap_stats_pair(ctx.h, frames.data_ptr() + ((i * c + layer) * h * w) * es, w, h,
+                                                    frames.data_ptr() + ((j * c + layer) * h * w) * es, w, h, 1, dt,
+                                                    C.byref(ai), C.byref(aj), int(args.lite_norm), C.byref(st)))
+                args.overlap_stats[(layer, i, j)] = st
+                if st.Nij == 0:
+                    continue
+                if args.lite_norm:  # :796-806
+                    Mij[layer, i, j], Mij[layer, j, i], Sij[layer, i, j], Sij[layer, j, i] = st.medij, st.medji, st.madij, st.madji
+                else:
+                    Mij[layer, i, j], Mij[layer, j, i], Sij[layer, i, j], Sij[layer, j, i] = st.locij, st.locji, st.scaij, st.scaji
+                Nij[layer, i, j] = Nij[layer, j, i] = st.Nij
+    off, mul, sc = np.zeros((c, n)), np.ones((c, n)), np.ones((c, n))    # init_coeffs
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for layer in range(c):
+        m = np.ascontiguousarray(Mij[layer])
+        rv = L.sgpu_overlap_solve(args.normalize, n, args.ref_image, p(np.ascontiguousarray(Nij[layer])), p(m),
+                                  p(np.ascontiguousarray(Sij[layer])), p(off[layer]), p(mul[layer]), p(sc[layer]))
+        if rv:
+            raise _lib.SgpuError(rv, "overlap normalization: the system is singular (a frame overlaps no other)")
+    args.coeff = NormCoeff(offset=off, mul=mul, scale=sc)
+    return ST_OK
+
+
 def do_normalization(args: StackingArgs) -> int:
-    """do_normalization (normalization.c:46-78) -> compute_normalization (:217-294)."""
+    """do_normalization (normalization.c:46-78) -> compute_normalization (:217-294), or, with args->overlap_norm,
+    compute_normalization_overlaps (:64-67, :666-938)."""
     if args.normalize == NO_NORM:
         return ST_OK
     try:
+        if args.overlap_norm:
+            return compute_normalization_overlaps(args)
         off, mul, sc, bg = compute_estimators(args)
         args.bgnoise = bg
         finalize_factors(args, off, mul, sc)

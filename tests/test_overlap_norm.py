@@ -147,3 +147,49 @@ def test_overlap_pair_with_too_few_common_pixels(ref):
     assert out.Nij == 0 and out.medij == 0 and out.scaij == 0
     bad = _lib.Rect(5, 5, 30, 20)
     assert L.sgpu_overlap_stats_pair(ctx.h, fi.ctypes.data, 30, 20, fj.ctypes.data, 30, 20, 0, 1, C.byref(bad), C.byref(bad), 0, C.byref(out)) != 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("normalize", [O.ADDITIVE_SCALING, O.MULTIPLICATIVE], ids=["addscale", "mul"])
+def test_do_normalization_by_overlaps_levels_a_mosaic(ref, normalize):
+    """do_normalization with args->overlap_norm (normalization.c:64-67): four panels of one sky, each with its own gain
+    and pedestal, shifted against each other; coefficients against the reference's own lines driven pair by pair"""
+    torch = pytest.importorskip("torch")
+    import siril_b200 as sb
+    from siril_b200 import _lib
+    L, R = _lib.lib(), _ref_lib(ref)
+    rng = np.random.default_rng(3)
+    N, Cn, H, W = 4, 2, 120, 160
+    yy, xx = np.mgrid[0:H + 80, 0:W + 80]
+    sky = 0.1 + 0.05 * np.sin(xx / 29.0) * np.cos(yy / 31.0)
+    dx, dy = np.array([0.0, 37.4, -12.6, 40.2]), np.array([0.0, -8.3, 33.7, 30.1])
+    gain, ped = np.array([1.0, 1.15, 0.9, 1.05]), np.array([0.0, 0.01, -0.004, 0.02]) * (normalize != O.MULTIPLICATIVE)
+    fr = np.zeros((N, Cn, H, W), dtype=np.float32)
+    for f in range(N):      # frame f sees the sky displaced by its registration shift (x to the right, y up in display terms)
+        ox, oy = 40 - int(round(dx[f])), 40 - int(round(dy[f]))
+        for l in range(Cn):
+            view = sky[oy:oy + H, ox:ox + W][::-1] * (1 + 0.1 * l)
+            fr[f, l] = (gain[f] * view + ped[f] + 0.004 * rng.standard_normal((H, W))).astype(np.float32)
+    fr[rng.random(fr.shape) < 0.01] = 0
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=torch.from_numpy(fr).cuda(), normalize=normalize,
+                           overlap_norm=True, reg_dx=dx, reg_dy=dy, ref_image=1)
+    assert sb.do_normalization(args) == 0
+    # the same through the reference: rectangles, per-pair statistics, solves
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for l in range(Cn):
+        Nij = np.zeros((N, N), dtype=np.uint64); Mij = np.zeros((N, N)); Sij = np.zeros((N, N))
+        for i in range(N):
+            for j in range(i + 1, N):
+                ei, ej = np.zeros(4, dtype=np.int32), np.zeros(4, dtype=np.int32)
+                n = R.ref_compute_overlap(W, H, W, H, dx[i], dy[i], dx[j], dy[j], ei.ctypes.data, ej.ctypes.data)
+                assert n > 0
+                reg = lambda f, a: np.ascontiguousarray(f[H - a[1] - a[3]: H - a[1], a[0]: a[0] + a[2]])
+                o = np.zeros(9)
+                R.ref_overlap_pair(1, reg(fr[i, l], ei).ctypes.data, reg(fr[j, l], ej).ctypes.data, n, 0, o.ctypes.data)
+                Nij[i, j] = Nij[j, i] = int(o[0]); Mij[i, j], Mij[j, i], Sij[i, j], Sij[j, i] = o[5], o[6], o[7], o[8]
+        exp = [np.zeros(N), np.ones(N), np.ones(N)]
+        assert R.ref_overlap_solve(normalize, N, 1, p(Nij), p(Mij), p(Sij), *[p(a) for a in exp]) == 0
+        for got, e in zip((args.coeff.offset[l], args.coeff.mul[l], args.coeff.scale[l]), exp):
+            np.testing.assert_allclose(got, e, rtol=2e-6, atol=1e-9)   # scaij is a float of double sums (3e-7), then a solve
+        if normalize == O.MULTIPLICATIVE:     # and the mosaic is levelled: mul_f = gain_ref / gain_f
+            np.testing.assert_allclose(args.coeff.mul[l], gain[1] / gain, rtol=5e-3)
