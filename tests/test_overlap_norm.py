@@ -115,7 +115,8 @@ def test_overlap_pair_statistics_match_the_reference(ref, dtype, lite, on_device
         # what readfits_partial_all_layers hands the reference: the rectangle's rows in memory (bottom-up) order
         reg = lambda f, a, ry: np.ascontiguousarray(f[ry - a.y - a.h: ry - a.y, a.x: a.x + a.w])
         exp = np.zeros(9)
-        assert R.ref_overlap_pair(int(dtype == np.float32), reg(fi, ai, ryi).ctypes.data, reg(fj, aj, ryj).ctypes.data, n, lite, exp.ctypes.data) == 0
+        ri, rj = reg(fi, ai, ryi), reg(fj, aj, ryj)
+        assert R.ref_overlap_pair(int(dtype == np.float32), ri.ctypes.data, rj.ctypes.data, n, lite, exp.ctypes.data) == 0
         if on_device:
             dev = lambda f: torch.from_numpy(f.view(np.int16) if f.dtype == np.uint16 else f).cuda()
             ti, tj = dev(fi), dev(fj)
@@ -185,7 +186,8 @@ def test_do_normalization_by_overlaps_levels_a_mosaic(ref, normalize):
                 assert n > 0
                 reg = lambda f, a: np.ascontiguousarray(f[H - a[1] - a[3]: H - a[1], a[0]: a[0] + a[2]])
                 o = np.zeros(9)
-                R.ref_overlap_pair(1, reg(fr[i, l], ei).ctypes.data, reg(fr[j, l], ej).ctypes.data, n, 0, o.ctypes.data)
+                ri, rj = reg(fr[i, l], ei), reg(fr[j, l], ej)
+                R.ref_overlap_pair(1, ri.ctypes.data, rj.ctypes.data, n, 0, o.ctypes.data)
                 Nij[i, j] = Nij[j, i] = int(o[0]); Mij[i, j], Mij[j, i], Sij[i, j], Sij[j, i] = o[5], o[6], o[7], o[8]
         exp = [np.zeros(N), np.ones(N), np.ones(N)]
         assert R.ref_overlap_solve(normalize, N, 1, p(Nij), p(Mij), p(Sij), *[p(a) for a in exp]) == 0
