@@ -161,13 +161,13 @@ def test_do_normalization_by_overlaps_levels_a_mosaic(ref, normalize):
     L, R = _lib.lib(), _ref_lib(ref)
     rng = np.random.default_rng(3)
     N, Cn, H, W = 4, 2, 120, 160
-    yy, xx = np.mgrid[0:H + 80, 0:W + 80]
+    yy, xx = np.mgrid[0:H + 100, 0:W + 100]
     sky = 0.1 + 0.05 * np.sin(xx / 29.0) * np.cos(yy / 31.0)
     dx, dy = np.array([0.0, 37.4, -12.6, 40.2]), np.array([0.0, -8.3, 33.7, 30.1])
     gain, ped = np.array([1.0, 1.15, 0.9, 1.05]), np.array([0.0, 0.01, -0.004, 0.02]) * (normalize != O.MULTIPLICATIVE)
     fr = np.zeros((N, Cn, H, W), dtype=np.float32)
     for f in range(N):      # frame f sees the sky displaced by its registration shift (x to the right, y up in display terms)
-        ox, oy = 40 - int(round(dx[f])), 40 - int(round(dy[f]))
+        ox, oy = 50 + int(round(dx[f])), 50 - int(round(dy[f]))   # x_j = x_i - (dx_j - dx_i), y likewise top-down (normalization.c:427-447)
         for l in range(Cn):
             view = sky[oy:oy + H, ox:ox + W][::-1] * (1 + 0.1 * l)
             fr[f, l] = (gain[f] * view + ped[f] + 0.004 * rng.standard_normal((H, W))).astype(np.float32)
