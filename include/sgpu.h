@@ -288,6 +288,14 @@ typedef int (*sgpu_reduce_fn)(void *user, void *host_buf, size_t count, int dtyp
 int sgpu_image_stats_sharded(sgpu_ctx *ctx, const void *shard, int on_device, int dtype, long nx, long ny,
 		long row0, long full_ny, int lite, sgpu_reduce_fn reduce, void *user, sgpu_imstats *out);
 
+/* the statistics cache across runs: one `M<layer>-<image> ...` line of a .seq file per cached imstats,
+ * exactly as writeseqfile prints it (io/seqfile.c:838-853: %ld counts, %lg — six significant digits — for the rest) and
+ * readseqfile parses it (:544-611; '*' in place of the layer marks CFA statistics and maps to layer 0).  A caller that
+ * caches sgpu_image_stats results this way gets the reference's second-run behaviour, rounding included.
+ * SGPU_SEQUENCE_ERROR for a line that is not a statistics record. */
+int sgpu_imstats_seq_record(int layer, int image_index, const sgpu_imstats *st, char *line, size_t cap);
+int sgpu_imstats_from_seq_record(const char *line, int *layer, int *image_index, sgpu_imstats *st);
+
 /* host-side scalar work, [nb_layers * nb_frames] arrays */
 /* _compute_estimators_for_image's choice of estimators (normalization.c:98-141) */
 int sgpu_estimators_from_stats(int normalize, int lite, const sgpu_imstats *st,

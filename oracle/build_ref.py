@@ -64,6 +64,9 @@ RANGES = {
     "norm_compute_overlap": ("src/stacking/normalization.c", 420, 456, None),
     "norm_overlap_layers":  ("src/stacking/normalization.c", 549, 593, None),
     "norm_overlap_solves":  ("src/stacking/normalization.c", 875, 906, None),
+    # --- statistics records of the .seq file ---
+    "seq_stats_write":   ("src/io/seqfile.c", 838, 853, None),
+    "seq_stats_read":    ("src/io/seqfile.c", 584, 600, None),
     "reg_translation_from_H": ("src/registration/registration.c", 301, 304, None),
     # --- sum / min / max stackers (ref_simple.c) ---
     "sum_pixel_loop":    ("src/stacking/sum.c", 186, 231, None),

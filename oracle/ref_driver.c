@@ -25,6 +25,7 @@
 #include <gsl/gsl_statistics_ushort.h>
 #include <gsl/gsl_linalg.h>
 #include <limits.h>
+#include <stdio.h>
 
 /* the shim fits/sequence are opaque in core/siril.h; the few members the extracted ranges
  * touch are provided by these layouts (same first members as the shim structs). */
@@ -422,6 +423,33 @@ int ref_reg_weights(int use_nbstars, int nb_layers, int N, const float *wfwhm, c
 	if (args.weights) memcpy(weights, args.weights, (size_t) nb_layers * N * sizeof(double));
 	free(args.weights); free(idx); free(rd);
 	return rv;
+}
+
+/* ---- the statistics records of a .seq file: the reference's own fprintf (seqfile.c:838-853) and sscanf (:584-600) ---- */
+typedef struct { imstats ***stats; int cfa_opened_monochrome; } ref_seq_view;
+int ref_seq_stats_write(int layer, int i, const double v[14], char *out, size_t cap) {
+	imstats st; memset(&st, 0, sizeof st);
+	st.total = (long) v[0]; st.ngoodpix = (long) v[1]; st.mean = v[2]; st.median = v[3]; st.sigma = v[4]; st.avgDev = v[5];
+	st.mad = v[6]; st.sqrtbwmv = v[7]; st.location = v[8]; st.scale = v[9]; st.min = v[10]; st.max = v[11]; st.normValue = v[12]; st.bgnoise = v[13];
+	imstats *row_[1] = { &st }; imstats **row = row_ - i;
+	imstats **layers_[3] = { 0, 0, 0 }; layers_[layer] = row;
+	ref_seq_view sv = { layers_, 0 }, *seq = &sv;
+	char *buf = NULL; size_t len = 0;
+	FILE *seqfile = open_memstream(&buf, &len);
+#include "gen/seq_stats_write.inc"
+	fclose(seqfile);
+	if (len + 1 > cap) { free(buf); return 1; }
+	memcpy(out, buf, len + 1); free(buf);
+	return 0;
+}
+int ref_seq_stats_read(const char *line, int *image_out, double v[14]) {
+	imstats st, *stats = &st; memset(&st, 0, sizeof st);
+	int image = -1, nb_tokens;
+#include "gen/seq_stats_read.inc"
+	*image_out = image;
+	v[0] = (double) st.total; v[1] = (double) st.ngoodpix; v[2] = st.mean; v[3] = st.median; v[4] = st.sigma; v[5] = st.avgDev;
+	v[6] = st.mad; v[7] = st.sqrtbwmv; v[8] = st.location; v[9] = st.scale; v[10] = st.min; v[11] = st.max; v[12] = st.normValue; v[13] = st.bgnoise;
+	return nb_tokens;
 }
 
 /* ---- overlap normalization: the reference's own lines around in-RAM data ---- */

@@ -104,6 +104,8 @@ SIGNATURES = {
     "sgpu_image_stats": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_int, C.POINTER(ImStats)]),
     "sgpu_image_stats_sharded": (C.c_int, [P, P, C.c_int, C.c_int, C.c_long, C.c_long, C.c_long, C.c_long, C.c_int, P, P,
                                            C.POINTER(ImStats)]),
+    "sgpu_imstats_seq_record": (C.c_int, [C.c_int, C.c_int, C.POINTER(ImStats), C.c_char_p, C.c_size_t]),
+    "sgpu_imstats_from_seq_record": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(ImStats)]),
     "sgpu_estimators_from_stats": (C.c_int, [C.c_int, C.c_int, C.POINTER(ImStats), C.POINTER(C.c_double),
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "sgpu_compute_factors": (C.c_int, [C.c_int] * 6 + [P, P, P]),

@@ -562,6 +562,32 @@ int sgpu_noise_weights(int nb_layers, int N, const double *scale, const double *
 	return SGPU_OK;
 }
 
+/* the statistics cache's record in a .seq file: written by writeseqfile (io/seqfile.c:838-853), read back by readseqfile
+ * (:544-611).  The reference prints with %lg — six significant digits — so a second run works from the ROUNDED numbers;
+ * the same format keeps that behaviour. */
+int sgpu_imstats_seq_record(int layer, int image_index, const sgpu_imstats *st, char *line, size_t cap) {
+	if (!st || !line || layer < 0 || layer > 9) return SGPU_GENERIC_ERROR;
+	const int n = snprintf(line, cap, "M%c-%d %ld %ld %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg\n", '0' + layer, image_index,
+			(long) st->total, (long) st->ngoodpix, st->mean, st->median, st->sigma, st->avgDev, st->mad, st->sqrtbwmv,
+			st->location, st->scale, st->min, st->max, st->normValue, st->bgnoise);
+	return (n < 0 || (size_t) n >= cap) ? SGPU_GENERIC_ERROR : SGPU_OK;
+}
+
+int sgpu_imstats_from_seq_record(const char *line, int *layer, int *image_index, sgpu_imstats *st) {
+	if (!line || !layer || !image_index || !st) return SGPU_GENERIC_ERROR;
+	if (line[0] != 'M' || line[1] == '\0') return SGPU_SEQUENCE_ERROR;
+	const int cur = line[1] == '*' ? 0 : line[1] - '0';	// '*': statistics of the CFA channel (:549-560)
+	if (cur < 0 || cur > 9 || line[2] != '-') return SGPU_SEQUENCE_ERROR;	// "sequence file format error"
+	long total, ngood; int image;
+	sgpu_imstats t;
+	const int tokens = sscanf(line + 3, "%d %ld %ld %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg %lg", &image, &total, &ngood,
+			&t.mean, &t.median, &t.sigma, &t.avgDev, &t.mad, &t.sqrtbwmv, &t.location, &t.scale, &t.min, &t.max, &t.normValue, &t.bgnoise);
+	if (tokens != 15) return SGPU_SEQUENCE_ERROR;
+	t.total = (double) total; t.ngoodpix = (double) ngood;
+	*st = t; *layer = cur; *image_index = image;
+	return SGPU_OK;
+}
+
 /* solve_overlap_coeffs (normalization.c:296-355): the (nb_frames - 1)^2 system of one layer, then LU with partial pivoting */
 static int solve_overlap_coeffs(int nb_frames, const int *index, int index_ref, const size_t *Nij, const double *Mij, bool additive, double *coeffs) {
 	const int N = nb_frames - 1;

@@ -135,3 +135,37 @@ def test_siril_glue_builds_against_the_reference_header_and_keeps_its_symbols():
     for name in ("stack_mean_with_rejection", "stack_median", "do_normalization", "gpu_stack_mean_or_median",
                  "gpu_do_normalization", "harness_stack"):
         assert hasattr(H, name), name
+
+
+def test_seq_statistics_records_match_the_reference(ref):
+    """the .seq file's `M` records (io/seqfile.c:838-853 written, :544-611 read): same text as the reference's own fprintf,
+    same numbers back as its sscanf — %lg's six digits included"""
+    from siril_b200 import _lib
+    L, R = _lib.lib(), ref.lib
+    R.ref_seq_stats_write.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_char_p, C.c_size_t]
+    R.ref_seq_stats_read.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.c_void_p]
+    rng = np.random.default_rng(12)
+    for k in range(200):
+        v = np.concatenate([[float(rng.integers(1, 1 << 33)), float(rng.integers(0, 1 << 33))],
+                            rng.standard_normal(12) * 10.0 ** rng.integers(-8, 8, 12)])
+        if k % 7 == 0:
+            v[2:] = np.round(v[2:])
+        if k % 11 == 0:
+            v[5] = v[7] = 0.0
+        st = _lib.ImStats(*v.tolist())
+        layer, image = int(rng.integers(0, 3)), int(rng.integers(0, 100000))
+        mine, theirs = C.create_string_buffer(1024), C.create_string_buffer(1024)
+        assert L.sgpu_imstats_seq_record(layer, image, C.byref(st), mine, 1024) == 0
+        assert R.ref_seq_stats_write(layer, image, v.ctypes.data, theirs, 1024) == 0
+        assert mine.value == theirs.value and mine.value.startswith(b"M%d-%d " % (layer, image))
+        back, gl, gi = _lib.ImStats(), C.c_int(), C.c_int()
+        assert L.sgpu_imstats_from_seq_record(mine.value, C.byref(gl), C.byref(gi), C.byref(back)) == 0
+        exp, ei = np.zeros(14), C.c_int()
+        assert R.ref_seq_stats_read(theirs.value, C.byref(ei), exp.ctypes.data) == 15
+        assert (gl.value, gi.value) == (layer, image) and ei.value == image
+        assert [getattr(back, n) for n, _ in _lib.ImStats._fields_] == exp.tolist()
+    last = mine.value
+    assert L.sgpu_imstats_seq_record(0, 1, C.byref(st), mine, 10) != 0            # buffer too small
+    assert L.sgpu_imstats_from_seq_record(b"R0 1 2 3", C.byref(gl), C.byref(gi), C.byref(back)) == -2
+    assert L.sgpu_imstats_from_seq_record(b"M0-3 12 11 0.5", C.byref(gl), C.byref(gi), C.byref(back)) == -2
+    assert L.sgpu_imstats_from_seq_record(b"M*-3 " + last.split(b" ", 1)[1], C.byref(gl), C.byref(gi), C.byref(back)) == 0 and gl.value == 0
