@@ -114,8 +114,11 @@ def config_of(args, wl, world, extra=None):
     cfg = {"workload": label, "name": args.workload, "rejection": REJ_NAMES[rej] if is_mean else "median",
            "frames": n, "width": w, "height": h, "layers": c, "rejection_maps": N_REJMAPS if is_mean and rej != NO_REJEC else 0,
            "l2": "inputs larger than L2 (%.1f GB per step)" % (n * c * h * w * (4 if dt == "f32" else 2) / 1e9),
-           "sharding": ("rows [H*g/N, H*(g+1)/N) of one image per rank; output rows and both rejection maps gathered to rank 0 "
-                        "with NCCL, counters all-reduced") if world > 1 else "single GPU"}
+           "sharding": (("rows [H*g/N, H*(g+1)/N) of one image per rank; every rank's kernels store its output rows and both rejection "
+                         "maps straight into the image on rank 0 over NVLink (peer mapping), counters all-reduced")
+                        if getattr(args, "gather", "peer") == "peer" else
+                        ("rows [H*g/N, H*(g+1)/N) of one image per rank; output rows and both rejection maps gathered to rank 0 "
+                         "with NCCL, counters all-reduced")) if world > 1 else "single GPU"}
     if extra:
         cfg.update(extra)
     return cfg
@@ -315,19 +318,33 @@ def run_ours(args, wl):
     rhi = torch.zeros((c, h, w), dtype=torch.uint16, device=dev) if maps else None
     irej = torch.zeros(6, dtype=torch.int64, device=dev)
     full = None
-    if world > 1 and rank == 0:     # the whole image on rank 0: [C][H][W] result and both maps
+    peer = None
+    if world > 1 and args.gather == "peer":
+        # the whole image lives on rank 0 and every rank's kernels store their rows straight into it over NVLink
+        # (CUDA IPC mapping, sharding.PeerImage): no gather step; what remains per step is the counters' all-reduce
+        peer = sharding.PeerImage(dist, ctx, c, H, w, 2 if maps else 0)
+        cargs.out_plane_stride = H * w
+        p_out, p_lo, p_hi = peer.pointers(r0)
+    elif world > 1 and rank == 0:     # the whole image on rank 0: [C][H][W] result and both maps
         full = [torch.empty((c, H, w), dtype=torch.float32, device=dev)] + \
                ([torch.empty((c, H, w), dtype=torch.uint16, device=dev) for _ in range(2)] if maps else [])
     bounds = [sharding.row_shard(H, g, world) for g in range(world)]
 
     def stack():
         irej.zero_()
+        if peer is not None:
+            ctx.check(L.sgpu_stack_block(ctx.h, blk, C.byref(cargs), C.c_void_p(p_out), C.c_void_p(p_lo) if maps else None,
+                                         C.c_void_p(p_hi) if maps else None, C.c_void_p(irej.data_ptr())))
+            return
         ctx.check(L.sgpu_stack_block(ctx.h, blk, C.byref(cargs), C.c_void_p(out.data_ptr()),
                                      C.c_void_p(rlo.data_ptr()) if maps else None, C.c_void_p(rhi.data_ptr()) if maps else None,
                                      C.c_void_p(irej.data_ptr())))
 
     def gather():
         """output rows and rejection maps of every rank into the image on rank 0; counters summed"""
+        if peer is not None:        # the rows are already in rank 0's image (or on their way: the timed region ends with
+            dist.all_reduce(irej)   # a device synchronize on every rank and a barrier)
+            return
         # (torch's NCCL binding has no 16-bit integer type: the maps travel as byte views of the same memory)
         i16 = lambda t: t.view(torch.uint8) if t.dtype == torch.uint16 else t    # noqa: E731
         parts = [i16(t) for t in [out] + ([rlo, rhi] if maps else [])]
@@ -499,6 +516,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="target", choices=sorted(WORKLOADS))
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how the rows reach rank 0 — stored into its image by the stacking kernels over NVLink (peer), "
+                         "or sent after the stack with NCCL send / recv (nccl)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's image height")

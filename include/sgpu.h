@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SGPU_ABI_VERSION 4
+#define SGPU_ABI_VERSION 5
 
 enum {	/* stacking.h:18-24 */
 	SGPU_OK = 0,
@@ -96,6 +96,18 @@ int sgpu_mem_info(sgpu_ctx *ctx, size_t *free_bytes, size_t *total_bytes);
 int sgpu_device_alloc(sgpu_ctx *ctx, size_t bytes, void **dev_ptr);
 void sgpu_device_free(sgpu_ctx *ctx, void *dev_ptr);
 int sgpu_download(sgpu_ctx *ctx, void *host_dst, const void *dev_src, size_t bytes);
+
+/* Outputs on a peer GPU ("output rows plus rejection maps gathered over NVLink").  One process per GPU:
+ * the root exports the image it allocated with sgpu_device_alloc, every other rank opens it and hands sgpu_stack_block
+ * pointers INTO it (its own rows; out_plane_stride = the image's plane): the stacking kernels' stores then travel over
+ * NVLink / NVSwitch while the stack is still being computed and no gather follows — the assembly of the result image that
+ * the reference does by writing every block into one fits (median_and_mean.c:1717-1734).  The writer's
+ * sgpu_ctx_synchronize (then a barrier between the processes) makes the rows visible to the owner.
+ * CUDA IPC underneath: same node, peer access between the two GPUs. */
+#define SGPU_IPC_HANDLE_BYTES 64
+int sgpu_ipc_export(sgpu_ctx *ctx, void *dev_ptr, unsigned char handle[SGPU_IPC_HANDLE_BYTES]);
+int sgpu_ipc_open(sgpu_ctx *ctx, const unsigned char handle[SGPU_IPC_HANDLE_BYTES], void **peer_ptr);
+int sgpu_ipc_close(sgpu_ctx *ctx, void *peer_ptr);
 
 /* pinned host memory for the upload / download legs */
 int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr);
@@ -191,6 +203,9 @@ typedef struct {
 	int nb_critical;		/* entries critical_value holds; 0: not stated (trusted to be (int) floor((float) nb_frames * sig[0])) */
 	int source_bitpix;		/* seq->bitpix of the frames as they were on disk; only 8 (BYTE_IMG) matters: with a 16-bit output and
 					 * output_norm the result is scaled by 65535/255 (normalize_to16bit, median_and_mean.c:547-555,1729-1733); 0: unknown */
+	size_t out_plane_stride;	/* sgpu_stack_block: elements between the layers of d_out / d_rej_low / d_rej_high; 0: height * width (dense).
+					 * A row shard that writes its rows straight into a taller image (its own or a peer GPU's, see
+					 * sgpu_ipc_open) passes the image's plane size and pointers to its first row. */
 	int engine;			/* 0: automatic; 1: force the exact thread-per-pixel engine; 2: force the sorted engine; 5: force the lane-sort engine; 6: force the selection engine */
 } sgpu_stack_args;
 

@@ -28,7 +28,7 @@ class StackArgs(C.Structure):
                 ("weights", C.c_void_p), ("shiftx", C.c_void_p),
                 ("output_norm", C.c_int), ("use_32bit_output", C.c_int),
                 ("create_rejmaps", C.c_int), ("merge_lowhigh_rejmaps", C.c_int), ("nb_critical", C.c_int),
-                ("source_bitpix", C.c_int), ("engine", C.c_int)]
+                ("source_bitpix", C.c_int), ("out_plane_stride", C.c_size_t), ("engine", C.c_int)]
 
 
 class ImStats(C.Structure):
@@ -81,6 +81,9 @@ SIGNATURES = {
     "sgpu_device_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_device_free": (None, [P, P]),
     "sgpu_download": (C.c_int, [P, P, P, C.c_size_t]),
+    "sgpu_ipc_export": (C.c_int, [P, P, P]),
+    "sgpu_ipc_open": (C.c_int, [P, P, C.POINTER(P)]),
+    "sgpu_ipc_close": (C.c_int, [P, P]),
     "sgpu_host_alloc": (C.c_int, [P, C.c_size_t, C.POINTER(P)]),
     "sgpu_host_free": (None, [P, P]),
     "sgpu_block_create": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P)]),

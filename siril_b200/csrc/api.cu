@@ -144,6 +144,34 @@ int sgpu_download(sgpu_ctx *ctx, void *host_dst, const void *dev_src, size_t byt
 	return SGPU_OK;
 }
 
+int sgpu_ipc_export(sgpu_ctx *ctx, void *dev_ptr, unsigned char handle[SGPU_IPC_HANDLE_BYTES]) {
+	static_assert(sizeof(cudaIpcMemHandle_t) == SGPU_IPC_HANDLE_BYTES, "handle size");
+	if (!ctx || !dev_ptr || !handle) return SGPU_GENERIC_ERROR;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaIpcMemHandle_t h;
+	SGPU_CUDA(ctx, cudaIpcGetMemHandle(&h, dev_ptr));
+	memcpy(handle, &h, sizeof h);
+	return SGPU_OK;
+}
+int sgpu_ipc_open(sgpu_ctx *ctx, const unsigned char handle[SGPU_IPC_HANDLE_BYTES], void **peer_ptr) {
+	if (!ctx || !handle || !peer_ptr) return SGPU_GENERIC_ERROR;
+	*peer_ptr = nullptr;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaIpcMemHandle_t h;
+	memcpy(&h, handle, sizeof h);
+	cudaError_t e = cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+	if (e != cudaSuccess) { *peer_ptr = nullptr; return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "cannot map the peer's image (cudaIpcOpenMemHandle: %s)", cudaGetErrorString(e)); }
+	return SGPU_OK;
+}
+int sgpu_ipc_close(sgpu_ctx *ctx, void *peer_ptr) {
+	if (!ctx) return SGPU_GENERIC_ERROR;
+	if (!peer_ptr) return SGPU_OK;
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	SGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	SGPU_CUDA(ctx, cudaIpcCloseMemHandle(peer_ptr));
+	return SGPU_OK;
+}
+
 int sgpu_host_alloc(sgpu_ctx *ctx, size_t bytes, void **ptr) {
 	if (!ctx || !ptr) return SGPU_GENERIC_ERROR;
 	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -285,6 +313,8 @@ static int check_args(sgpu_ctx *ctx, const sgpu_block_desc &d, const sgpu_stack_
 	if (a->is_mean && a->type_of_rejection == SGPU_GESDT && a->nb_critical > 0 && a->nb_critical < (int) floorf((float) d.nb_frames * a->sig[0]))
 		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "GESDT: %d critical values given, %d needed", a->nb_critical, (int) floorf((float) d.nb_frames * a->sig[0]));
 	if (!a->use_32bit_output && d.dtype == SGPU_F32) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "16-bit output needs 16-bit input");
+	if (a->out_plane_stride && a->out_plane_stride < (size_t) d.height * d.width)
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "output plane stride %zu is smaller than the block's plane (%d x %d)", a->out_plane_stride, d.width, d.height);
 	return SGPU_OK;
 }
 
@@ -467,7 +497,8 @@ int sgpu_stack_host_impl(sgpu_ctx *ctx, const sgpu_block_desc *desc, const std::
 		char *d_out = d_buf + off * out_es;
 		uint16_t *d_lo = nmaps >= 1 ? (uint16_t *) (d_buf + out_bytes) + off : nullptr;
 		uint16_t *d_hi = nmaps == 2 ? (uint16_t *) (d_buf + out_bytes + map_bytes) + off : nullptr;
-		rv = sgpu_stack_block(ctx, blks[k], a, d_out, d_lo, d_hi, d_irej);
+		sgpu_stack_args dense = *a; dense.out_plane_stride = 0;	// the row blocks' outputs are dense staging planes
+		rv = sgpu_stack_block(ctx, blks[k], &dense, d_out, d_lo, d_hi, d_irej);
 		if (rv) return cleanup(rv);
 		if (cudaEventRecord(done[k], compute) != cudaSuccess) return cleanup(SGPU_GENERIC_ERROR);
 		for (int l = 0; l < C; l++) {

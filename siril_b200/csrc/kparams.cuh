@@ -17,6 +17,7 @@ struct StackParams {
 	int is_mean, output_norm, out32, rejmaps;	// rejmaps: 0 none, 1 merged, 2 low+high
 	int norm16;		// 8-bit frames, 16-bit output, output_norm: the result is scaled by 65535/255 (normalize_to16bit)
 	void *out; u16 *rej_low, *rej_high;
+	size_t out_plane;	// elements between the layers of out / rej_low / rej_high (H * W unless the caller's image is taller than the block)
 	unsigned long long *irej;	// [3][2]
 	void *scratch;		// exact engine: global columns when the tile does not fit in shared memory
 	int use_aux;

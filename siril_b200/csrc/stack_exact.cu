@@ -39,7 +39,7 @@ __device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, siz
 	} else {
 		result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
 	}
-	store_result<T>(p, (size_t) layer * npix + pix, result, rej);
+	store_result<T>(p, (size_t) layer * p.out_plane + pix, result, rej);
 }
 
 template <typename T, bool SMEM, bool LIST>
@@ -116,6 +116,7 @@ void sgpu_fill_stack_params(StackParams &p, sgpu_block *blk, const sgpu_stack_ar
 	p.is_mean = a->is_mean; p.output_norm = a->output_norm; p.out32 = a->use_32bit_output;
 	p.norm16 = a->source_bitpix == 8 && a->output_norm && !a->use_32bit_output;
 	p.rejmaps = (a->is_mean && a->create_rejmaps) ? (a->merge_lowhigh_rejmaps ? 1 : 2) : 0;
+	p.out_plane = a->out_plane_stride ? a->out_plane_stride : (size_t) d.height * d.width;
 	p.out = d_out; p.rej_low = d_rej_low; p.rej_high = d_rej_high; p.irej = (unsigned long long *) d_irej;
 	p.use_aux = a->is_mean && (p.rc.type == SGPU_MAD || p.rc.type == SGPU_GESDT);
 }

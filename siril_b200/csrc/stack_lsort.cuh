@@ -255,8 +255,8 @@ __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) /
 			}
 		}
 		if (status == FAST_DONE) {
-			if (p.is_u16) store_result<u16>(p, (size_t) layer * npix + pix, result, rej);
-			else store_result<float>(p, (size_t) layer * npix + pix, result, rej);
+			if (p.is_u16) store_result<u16>(p, (size_t) layer * p.out_plane + pix, result, rej);
+			else store_result<float>(p, (size_t) layer * p.out_plane + pix, result, rej);
 		} else {
 			rej[0] = rej[1] = 0;
 			p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pix;

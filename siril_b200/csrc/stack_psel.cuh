@@ -218,8 +218,8 @@ __device__ __forceinline__ void psel_finish(const StackParams &p, const Store &c
 		if (p.dbg_stop == 4 && result != 123.456) return;	// timing: the rejection without the stores
 		if (!store) rej[0] = rej[1] = 0;
 		else if (status == FAST_DONE) {
-			if (p.is_u16) store_result<u16>(p, (size_t) layer * npix + pix, result, rej);
-			else store_result<float>(p, (size_t) layer * npix + pix, result, rej);
+			if (p.is_u16) store_result<u16>(p, (size_t) layer * p.out_plane + pix, result, rej);
+			else store_result<float>(p, (size_t) layer * p.out_plane + pix, result, rej);
 		} else {
 			rej[0] = rej[1] = 0;
 			p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pix;

@@ -68,8 +68,8 @@ __global__ void __launch_bounds__(FIN_THREADS) stack_psel_finish_kernel(const St
 			result = psel_pixel<false>(col, h, N, p.is_mean, p.rc, w, orig, rej, &status, p.rcp_tab);
 		}
 		if (status == FAST_DONE) {
-			if (p.is_u16) store_result<u16>(p, (size_t) layer * npix + pix, result, rej);
-			else store_result<float>(p, (size_t) layer * npix + pix, result, rej);
+			if (p.is_u16) store_result<u16>(p, (size_t) layer * p.out_plane + pix, result, rej);
+			else store_result<float>(p, (size_t) layer * p.out_plane + pix, result, rej);
 		} else {
 			rej[0] = rej[1] = 0;
 			p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pix;

@@ -285,8 +285,8 @@ __global__ void __launch_bounds__(SORT_WARPS * 32, (RE > 44 ? 12 : (RE > 25 ? 16
 			}
 		}
 		if (status == FAST_DONE) {
-			if (p.is_u16) store_result<u16>(p, (size_t) layer * npix + pix, result, rej);
-			else store_result<float>(p, (size_t) layer * npix + pix, result, rej);
+			if (p.is_u16) store_result<u16>(p, (size_t) layer * p.out_plane + pix, result, rej);
+			else store_result<float>(p, (size_t) layer * p.out_plane + pix, result, rej);
 		} else {
 			rej[0] = rej[1] = 0;
 			p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pix;

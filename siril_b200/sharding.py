@@ -102,3 +102,68 @@ def reduce_minmax(dist, mn, mx, device=None):
     if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return -float(t[0]), float(t[1])
+
+
+class PeerImage:
+    """The result image [C][H][W] float32 (or uint16) and its rejection maps, allocated once on rank `root` and mapped by
+    every other rank (sgpu_ipc_export / sgpu_ipc_open, CUDA IPC): a rank hands sgpu_stack_block pointers to ITS rows
+    inside the root's memory (`pointers(r0)`, `plane`), so the stacking kernels store over NVLink while they compute and
+    no gather follows.  After the stack: ctx.synchronize() on every rank, then a barrier, then the root owns the image."""
+
+    def __init__(self, dist, ctx, layers, height, width, n_maps, out32=True, root=0):
+        import ctypes as C
+        import torch
+        from . import _lib
+        self.L, self.ctx, self.dist, self.root = _lib.lib(), ctx, dist, root
+        self.rank = dist.get_rank()
+        self.shape, self.n_maps, self.out32 = (layers, height, width), n_maps, out32
+        self.plane = height * width
+        npx = layers * height * width
+        al = lambda b: (b + 255) & ~255    # noqa: E731
+        self.out_bytes, self.map_bytes = al(npx * (4 if out32 else 2)), al(npx * 2)
+        self.base = C.c_void_p()
+        handle = torch.zeros(64, dtype=torch.uint8)
+        if self.rank == root:
+            ctx.check(self.L.sgpu_device_alloc(ctx.h, self.out_bytes + n_maps * self.map_bytes, C.byref(self.base)))
+            h = (C.c_ubyte * 64)()
+            ctx.check(self.L.sgpu_ipc_export(ctx.h, self.base, h))
+            handle = torch.tensor(list(h), dtype=torch.uint8)
+            ctx.synchronize()
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else None
+        t = handle.to(dev) if dev is not None else handle
+        dist.broadcast(t, src=root)
+        if self.rank != root:
+            h = (C.c_ubyte * 64)(*t.cpu().tolist())
+            ctx.check(self.L.sgpu_ipc_open(ctx.h, h, C.byref(self.base)))
+
+    def pointers(self, row0):
+        """device pointers to row `row0` of layer 0 of the image and of the maps (None where there is no map)"""
+        b = self.base.value
+        es = 4 if self.out32 else 2
+        w = self.shape[2]
+        maps = [b + self.out_bytes + k * self.map_bytes + row0 * w * 2 for k in range(self.n_maps)]
+        return [b + row0 * w * es] + maps + [None] * (2 - self.n_maps)
+
+    def tensors(self):
+        """on the root: torch views of the image and the maps (no copy)"""
+        import torch
+        assert self.rank == self.root
+
+        class _Arr:
+            def __init__(self, ptr, shape, typestr):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+        b = self.base.value
+        dev = torch.device("cuda", torch.cuda.current_device())
+        out = torch.as_tensor(_Arr(b, self.shape, "<f4" if self.out32 else "<u2"), device=dev)
+        maps = [torch.as_tensor(_Arr(b + self.out_bytes + k * self.map_bytes, self.shape, "<u2"), device=dev) for k in range(self.n_maps)]
+        return out, maps
+
+    def close(self):
+        if self.base:
+            if self.rank == self.root:
+                self.dist.barrier()     # the peers unmap first
+                self.L.sgpu_device_free(self.ctx.h, self.base)
+            else:
+                self.L.sgpu_ipc_close(self.ctx.h, self.base)
+                self.dist.barrier()
+            self.base = None

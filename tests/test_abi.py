@@ -19,7 +19,7 @@ def test_header_symbols_exported():
     L = _lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.sgpu_abi_version() == 4
+    assert L.sgpu_abi_version() == 5
 
 
 def test_no_cpu_fallback():

@@ -57,9 +57,34 @@ def _worker(rank, world, port, q, dtype_name, normalize, rejection, sig):
         lo = sh.gather_rows(dist, args.result.rejmap_low)
         hi = sh.gather_rows(dist, args.result.rejmap_high)
         irej = sh.reduce_irej(dist, torch.from_numpy(args.result.irej.astype(np.int64)).to(dev)).cpu().numpy()
+        # the same stack again, every rank's kernels storing its rows straight into rank 0's image over NVLink
+        # (sgpu_ipc_export / sgpu_ipc_open + out_plane_stride): no gather
+        import ctypes as Cc
+        from siril_b200 import _lib
+        L, ctx = _lib.lib(), args.ctx
+        peer = sh.PeerImage(dist, ctx, C, H, W, 2)
+        keep = []
+        args.coeff = sb.NormCoeff(offset=args.coeff.offset, mul=args.coeff.mul, scale=args.coeff.scale)
+        ca = sb.stacking._fill_cargs(args, N, C, True, keep)
+        ca.out_plane_stride = H * W
+        blk = Cc.c_void_p()
+        desc = _lib.BlockDesc(N, C, W, r1 - r0, 1 if dtype_name == "float32" else 0)
+        ctx.check(L.sgpu_block_wrap(ctx.h, Cc.byref(desc), Cc.c_void_p(mine.data_ptr()), Cc.byref(blk)))
+        pirej = torch.zeros(6, dtype=torch.int64, device=dev)
+        po, pl, ph = peer.pointers(r0)
+        ctx.check(L.sgpu_stack_block(ctx.h, blk, Cc.byref(ca), Cc.c_void_p(po), Cc.c_void_p(pl), Cc.c_void_p(ph), Cc.c_void_p(pirej.data_ptr())))
+        ctx.synchronize()
+        dist.barrier()
+        L.sgpu_block_destroy(blk)
+        peer_res = None
+        if rank == 0:
+            pout, (plo, phi) = peer.tensors()
+            peer_res = (to_np(pout.clone()), to_np(plo.clone()), to_np(phi.clone()))
+        dist.all_reduce(pirej)
+        peer.close()
         if rank == 0:
             q.put((rank, dict(off=off, mul=mul, sc=sc, bg=bg, coeff=(args.coeff.offset, args.coeff.mul, args.coeff.scale),
-                              out=to_np(out), lo=to_np(lo), hi=to_np(hi), irej=irej)))
+                              out=to_np(out), lo=to_np(lo), hi=to_np(hi), irej=irej, peer=peer_res, pirej=pirej.cpu().numpy())))
         else:
             q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
@@ -116,6 +141,10 @@ def test_row_sharded_normalization_and_stack(orc, dtype, normalize, rejection, s
     assert np.array_equal(got["lo"], to_np(one.rejmap_low)) and np.array_equal(got["hi"], to_np(one.rejmap_high))
     a, b = got["out"], to_np(one.data)
     assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30)) <= 1e-6
+    # rows stored straight into rank 0's image by every rank's kernels: the same image, bit for bit, as the gathered one
+    assert np.array_equal(got["peer"][0], got["out"], equal_nan=True)
+    assert np.array_equal(got["peer"][1], got["lo"]) and np.array_equal(got["peer"][2], got["hi"])
+    assert np.array_equal(got["pirej"], got["irej"].reshape(-1))
     ref = orc.stack(fr, rejection=rejection, sig=sig, normalize=normalize, offset=coeff[0], mul=coeff[1], scale=coeff[2],
                     create_rejmaps=True)
     assert np.array_equal(to_np(one.rejmap_low), ref["rej_low"]) and np.array_equal(one.irej, ref["irej"])
