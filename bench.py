@@ -265,9 +265,13 @@ def run_ours(args, wl):
         raise SystemExit("bench.py: no CUDA device; the stacking path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    json_fd = 1
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: one JSON line
+        # NCCL prints its version banner on stdout when the first communicator comes up: keep the descriptor for the ONE
+        # JSON line aside and point fd 1 at stderr for everything else
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     L = _lib.lib()
     stream = torch.cuda.current_stream(dev)
@@ -501,9 +505,12 @@ def run_ours(args, wl):
                                     if kernel_name == "stack_psel_kernel" else "")},
             "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if blk is not None:
         L.sgpu_block_destroy(blk)
+    if peer is not None:
+        torch.cuda.synchronize()
+        peer.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
