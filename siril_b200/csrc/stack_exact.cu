@@ -13,19 +13,12 @@
 
 namespace sgpu {
 
+// the pixel's rejection / combine on the stack already parked in the column `st`
 template <typename T>
-__device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, size_t pix, Col<T> st, Col<u16> aux, int rej[2]) {
+__device__ __forceinline__ void exact_pixel_body(const StackParams &p, int layer, size_t pix, Col<T> st, Col<u16> aux, int rej[2]) {
 	const size_t npix = (size_t) p.H * p.W;
 	const int x = (int) (pix % p.W);
 	const int N = p.N;
-	int f = 0;
-	for (; f + 4 <= N; f += 4) {	// 4 independent loads in flight per thread
-		const T v0 = load_norm<T>(p, f, layer, pix, x), v1 = load_norm<T>(p, f + 1, layer, pix, x);
-		const T v2 = load_norm<T>(p, f + 2, layer, pix, x), v3 = load_norm<T>(p, f + 3, layer, pix, x);
-		st.set(f, v0); st.set(f + 1, v1); st.set(f + 2, v2); st.set(f + 3, v3);
-	}
-	for (; f < N; f++) st.set(f, load_norm<T>(p, f, layer, pix, x));
-
 	double result;
 	if (p.is_mean) {
 		const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
@@ -40,6 +33,32 @@ __device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, siz
 		result = quickmedian_col(st, N);	// median_and_mean.c:1711-1715
 	}
 	store_result<T>(p, (size_t) layer * p.out_plane + pix, result, rej);
+}
+
+template <typename T>
+__device__ __forceinline__ void exact_pixel(const StackParams &p, int layer, size_t pix, Col<T> st, Col<u16> aux, int rej[2]) {
+	const int x = (int) (pix % p.W);
+	const int N = p.N;
+	int f = 0;
+	for (; f + 4 <= N; f += 4) {	// 4 independent loads in flight per thread
+		const T v0 = load_norm<T>(p, f, layer, pix, x), v1 = load_norm<T>(p, f + 1, layer, pix, x);
+		const T v2 = load_norm<T>(p, f + 2, layer, pix, x), v3 = load_norm<T>(p, f + 3, layer, pix, x);
+		st.set(f, v0); st.set(f + 1, v1); st.set(f + 2, v2); st.set(f + 3, v3);
+	}
+	for (; f < N; f++) st.set(f, load_norm<T>(p, f, layer, pix, x));
+	exact_pixel_body<T>(p, layer, pix, st, aux, rej);
+}
+
+// LIST mode: one hand-over pixel per WARP.  Its samples sit a whole plane apart, so nothing coalesces; what the warp
+// offers is 32 loads in flight instead of 4, and — the bigger part — lane 0 alone replays the pixel: 32 listed pixels on
+// the 32 lanes of one warp would each take their own path through the rejection and serialize.
+template <typename T>
+__device__ __forceinline__ void exact_pixel_warp(const StackParams &p, int layer, size_t pix, Col<T> st0, Col<u16> aux0, int lane, int rej[2]) {
+	const int x = (int) (pix % p.W);
+	for (int f = lane; f < p.N; f += 32) st0.set(f, load_norm<T>(p, f, layer, pix, x));
+	__syncwarp();
+	if (lane == 0) exact_pixel_body<T>(p, layer, pix, st0, aux0, rej);
+	__syncwarp();
 }
 
 template <typename T, bool SMEM, bool LIST>
@@ -71,13 +90,20 @@ __global__ void __launch_bounds__(256) stack_exact_kernel(const StackParams p) {
 		}
 	} else {
 		const unsigned count = *p.list_count;
-		const unsigned stride = gridDim.x * blockDim.x;
-		for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += stride) {
+		const int lane = threadIdx.x & 31;
+		const unsigned nwarps = gridDim.x * (blockDim.x >> 5);
+		Col<T> st0 = { st.p - lane, st.s }; Col<u16> aux0 = { aux.p - lane, aux.s };	// the column of the warp's lane 0
+		if (SMEM) {	// one column per WARP: a CTA of 8 warps holds 8 stacks, so thousands of warps are resident and every listed pixel has its own
+			const int nw = blockDim.x >> 5, wi = threadIdx.x >> 5;
+			st0.p = (T *) smem_raw + wi; st0.s = nw;
+			aux0.p = (u16 *) (smem_raw + (size_t) p.N * nw * sizeof(T)) + wi; aux0.s = nw;
+		}
+		for (unsigned e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); e < count; e += nwarps) {
 			const unsigned ent = p.list[e];
 			const int layer = (int) (ent >> 30);
 			int rej[2] = { 0, 0 };
-			exact_pixel<T>(p, layer, (size_t) (ent & 0x3fffffffu), st, aux, rej);
-			if (p.is_mean && (rej[0] | rej[1])) {
+			exact_pixel_warp<T>(p, layer, (size_t) (ent & 0x3fffffffu), st0, aux0, lane, rej);
+			if (lane == 0 && p.is_mean && (rej[0] | rej[1])) {
 				if (rej[0]) atomicAdd(&p.irej[layer * 2], (unsigned long long) rej[0]);
 				if (rej[1]) atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) rej[1]);
 			}
@@ -174,9 +200,14 @@ int sgpu_launch_exact_list(sgpu_ctx *ctx, sgpu_block *blk, StackParams p) {
 	const size_t per_thread = (size_t) d.nb_frames * blk->elem() + (p.use_aux ? (size_t) d.nb_frames * 2 : 0);
 	int bd; bool smem;
 	exact_shape(ctx, per_thread, &bd, &smem);
-	const size_t shm = smem ? per_thread * bd : 0;
-	// a fixed grid that walks the list: the count only exists on the device
+	size_t shm = smem ? per_thread * bd : 0;
+	// a fixed grid that walks the list, one listed pixel per warp: the count only exists on the device
 	dim3 grid((unsigned) (ctx->sm_count * 2), 1);
+	if (per_thread * 8 + 16 <= ctx->smem_optin) {	// shared-memory columns, one per warp
+		smem = true; bd = 256; shm = per_thread * 8 + 16;
+		const size_t per_sm = ctx->smem_optin / (shm + 1024);
+		grid.x = (unsigned) (ctx->sm_count * (per_sm > 8 ? 8 : (per_sm < 1 ? 1 : per_sm)));
+	}
 	if (!smem) {
 		int rv = sgpu_ensure_scratch(ctx, per_thread * (size_t) grid.x * bd);
 		if (rv) return rv;

@@ -105,7 +105,7 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 			if (chunk_px * rec_bytes > budget) chunk_px = budget / rec_bytes;
 		}
 		if (const char *ce = getenv("SGPU_PSEL_CHUNK")) { const size_t c = (size_t) atol(ce); if (c > 0 && c < chunk_px) chunk_px = c; }	// tests: force chunks
-		chunk_px = chunk_px / pxc * pxc;
+		if (chunk_px < npix) chunk_px = chunk_px / pxc * pxc;	// (a block that goes through whole keeps its ragged last tile: no second pair of launches for 16 pixels)
 		if (chunk_px < (size_t) pxc) p.split = 0;	// no room for records: the one-kernel form
 		else {
 			rv = sgpu_ensure_scratch(ctx, chunk_px * rec_bytes);
