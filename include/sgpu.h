@@ -135,6 +135,18 @@ void *sgpu_block_device_ptr(sgpu_block *blk);
 int sgpu_block_upload_frame(sgpu_block *blk, int frame, const void *host_frame, int frame_height,
 		int row0, int shifty);
 
+/* Maximized framing / sequences of variable-size frames.  With args->maximize_framing the result is
+ * the canvas that holds every registered frame (stack_open_all_files, median_and_mean.c:160-190): naxes0 x naxes1 and the
+ * origin args->offset from the frames' sizes and homography translations (regparam[].H.h02 / .h12). */
+int sgpu_maximized_framing(int nb_frames, const int *rx, const int *ry, const double *h02, const double *h12,
+		int upscale_at_stacking, long *naxes0, long *naxes1, int offset[2]);
+/* sgpu_block_upload_frame for a frame of its own size [nb_layers][frame_height][frame_width] into a block of the canvas'
+ * width: what seq_opened_read_region + rearrange_block_data leave in data->pix[frame] (:363-380, :394-480) — the frame's
+ * rows at the left of the block's rows, zero padded to the block's width, its TOP row on the canvas' top row before the y
+ * shift.  image_height is the canvas height (naxes1), row0 the canvas (memory) row of block row 0. */
+int sgpu_block_upload_frame_sized(sgpu_block *blk, int frame, const void *host_frame, int frame_width, int frame_height,
+		int image_height, int row0, int shifty);
+
 /* ---- feather masks and drizzle weights ---------------------------------------
  * Two optional float plane sets of a block, what data->mask[frame] and data->drizz[frame] are in the reference
  * (stack_read_block_data, median_and_mean.c:483-542): the feather mask of every frame, [nb_frames][height][width]

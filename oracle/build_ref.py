@@ -47,6 +47,8 @@ RANGES = {
     "mm_norm01":         ("src/stacking/median_and_mean.c", 557, 582, None),
     "mm_rejection_u16":  ("src/stacking/median_and_mean.c", 590, 1101, None),
     "mm_noise_weights":  ("src/stacking/median_and_mean.c", 1111, 1135, None),
+    "mm_maxframe_accum": ("src/stacking/median_and_mean.c", 161, 169, None),
+    "mm_maxframe_final": ("src/stacking/median_and_mean.c", 182, 189, None),
     "mm_other_weights":  ("src/stacking/median_and_mean.c", 1137, 1230, None),
     "mm_linfit_precalc": ("src/stacking/median_and_mean.c", 1491, 1499, None),
     "mm_mask_ramp":      ("src/stacking/median_and_mean.c", 513, 521, None),

@@ -425,6 +425,31 @@ int ref_reg_weights(int use_nbstars, int nb_layers, int N, const float *wfwhm, c
 	return rv;
 }
 
+/* ---- maximized framing: the reference's own lines of stack_open_all_files (median_and_mean.c:161-170 per frame,
+ * :182-189 after the loop) around in-RAM registration data ---- */
+#include <float.h>
+int ref_maximized_framing(int nb_frames, const int *rxs, const int *rys, const double *h02, const double *h12, int upscale,
+		long naxes_out[2], int offset_out[2]) {
+	struct stacking_args a_, *args = &a_; sequence seq_;
+	memset(&a_, 0, sizeof a_); memset(&seq_, 0, sizeof seq_);
+	regdata *rd = calloc(nb_frames, sizeof(regdata)); imgdata *im = calloc(nb_frames, sizeof(imgdata));
+	for (int i = 0; i < nb_frames; i++) { rd[i].H.h02 = h02[i]; rd[i].H.h12 = h12[i]; im[i].rx = rxs[i]; im[i].ry = rys[i]; }
+	regdata *layers[1] = { rd };
+	seq_.regparam = layers; seq_.is_variable = TRUE; seq_.imgparam = im; a_.seq = &seq_; a_.reglayer = 0; a_.maximize_framing = TRUE;
+	double xmin = DBL_MAX, xmax = -DBL_MAX, ymin = DBL_MAX, ymax = -DBL_MAX;
+	double scale = upscale ? 2. : 1.;
+	long naxes[3] = { 0, 0, 1 };
+	for (int image_index = 0; image_index < nb_frames; image_index++) {
+#include "gen/mm_maxframe_accum.inc"
+	}
+	gboolean update_wcs = TRUE; (void) update_wcs;
+#include "gen/mm_maxframe_final.inc"
+	}
+	naxes_out[0] = naxes[0]; naxes_out[1] = naxes[1]; offset_out[0] = a_.offset[0]; offset_out[1] = a_.offset[1];
+	free(rd); free(im);
+	return 0;
+}
+
 /* ---- the statistics records of a .seq file: the reference's own fprintf (seqfile.c:838-853) and sscanf (:584-600) ---- */
 typedef struct { imstats ***stats; int cfa_opened_monochrome; } ref_seq_view;
 int ref_seq_stats_write(int layer, int i, const double v[14], char *out, size_t cap) {

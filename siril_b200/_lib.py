@@ -91,6 +91,8 @@ SIGNATURES = {
     "sgpu_block_destroy": (None, [P]),
     "sgpu_block_device_ptr": (P, [P]),
     "sgpu_block_upload_frame": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int]),
+    "sgpu_maximized_framing": (C.c_int, [C.c_int, P, P, P, P, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_long), C.POINTER(C.c_int)]),
+    "sgpu_block_upload_frame_sized": (C.c_int, [P, C.c_int, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "sgpu_block_upload_weight_plane": (C.c_int, [P, C.c_int, C.c_int, P, C.c_int, C.c_int, C.c_int]),
     "sgpu_block_set_weight_planes": (C.c_int, [P, P, P]),
     "sgpu_block_mask_ramp": (C.c_int, [P, C.c_int]),

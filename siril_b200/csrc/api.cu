@@ -246,6 +246,53 @@ int sgpu_block_upload_frame(sgpu_block *b, int frame, const void *host, int fram
 	return SGPU_OK;
 }
 
+/* maximized framing (median_and_mean.c:160-190): the canvas that holds every registered frame, and the origin
+ * args->offset; h02 / h12 are the frames' homography translations, rx / ry their sizes */
+int sgpu_maximized_framing(int nb_frames, const int *rx, const int *ry, const double *h02, const double *h12, int upscale_at_stacking,
+		long *naxes0, long *naxes1, int offset[2]) {
+	if (!rx || !ry || !h02 || !h12 || !naxes0 || !naxes1 || !offset || nb_frames < 1) return SGPU_GENERIC_ERROR;
+	const double scale = upscale_at_stacking ? 2. : 1.;
+	double xmin = DBL_MAX, xmax = -DBL_MAX, ymin = DBL_MAX, ymax = -DBL_MAX;
+	for (int i = 0; i < nb_frames; i++) {
+		xmin = (xmin > h02[i] * scale) ? h02[i] * scale : xmin;
+		ymin = (ymin > h12[i] * scale) ? h12[i] * scale : ymin;
+		xmax = (xmax < h02[i] * scale + rx[i]) ? h02[i] * scale + rx[i] : xmax;
+		ymax = (ymax < h12[i] * scale + ry[i]) ? h12[i] * scale + ry[i] : ymax;
+	}
+	*naxes0 = (int) xmax - (int) xmin + 1;
+	*naxes1 = (int) ymax - (int) ymin + 1;
+	offset[0] = (int) xmin;
+	offset[1] = -(int) ymin;
+	return SGPU_OK;
+}
+
+/* a frame of its own size into a block of the canvas' width (maximize_framing, variable-size sequences): what
+ * seq_opened_read_region + rearrange_block_data (median_and_mean.c:363-380, :394-480) leave in data->pix[frame] — the
+ * frame's rows at the LEFT of the block's rows, zero padded, the frame's TOP row on the canvas' top row before the y shift */
+int sgpu_block_upload_frame_sized(sgpu_block *b, int frame, const void *host, int frame_width, int frame_height,
+		int image_height, int row0, int shifty) {
+	if (!b || !host) return SGPU_GENERIC_ERROR;
+	sgpu_ctx *ctx = b->ctx;
+	const sgpu_block_desc &d = b->d;
+	if (frame < 0 || frame >= d.nb_frames) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d out of range", frame);
+	if (frame_width < 1 || frame_width > d.width || frame_height < 1) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame of %d x %d does not fit a block %d wide", frame_width, frame_height, d.width);
+	const size_t es = b->elem(), rowb = (size_t) d.width * es, frowb = (size_t) frame_width * es;
+	// memory rows are bottom-up: canvas row r holds top-down row image_height - 1 - r, which the reference reads from the
+	// frame's top-down row (image_height - 1 - r) + shifty, i.e. frame memory row r - shifty - (image_height - frame_height)
+	const long sh = (long) shifty + ((long) image_height - frame_height);
+	long lo = sh - row0; if (lo < 0) lo = 0;
+	long hi = (long) frame_height + sh - row0; if (hi > d.height) hi = d.height;
+	for (int l = 0; l < d.nb_layers; l++) {
+		char *dst = (char *) b->dev + (((size_t) frame * d.nb_layers + l) * b->plane()) * es;
+		const char *src = (const char *) host + (size_t) l * frame_height * frowb;
+		SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) d.height * rowb, ctx->stream));
+		if (hi <= lo) continue;
+		SGPU_CUDA(ctx, cudaMemcpy2DAsync(dst + (size_t) lo * rowb, rowb, src + (size_t) (row0 + lo - sh) * frowb, frowb,
+				frowb, (size_t) (hi - lo), cudaMemcpyDefault, ctx->stream));
+	}
+	return SGPU_OK;
+}
+
 /* ---- feather masks / drizzle weights: two more float plane sets of the block (median_and_mean.c:483-542) ---- */
 static size_t weight_plane_floats(const sgpu_block *b, int which) {
 	return (size_t) b->d.nb_frames * (which == SGPU_PLANE_DRIZZLE ? b->d.nb_layers : 1) * b->plane();
