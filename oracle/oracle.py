@@ -206,7 +206,9 @@ class Oracle:
         p.shiftx, p.shifty = arr(shiftx, np.int32), arr(shifty, np.int32)
         p.output_norm, p.use_32bit_output = int(output_norm), int(use_32bit_output)
         p.create_rejmaps, p.merge_rejmaps = int(create_rejmaps), int(merge_rejmaps)
-        p.nthreads = nthreads or os.cpu_count() or 1
+        # (the reference's planner is made for images far taller than the thread count: with more threads than
+        # rows it plans blocks past the image; the result does not depend on the thread count, so cap it)
+        p.nthreads = max(1, min(nthreads or os.cpu_count() or 1, H))
         p.max_rows = max_rows
         p.source_bitpix = source_bitpix
         # feather masks [N][H][W] (distances, before the ramp) / drizzle weights [N][C][H][W] (median_and_mean.c:483-542)

@@ -414,11 +414,14 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	if (a->engine == 2 && !sgpu_sorted_supports(blk->d, a)) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the sorted engine does not cover this configuration");
 	ctx->list_used = false;
 	sgpu_stack_args forced;
-	if (a->is_mean && (blk->mask || blk->drizz)) {
-		// feather masks / drizzle weights: per-sample weights in the combine and, for drizzle, in what counts as a null
-		// sample.  Served by the exact engine (the others have no plane loads); asking for another one is an error.
-		if (a->engine != 0 && a->engine != 1) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "mask / drizzle weight planes are served by the exact engine only");
+	const bool masked = a->is_mean && blk->mask;	// feather masks: per-sample weights in the combine — every engine but the selection engine carries them
+	if (a->is_mean && blk->drizz) {
+		// drizzle weights also decide what counts as a null sample before the rejection: served by the exact engine
+		// (the others have no plane loads at that point); asking for another one is an error
+		if (a->engine != 0 && a->engine != 1) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "drizzle weight planes are served by the exact engine only");
 		forced = *a; forced.engine = 1; a = &forced;
+	} else if (masked && a->engine == 6) {
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the selection engine does not carry mask planes");
 	} else
 	if (a->engine == 0) if (const char *e = getenv("SGPU_ENGINE")) {	// tuning aid: force an engine from the environment
 		forced = *a; forced.engine = atoi(e);
@@ -430,7 +433,7 @@ int sgpu_stack_block(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a,
 	static const int psel_min = getenv("SGPU_PSEL_MIN") ? atoi(getenv("SGPU_PSEL_MIN")) : 64;
 	// (winsorized was tried in the selection engine: with a quarter of the stack beyond the clamp there is little to select —
 	// C2 took 22.5 ms against the lane-sort engine's 16.4 — and it is not served there)
-	if (((a->engine == 0 && blk->d.nb_frames >= psel_min) || a->engine == 6) && sgpu_psel_supports(blk->d, a))
+	if (((a->engine == 0 && blk->d.nb_frames >= psel_min && !masked) || a->engine == 6) && sgpu_psel_supports(blk->d, a))
 		return ctx->last_engine = 6, sgpu_launch_psel(ctx, blk, a, dp, d_out, d_rej_low, d_rej_high, d_irej);
 	if (a->engine == 6) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "the selection engine does not cover this configuration");
 	// the lane-sort engine wherever it applies (up to 1024 frames), else the sorted engine, else the

@@ -435,13 +435,13 @@ SGPU_HD void fast_reject(Acc &s, int n, int nb, const RejCfg &c, const Sums *S0,
 }
 
 // the combine of a decided stack (o.status == FAST_DONE, n > 0)
-template <typename OrigFn>
-SGPU_HD double fast_combine(const FastRes &o, int nb, const double *w, OrigFn orig) {
-	if (w) {
+template <typename OrigFn, typename W>
+SGPU_HD double fast_combine(const FastRes &o, int nb, const W &w, OrigFn orig) {
+	if (w) {	// frame weights (a plain pointer) or PixWeights with the pixel's feather-mask samples (exact.cuh)
 		double sum = 0.0, norm = 0.0;
 		for (int f = 0; f < nb; f++) {
 			const float v = orig(f);
-			if (v >= o.pmin && v <= o.pmax && v != 0.f) { sum += (double) v * w[f]; norm += w[f]; }
+			if (v >= o.pmin && v <= o.pmax && v != 0.f) { const double n = w[f]; sum += (double) v * n; norm += n; }
 		}
 		if (norm == 0. || sum == 0.) {
 			sum = 0.;
@@ -453,8 +453,8 @@ SGPU_HD double fast_combine(const FastRes &o, int nb, const double *w, OrigFn or
 	return div_by_int(o.sum, o.kept);	// the correctly rounded quotient, without the division routine
 }
 
-template <bool U16, class Acc, typename OrigFn>
-SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const double *w, OrigFn orig,
+template <bool U16, class Acc, typename OrigFn, typename W>
+SGPU_HD double fast_mean_and_reject(Acc &s, int n, int nb, const RejCfg &c, const W &w, OrigFn orig,
 		const Sums *S0, int rej[2], int *status) {
 	*status = FAST_DONE;
 	if (n == 0) return 0.0;

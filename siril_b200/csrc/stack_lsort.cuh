@@ -241,7 +241,9 @@ __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) /
 		if (status == FAST_DONE) {
 			if (p.is_mean) {
 				const int x = (int) (pix % p.W);
-				const double *w = p.weights ? p.weights + (size_t) layer * N : nullptr;
+				const double *fw = p.weights ? p.weights + (size_t) layer * N : nullptr;
+				// frame weights, and the pixel's feather-mask samples where the block carries masks (median_and_mean.c:1060-1066)
+				const PixWeights w = { fw, p.mask ? p.mask + pix : nullptr, nullptr, npix, 0, p.shiftx };
 				const Sums *S0 = (p.need_sums && n > 0) ? &sums[threadIdx.x] : nullptr;
 				if (p.is_u16) {
 					auto orig = [&](int ff) { return (float) load_norm<u16>(p, ff, layer, pix, x); };
