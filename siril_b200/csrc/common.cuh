@@ -51,6 +51,7 @@ int sgpu_cuda_fail(sgpu_ctx *ctx, cudaError_t e, const char *what);
 int sgpu_ensure_scratch(sgpu_ctx *ctx, size_t bytes);
 int sgpu_ensure_list(sgpu_ctx *ctx, size_t bytes);
 void sgpu_free_stage(sgpu_ctx *ctx);
+const double *sgpu_rcp_table(sgpu_ctx *ctx);	// device table of correctly rounded 1.0 / i, i < SGPU_RCP_N (stack_psel.cu); null on failure
 int sgpu_launch_mask_ramp(sgpu_ctx *ctx, float *d_mask, size_t n, int feather_dist);
 
 #define SGPU_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return sgpu_cuda_fail((ctx), e__, #call); } while (0)

@@ -32,7 +32,9 @@ struct Col {
 struct RejCfg {
 	int type; float s0, s1; const float *crit; int nb_frames; float m_x, m_dx2;
 	const float *xf;	// optional table 1.f / (i + 1) (median_and_mean.c:1493) for the linear-fit running means; nullptr: computed in place
+	const double *rcp;	// optional table of correctly rounded 1.0 / i, i < SGPU_RCP_N (device memory); nullptr: computed in place
 };
+#define SGPU_RCP_N 1282
 
 // ---- rounding helpers (src/core/proto.h:208-237, 324-346) ----
 SGPU_HD __forceinline__ u16 round_to_word(double x) {

@@ -80,6 +80,16 @@ SGPU_HD __forceinline__ double div_by_int(double a, int n) {
 	return fma(r, y, q);
 }
 
+// 1 / n from the table of correctly rounded reciprocals when there is one (a load instead of MUFU.RCP64H and its
+// Newton steps), else rcp_d: the same value either way
+SGPU_HD __forceinline__ double rcp_t(const double *tab, int n) {
+#ifdef __CUDA_ARCH__
+	if (tab && n < SGPU_RCP_N) return __ldg(tab + n);
+#endif
+	(void) tab;
+	return rcp_d(n);
+}
+
 struct Sums {
 	double K, S1, S2;
 	SGPU_HD __forceinline__ void init(float k) { K = (double) k; S1 = 0.0; S2 = 0.0; }
@@ -381,23 +391,39 @@ SGPU_HD void fast_gesdt(const Acc &s, int n, int nb, const RejCfg &c, const Sums
 		// exact in double (samples of one sign within 2^16 of each other, or integers) S.sum() IS
 		// the reference's sum, so the float mean is bit-identical, ties included; otherwise the
 		// reference's own summation order matters whenever the quotient sits on a rounding boundary
-		const double avg_d = div_by_int(S.sum(size), size);
+		const double r0 = rcp_t(c.rcp, size), r1 = rcp_t(c.rcp, size - 1), b = (double) size;
+		const double a = S.sum(size);
+		double avg_d = a * r0;		// div_by_int(a, size) with the reciprocal from the table
+		avg_d = fma(fma(-avg_d, b, a), r0, avg_d);
 		const float avg = (float) avg_d;
 		if (!exact_sums) {
 			const double tiny = fabs(avg_d) * 1e-12;
 			if ((float) (avg_d + tiny) != avg || (float) (avg_d - tiny) != avg) { FAST_WHY(72); return; }
 		}
-		float slo, shi;
-		if (!sd_interval(S.var(size), avg_d, size, SGPU_DELTA_SD, 1.f, &slo, &shi)) { FAST_WHY(73); return; }
 		const float xl = s(lo), xh = s(lo + size - 1);
 		float dev = avg - xl;
 		const float md2 = xh - avg;
 		const bool low_end = !(md2 > dev);
 		if (!low_end) dev = md2;
 		if (it > 1) {
-			const float cr = c.crit[it + removed];
-			if (dev / shi > cr) last = -2;	// certainly an outlier: snapshot below
-			else if (dev / slo > cr) amb = it;
+			// G = dev / sd against the critical value, decided for both ends of the interval [slo, shi] that holds the
+			// reference's float sd (sd_interval).  First in squares, in double, with room for every rounding between here
+			// and the float quotient (the sd's two float roundings and its (1 +- delta) factors, the division's one): only
+			// what falls between the two bounds takes the float path below
+			const double var = (S.S2 - S.S1 * S.S1 * r0) * r1;
+			if (!(var >= 0.0)) { FAST_WHY(73); return; }
+			const double e = fabs(avg_d) * 5.9604645e-08;
+			const double var_hi = var + e * e * 2.0;	// sd_interval's term, n / (n - 1) <= 2
+			const double cr = (double) c.crit[it + removed], d2 = (double) dev * (double) dev, c2 = cr * cr;
+			const bool normal = var > 1e-30 && var_hi < 1e30;	// the float sd is a normal number: its roundings are relative
+			if (normal && d2 > c2 * var_hi * (1.0 + 4.0e-6)) last = -2;	// certainly an outlier: snapshot below
+			else if (!normal || !(d2 < c2 * var * (1.0 - 4.0e-6))) {	// too close to call in squares (or a degenerate sd): the float path
+				float slo, shi;
+				if (!sd_interval(var, avg_d, size, SGPU_DELTA_SD, 1.f, &slo, &shi)) { FAST_WHY(73); return; }
+				const float crf = c.crit[it + removed];
+				if (dev / shi > crf) last = -2;
+				else if (dev / slo > crf) amb = it;
+			}
 		}
 		float xrem, xflag;
 		if (low_end) { xrem = xl; xflag = xl; lo++; if (first_low < 0) first_low = it; }

@@ -127,6 +127,7 @@ void sgpu_fill_stack_params(StackParams &p, sgpu_block *blk, const sgpu_stack_ar
 	p.rc.type = a->is_mean ? a->type_of_rejection : SGPU_NO_REJEC;
 	p.rc.s0 = a->sig[0]; p.rc.s1 = a->sig[1]; p.rc.crit = dp.crit; p.rc.nb_frames = d.nb_frames;
 	p.rc.m_x = 0.f; p.rc.m_dx2 = 0.f; p.rc.xf = nullptr;
+	p.rc.rcp = p.rc.type == SGPU_GESDT ? sgpu_rcp_table(blk->ctx) : nullptr;	// the sorted engines' Grubbs loop reads 1 / n from it
 	if (p.rc.type == SGPU_LINEARFIT) {	// median_and_mean.c:1491-1499 (host, float)
 		volatile float mx = (d.nb_frames - 1) * 0.5f, acc = 0.f;
 		for (int j = 0; j < d.nb_frames; ++j) {

@@ -25,9 +25,9 @@ static const PselVariant *pick(int N) {
 }
 
 // correctly rounded reciprocals 1 / i for the B2 arithmetic (psel_rcp), filled once per device
-#define PSEL_RCP_N 1282
+#define PSEL_RCP_N SGPU_RCP_N
 static __device__ double g_psel_rcp[PSEL_RCP_N];
-static const double *psel_rcp_table(sgpu_ctx *ctx) {
+const double *sgpu_rcp_table(sgpu_ctx *ctx) {
 	static std::mutex mu;
 	static const double *addr[64];
 	if (ctx->device < 0 || ctx->device >= 64) return nullptr;
@@ -69,7 +69,7 @@ int sgpu_launch_psel(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, c
 	ctx->list_used = true;
 	p.is_u16 = d.dtype == SGPU_U16;
 	{ const char *e = getenv("SGPU_PSEL_STOP"); p.dbg_stop = e ? atoi(e) : 0; }
-	p.rcp_tab = psel_rcp_table(ctx);	// null: the kernel computes the reciprocals
+	p.rcp_tab = sgpu_rcp_table(ctx);	// null: the kernel computes the reciprocals
 	// TMA tile load: f32 samples, no per-frame x shift, plane stride a multiple of 16 bytes
 	CUtensorMap tmap;
 	p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; p.use_tma = 0;
