@@ -481,7 +481,7 @@ def run_ours(args, wl):
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp)).get(args.workload)
-            if tj and tj.get("kernel") == kernel_name:
+            if tj and str(tj.get("kernel", "")).split(" + ")[0] == kernel_name:     # ("stack_psel_kernel + stack_psel_finish_kernel": the pair)
                 traffic = tj["dram_bytes_per_px_frame"] * n * c * h * w
         cb = None
         if not args.no_cpu:
