@@ -4,9 +4,9 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload target] [--impl reference]
 
 One "step" = one pass of the stacking call (normalization apply + rejection + combine + output and
-rejection-map writes; for N > 1 also the NCCL gather of the output rows and both rejection maps to
-rank 0 and the all-reduce of the rejection counters) over one synthetic frame block resident in
-HBM.  Workloads are BASELINE.json's configs plus the north-star target (sigma clip of 300 x 61 MP
+rejection-map writes; for N > 1 every rank's kernels store their rows straight into the image on
+rank 0 over NVLink — or, --gather nccl, the rows are sent there after the stack — and the rejection
+counters are all-reduced) over one synthetic frame block resident in HBM.  Workloads are BASELINE.json's configs plus the north-star target (sigma clip of 300 x 61 MP
 float frames), which is the default.  For N > 1 ONE image is row-sharded over the ranks (strong
 scaling): rank g holds rows [H*g/N, H*(g+1)/N) of every frame.
 
@@ -326,10 +326,14 @@ def run_ours(args, wl):
     if world > 1 and args.gather == "peer":
         # the whole image lives on rank 0 and every rank's kernels store their rows straight into it over NVLink
         # (CUDA IPC mapping, sharding.PeerImage): no gather step; what remains per step is the counters' all-reduce
-        peer = sharding.PeerImage(dist, ctx, c, H, w, 2 if maps else 0)
-        cargs.out_plane_stride = H * w
-        p_out, p_lo, p_hi = peer.pointers(r0)
-    elif world > 1 and rank == 0:     # the whole image on rank 0: [C][H][W] result and both maps
+        try:
+            peer = sharding.PeerImage(dist, ctx, c, H, w, 2 if maps else 0)
+            cargs.out_plane_stride = H * w
+            p_out, p_lo, p_hi = peer.pointers(r0)
+        except RuntimeError as e:       # (raised on every rank alike) no peer mapping on this box: gather with NCCL instead
+            print(f"bench.py: {e}; falling back to --gather nccl", file=sys.stderr)
+            args.gather = "nccl"
+    if world > 1 and peer is None and rank == 0:     # the whole image on rank 0: [C][H][W] result and both maps
         full = [torch.empty((c, H, w), dtype=torch.float32, device=dev)] + \
                ([torch.empty((c, H, w), dtype=torch.uint16, device=dev) for _ in range(2)] if maps else [])
     bounds = [sharding.row_shard(H, g, world) for g in range(world)]

@@ -123,18 +123,41 @@ class PeerImage:
         self.out_bytes, self.map_bytes = al(npx * (4 if out32 else 2)), al(npx * 2)
         self.base = C.c_void_p()
         handle = torch.zeros(64, dtype=torch.uint8)
-        if self.rank == root:
-            ctx.check(self.L.sgpu_device_alloc(ctx.h, self.out_bytes + n_maps * self.map_bytes, C.byref(self.base)))
-            h = (C.c_ubyte * 64)()
-            ctx.check(self.L.sgpu_ipc_export(ctx.h, self.base, h))
-            handle = torch.tensor(list(h), dtype=torch.uint8)
-            ctx.synchronize()
+        ok, why = 1, ""
+        import os
+        if os.environ.get("SGPU_NO_PEER") == str(self.rank):     # tests: make the mapping fail on one rank
+            ok, why = 0, "SGPU_NO_PEER"
+        if self.rank == root and ok:
+            try:
+                ctx.check(self.L.sgpu_device_alloc(ctx.h, self.out_bytes + n_maps * self.map_bytes, C.byref(self.base)))
+                h = (C.c_ubyte * 64)()
+                ctx.check(self.L.sgpu_ipc_export(ctx.h, self.base, h))
+                handle = torch.tensor(list(h), dtype=torch.uint8)
+                ctx.synchronize()
+            except _lib.SgpuError as e:
+                ok, why = 0, str(e)
         dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else None
         t = handle.to(dev) if dev is not None else handle
         dist.broadcast(t, src=root)
-        if self.rank != root:
-            h = (C.c_ubyte * 64)(*t.cpu().tolist())
-            ctx.check(self.L.sgpu_ipc_open(ctx.h, h, C.byref(self.base)))
+        if self.rank != root and ok:
+            try:
+                h = (C.c_ubyte * 64)(*t.cpu().tolist())
+                ctx.check(self.L.sgpu_ipc_open(ctx.h, h, C.byref(self.base)))
+            except _lib.SgpuError as e:
+                ok, why = 0, str(e)
+        # every rank learns whether every rank has the image: a mapping that fails on one GPU (no peer access, a
+        # container without shared IPC) must not leave the others waiting
+        flag = torch.tensor([ok], dtype=torch.int32)
+        flag = flag.to(dev) if dev is not None else flag
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.cpu()[0]) == 0:
+            if self.base:
+                if self.rank == root:
+                    self.L.sgpu_device_free(ctx.h, self.base)
+                elif ok:
+                    self.L.sgpu_ipc_close(ctx.h, self.base)
+            self.base = None
+            raise RuntimeError("the root's image cannot be mapped on every rank" + (": " + why if why else ""))
 
     def pointers(self, row0):
         """device pointers to row `row0` of layer 0 of the image and of the maps (None where there is no map)"""
