@@ -217,6 +217,102 @@ SGPU_HD void fast_sigma(const Acc &s, int n, const RejCfg &c, const Sums *S0, in
 	finish_range(s, a, b, S, o);
 }
 
+// ---- MAD (rejection_float.c:174-209 with siril_stats_float_mad, statistics_float.c:79-101 -> findMinMaxPercentile,
+// rt_algo.cc:38-171; median_and_mean.c:777-813 with siril_stats_ushort_mad, statistics.c:133-154) --------------------
+// On the sorted stack the absolute deviations from the median come out in ascending order from a two-pointer walk
+// outwards from where the median sits, so neither the reference's scratch copy nor its histogram is needed: the
+// histogram median of the float version depends only on how many deviations fall into each of its n bins, and the
+// bin of a deviation grows with it — the walk meets the bins in order.  The result is the reference's value exactly
+// (same float operations per sample, integer counts), not an interval.
+// first rank in [a, a + n) whose sample is >= x
+template <class Acc>
+SGPU_HD __forceinline__ int lower_rank(const Acc &s, int a, int n, float x) {
+	int lo = a, hi = a + n;
+	while (lo < hi) { const int mid = (lo + hi) >> 1; if (s(mid) < x) lo = mid + 1; else hi = mid; }
+	return lo;
+}
+
+template <class Acc>
+SGPU_HD float mad_sorted_f32(const Acc &s, int a, int n, double m) {
+	const float med = (float) m;
+	const int p = lower_rank(s, a, n, med);
+	int i = p - 1, j = p;
+	const int e = a + n;
+	float vi = i >= a ? fabsf(s(i) - med) : __builtin_huge_valf(), vj = j < e ? fabsf(s(j) - med) : __builtin_huge_valf();
+	const float mn = vi < vj ? vi : vj;
+	const float dl = fabsf(s(a) - med), dh = fabsf(s(e - 1) - med);
+	const float mx = dl < dh ? dh : dl;
+	if (fabsf(mx - mn) == 0.f) return mn;
+	const unsigned hs = n < 65536 ? (unsigned) n : 65536u;
+	const float scale = (hs - 1) / (mx - mn);
+	const float thresh = 0.5f * n;
+	unsigned cum = 0, cur = 0, bin = 0;	// samples in the bins below `bin`, and in it
+	for (int k = 0; k < n; k++) {
+		const bool low = vi <= vj;
+		const float v = low ? vi : vj;
+		const unsigned bk = (unsigned) (u16) (scale * (v - mn));
+		if (bk != bin) {
+			if (!((float) (cum + cur) < thresh)) break;	// `while (count < thresh) count += histo[k++]` stopped on the bin before
+			cum += cur; cur = 0; bin = bk;
+		}
+		cur++;
+		if (low) { i--; vi = i >= a ? fabsf(s(i) - med) : __builtin_huge_valf(); }
+		else { j++; vj = j < e ? fabsf(s(j) - med) : __builtin_huge_valf(); }
+	}
+	const unsigned count = cum + cur, kbin = bin + 1;
+	const float c0 = (float) count - thresh, c1 = thresh - (float) cum;
+	float v = (c1 * (float) kbin + c0 * (float) (kbin - 1)) / (c0 + c1);
+	v /= scale; v += mn;
+	{ const float t = v < mx ? v : mx; v = mn < t ? t : mn; }
+	return v;
+}
+
+// WORD samples: the exact median of |x - round(m)| (histogram_median, sorting.c:577-642)
+template <class Acc>
+SGPU_HD float mad_sorted_u16(const Acc &s, int a, int n, double m) {
+	const int med = round_to_int_d(m);
+	const int p = lower_rank(s, a, n, (float) med);
+	int i = p - 1, j = p;
+	const int e = a + n, k = n / 2;
+	int prev = 0, cur = 0;
+	for (int q = 0; q <= k; q++) {	// order statistics k - 1 and k of the deviations
+		const int vi = i >= a ? med - (int) s(i) : 0x7fffffff, vj = j < e ? (int) s(j) - med : 0x7fffffff;
+		prev = cur;
+		if (vi <= vj) { cur = vi; i--; } else { cur = vj; j++; }
+	}
+	const double r = (n % 2 == 0) ? (prev + cur) / 2.0 : (double) cur;
+	return (float) r;
+}
+
+template <bool U16, class Acc>
+SGPU_HD void fast_mad(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	double median = median_sorted<U16>(s, 0, n);
+	if (U16) median = (double) (float) median;	// the WORD path keeps the median as a float (median_and_mean.c:705)
+	if (median == 0.0) return;
+	Sums S = sums_of(s, n, S0);
+	int a = 0, b = n, r = 0;
+	bool first = true;
+	for (;;) {
+		const int nn = b - a;
+		if (nn - r <= 4) break;		// the guard refuses every rejection of this pass
+		// the MAD is taken about the median of the PASS BEFORE; the median is renewed after it (:183-186)
+		const float var = U16 ? mad_sorted_u16(s, a, nn, median) : mad_sorted_f32(s, a, nn, median);
+		if (!first) { median = median_sorted<U16>(s, a, nn); if (U16) median = (double) (float) median; }
+		first = false;
+		int a2, b2;
+		if (clip_range(s, a, b, (float) median, var, var, c.s0, c.s1, &a2, &b2)) return;
+		const int K = (a2 - a) + (b - b2);
+		if (K == 0) break;
+		if (nn - r - K < 4) return;	// the guard would cut this pass short: order dependent
+		for (int i = a; i < a2; i++) S.sub(s(i));
+		for (int i = b2; i < b; i++) S.sub(s(i));
+		rej[0] += a2 - a; rej[1] += b - b2; r += K; a = a2; b = b2;
+		if (b - a <= 3) break;
+	}
+	finish_range(s, a, b, S, o);
+}
+
 // ---- WINSORIZED, float samples (rejection_float.c:223-259) --------------------------------------
 template <class Acc>
 SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
@@ -455,7 +551,8 @@ SGPU_HD void fast_reject(Acc &s, int n, int nb, const RejCfg &c, const Sums *S0,
 	case SGPU_WINSORIZED: if (U16) o.status = FAST_FALLBACK; else fast_winsorized(s, n, c, S0, rej, o); break;
 	case SGPU_LINEARFIT: fast_linearfit(s, n, c, rej, o); break;
 	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, S0, rej, o); break;
-	default: o.status = FAST_FALLBACK; break;	// MAD, SIGMEDIAN: exact engine
+	case SGPU_MAD: fast_mad<U16>(s, n, c, S0, rej, o); break;
+	default: o.status = FAST_FALLBACK; break;	// SIGMEDIAN: exact engine
 	}
 	if (o.status != FAST_DONE || o.kept == 0) o.status = FAST_FALLBACK;
 }
