@@ -313,6 +313,60 @@ SGPU_HD void fast_mad(const Acc &s, int n, const RejCfg &c, const Sums *S0, int 
 	finish_range(s, a, b, S, o);
 }
 
+// ---- SIGMEDIAN (rejection_float.c:210-222 / median_and_mean.c:814-830) -----------------------------
+// Every sample beyond median -+ k sigma is REPLACED by the median and the pass is repeated until none is; nothing is
+// removed.  On the sorted stack the replaced samples are the two ends of the originals' range [a, b); the copies
+// that took their place are kept as a short list of (value, count) groups — each value a median, so inside the
+// range — and sums, medians and extremes are those of originals + groups.
+template <bool U16, class Acc>
+SGPU_HD void fast_sigmedian(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	constexpr int MAXG = 6;
+	float gv[MAXG]; int gc[MAXG], gpos[MAXG];	// ascending by value; gpos: originals (of all n) below the value
+	int ng = 0;
+	if (U16 && (float) median_sorted<true>(s, 0, n) == 0.f) return;	// median_and_mean.c:747-759: the exact engine's case
+	Sums S = sums_of(s, n, S0);
+	int a = 0, b = n;
+	auto rank = [&](int k) -> float {	// k-th smallest of originals [a, b) + groups
+		int used = 0;
+		for (int g = 0; g < ng; g++) {
+			int below = gpos[g] - a; below = below < 0 ? 0 : (below > b - a ? b - a : below);
+			const int base = below + used;
+			if (k < base) return s(a + k - used);
+			if (k < base + gc[g]) return gv[g];
+			used += gc[g];
+		}
+		return s(a + k - used);
+	};
+	for (;;) {
+		float slo, shi;
+		if (!sd_interval(S.var(n), S.mean(n), n, SGPU_DELTA_SD, 1.f, &slo, &shi)) return;
+		const int k = n >> 1;
+		double med;
+		if (n & 1) med = (double) rank(k);
+		else { const float x = rank(k - 1), y = rank(k); med = (!U16 && n < 9) ? (x + y) / 2.0 : ((double) x + (double) y) / 2.0; }
+		const float medf = (float) med;
+		int a2, b2;
+		if (clip_range(s, a, b, medf, slo, shi, c.s0, c.s1, &a2, &b2)) return;
+		for (int g = 0; g < ng; g++)	// a copy that a later, narrower pass would replace again: the exact engine's case
+			if (medf - gv[g] > slo * c.s0 || gv[g] - medf > slo * c.s1) return;
+		const int K = (a2 - a) + (b - b2);
+		if (K == 0) break;
+		if (ng == MAXG) return;
+		const float rv = U16 ? (float) (u16) medf : medf;	// `stack[f] = (T) median`
+		for (int i = a; i < a2; i++) S.sub(s(i));
+		for (int i = b2; i < b; i++) S.sub(s(i));
+		{ const double y = (double) rv - S.K; S.S1 += (double) K * y; S.S2 += (double) K * y * y; }
+		rej[0] += a2 - a; rej[1] += b - b2; a = a2; b = b2;
+		int g = ng;
+		while (g > 0 && gv[g - 1] > rv) { gv[g] = gv[g - 1]; gc[g] = gc[g - 1]; gpos[g] = gpos[g - 1]; g--; }
+		gv[g] = rv; gc[g] = K; gpos[g] = lower_rank(s, 0, n, rv); ng++;
+	}
+	o.status = FAST_DONE; o.kept = n; o.sum = S.sum(n);
+	o.pmin = s(a); o.pmax = s(b - 1);
+	if (ng) { o.pmin = gv[0] < o.pmin ? gv[0] : o.pmin; o.pmax = gv[ng - 1] > o.pmax ? gv[ng - 1] : o.pmax; }
+}
+
 // ---- WINSORIZED, float samples (rejection_float.c:223-259) --------------------------------------
 template <class Acc>
 SGPU_HD void fast_winsorized(const Acc &s, int n, const RejCfg &c, const Sums *S0, int rej[2], FastRes &o) {
@@ -552,7 +606,8 @@ SGPU_HD void fast_reject(Acc &s, int n, int nb, const RejCfg &c, const Sums *S0,
 	case SGPU_LINEARFIT: fast_linearfit(s, n, c, rej, o); break;
 	case SGPU_GESDT: fast_gesdt<U16>(s, n, nb, c, S0, rej, o); break;
 	case SGPU_MAD: fast_mad<U16>(s, n, c, S0, rej, o); break;
-	default: o.status = FAST_FALLBACK; break;	// SIGMEDIAN: exact engine
+	case SGPU_SIGMEDIAN: fast_sigmedian<U16>(s, n, c, S0, rej, o); break;
+	default: o.status = FAST_FALLBACK; break;
 	}
 	if (o.status != FAST_DONE || o.kept == 0) o.status = FAST_FALLBACK;
 }

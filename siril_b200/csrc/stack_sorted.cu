@@ -32,9 +32,9 @@ bool sgpu_sorted_supports(const sgpu_block_desc &d, const sgpu_stack_args *a) {
 	if (d.nb_frames > 2048 || (size_t) d.height * d.width >= (1u << 30)) return false;
 	if (!a->is_mean) return true;
 	switch (a->type_of_rejection) {
-	case SGPU_NO_REJEC: case SGPU_PERCENTILE: case SGPU_SIGMA: case SGPU_MAD: case SGPU_LINEARFIT: case SGPU_GESDT: return true;
+	case SGPU_NO_REJEC: case SGPU_PERCENTILE: case SGPU_SIGMA: case SGPU_MAD: case SGPU_SIGMEDIAN: case SGPU_LINEARFIT: case SGPU_GESDT: return true;
 	case SGPU_WINSORIZED: return d.dtype == SGPU_F32;
-	default: return false;	// SIGMEDIAN, 16-bit WINSORIZED: exact engine
+	default: return false;	// 16-bit WINSORIZED: exact engine
 	}
 }
 

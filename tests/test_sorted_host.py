@@ -17,11 +17,11 @@ SO = os.path.join(HERE, "helpers", "libsorted_host.so")
 SRC = os.path.join(HERE, "helpers", "sorted_host.cu")
 HDRS = [os.path.join(HERE, "..", "siril_b200", "csrc", h) for h in ("sorted.cuh", "exact.cuh")]
 
-FAST = [O.NO_REJEC, O.PERCENTILE, O.SIGMA, O.MAD, O.WINSORIZED, O.LINEARFIT, O.GESDT]
+FAST = [O.NO_REJEC, O.PERCENTILE, O.SIGMA, O.MAD, O.SIGMEDIAN, O.WINSORIZED, O.LINEARFIT, O.GESDT]
 NAMES = {O.NO_REJEC: "none", O.PERCENTILE: "percentile", O.SIGMA: "sigma", O.WINSORIZED: "winsorized",
-         O.LINEARFIT: "linearfit", O.GESDT: "gesdt", O.MAD: "mad"}
+         O.LINEARFIT: "linearfit", O.GESDT: "gesdt", O.MAD: "mad", O.SIGMEDIAN: "sigmedian"}
 SIGS = {O.NO_REJEC: (3, 3), O.PERCENTILE: (0.2, 0.3), O.SIGMA: (3, 3), O.WINSORIZED: (3, 3), O.LINEARFIT: (5, 5),
-        O.GESDT: (0.3, 0.05), O.MAD: (3, 3)}
+        O.GESDT: (0.3, 0.05), O.MAD: (3, 3), O.SIGMEDIAN: (3, 3)}
 
 
 @pytest.fixture(scope="module")
