@@ -297,12 +297,33 @@ def run_ours(args, wl):
     stats_ms = None
     if nrm != NO_NORM:
         from siril_b200.stacking import compute_estimators, finalize_factors, STATS_WORKERS
-        if world > 1:       # every rank holds rows of every frame: the reductions behind the statistics are all-reduced
+        if world > 1 and args.stats == "reduce":
+            # every rank holds rows of every frame: the reductions behind the statistics are all-reduced, plane by plane
             dist.all_reduce(torch.zeros(1, device=dev))     # the first collective pays the communicator set-up
             reducer = sharding.make_reducer(dist, dev)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             off, mul, sc, bg = compute_estimators(sargs, shard=(reducer, r0, H))
+        elif world > 1:
+            # frame-parallel: one all-to-all turns the row shards into whole frames (frames f = rank mod N here), each
+            # GPU computes its frames' statistics with the single-GPU kernels, the estimators are all-gathered
+            dist.all_reduce(torch.zeros(1, device=dev))
+            whole, mine = sharding.frames_from_shards(dist, frames, rank, world)       # warm-up: communicator, allocator
+            wargs = sb.StackingArgs(method=sargs.method, frames=whole, normalize=nrm, ctx=ctx)
+            compute_estimators(wargs, list(range(min(len(mine), STATS_WORKERS))))
+            del whole, wargs
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            whole, mine = sharding.frames_from_shards(dist, frames, rank, world)
+            wargs = sb.StackingArgs(method=sargs.method, frames=whole, normalize=nrm, ctx=ctx)
+            lo, lm, ls, lb = compute_estimators(wargs)
+            part = [np.zeros((c, n)) for _ in range(4)]
+            for a, l in zip(part, (lo, lm, ls, lb)):
+                a[:, mine] = l
+            off, mul, sc, bg = sharding.merge_estimators(dist, part, mine, dev)
+            del whole, wargs
+            torch.cuda.empty_cache()
         else:
             compute_estimators(sargs, list(range(min(n, STATS_WORKERS))))     # warm-up: worker contexts, scratch, kernel attributes
             torch.cuda.synchronize()
@@ -530,6 +551,9 @@ def main():
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: how the rows reach rank 0 — stored into its image by the stacking kernels over NVLink (peer), "
                          "or sent after the stack with NCCL send / recv (nccl)")
+    ap.add_argument("--stats", default="frames", choices=["frames", "reduce"],
+                    help="N > 1, workloads with normalization: statistics frame-parallel after an all-to-all of the shards "
+                         "(frames) or on the row shards with every reduction all-reduced (reduce)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--height", type=int, default=0, help="profiling only: override the workload's image height")

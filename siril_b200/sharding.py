@@ -190,3 +190,32 @@ class PeerImage:
                 self.L.sgpu_ipc_close(self.ctx.h, self.base)
                 self.dist.barrier()
             self.base = None
+
+
+def frames_from_shards(dist, shard, rank=None, world=None):
+    """Row shards -> whole frames, frame-parallel (first alternative of the statistics phase): every rank
+    holds rows [H*g/G, H*(g+1)/G) of EVERY frame ([N][C][h_g][W], device resident) and ends up with ALL rows of the frames
+    f = rank (mod G) ([N_g][C][H][W]): one all-to-all of pixel data over NVLink, (G-1)/G of the shard out and as much in.
+    The per-frame statistics are whole-frame quantities (normalization.c:217-294): after this each frame's statistics
+    are computed by one GPU with the single-GPU kernels — bit-identical to one GPU — and only the estimators travel
+    (merge_estimators).  Returns (frames [N_g][C][H][W], indices of those frames)."""
+    import torch
+    world = dist.get_world_size() if world is None else world
+    rank = dist.get_rank() if rank is None else rank
+    n, c, h, w = shard.shape
+    u16 = shard.dtype == torch.uint16
+    if u16:     # (no 16-bit integer type in torch's NCCL binding: the samples travel as byte views, 2 W bytes per row)
+        shard = shard.contiguous().view(torch.uint8)
+        w = 2 * w
+    mine = list(range(rank, n, world))
+    rows = torch.tensor([h], dtype=torch.int64, device=shard.device)
+    all_rows = [torch.zeros_like(rows) for _ in range(world)]
+    dist.all_gather(all_rows, rows)
+    heights = [int(r) for r in all_rows]
+    send = [shard[r::world].contiguous() for r in range(world)]                       # my rows of rank r's frames
+    recv = [torch.empty((len(mine), c, heights[r], w), dtype=shard.dtype, device=shard.device) for r in range(world)]
+    dist.all_to_all(recv, send)
+    del send
+    whole = torch.cat(recv, dim=2)      # rank order is row order
+    del recv
+    return (whole.view(torch.uint16) if u16 else whole), mine

@@ -57,6 +57,15 @@ def _worker(rank, world, port, q, dtype_name, normalize, rejection, sig):
         lo = sh.gather_rows(dist, args.result.rejmap_low)
         hi = sh.gather_rows(dist, args.result.rejmap_high)
         irej = sh.reduce_irej(dist, torch.from_numpy(args.result.irej.astype(np.int64)).to(dev)).cpu().numpy()
+        # statistics the other way: one all-to-all turns the shards into whole frames, each GPU computes its frames'
+        # statistics with the single-GPU kernels, the estimators are all-gathered (sharding.frames_from_shards)
+        whole, idx = sh.frames_from_shards(dist, mine, rank, world)
+        wargs = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=whole, normalize=normalize, ctx=args.ctx)
+        part = [np.zeros((C, N)) for _ in range(4)]
+        for arr, loc in zip(part, compute_estimators(wargs)):
+            arr[:, idx] = loc
+        est2 = sh.merge_estimators(dist, part, idx, dev)
+        del whole, wargs
         # the same stack again, every rank's kernels storing its rows straight into rank 0's image over NVLink
         # (sgpu_ipc_export / sgpu_ipc_open + out_plane_stride): no gather
         import ctypes as Cc
@@ -84,7 +93,7 @@ def _worker(rank, world, port, q, dtype_name, normalize, rejection, sig):
         peer.close()
         if rank == 0:
             q.put((rank, dict(off=off, mul=mul, sc=sc, bg=bg, coeff=(args.coeff.offset, args.coeff.mul, args.coeff.scale),
-                              out=to_np(out), lo=to_np(lo), hi=to_np(hi), irej=irej, peer=peer_res, pirej=pirej.cpu().numpy())))
+                              out=to_np(out), lo=to_np(lo), hi=to_np(hi), irej=irej, peer=peer_res, pirej=pirej.cpu().numpy(), est2=est2)))
         else:
             q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
@@ -130,6 +139,8 @@ def test_row_sharded_normalization_and_stack(orc, dtype, normalize, rejection, s
         assert np.array_equal(a, b), (name, np.abs(a - b).max())
     assert np.allclose(got["sc"], sc, rtol=1e-12, atol=0), np.abs(got["sc"] / sc - 1).max()
     assert np.allclose(got["bg"], bg, rtol=1e-12, atol=0), np.abs(got["bg"] / bg - 1).max()
+    for a, b in zip(got["est2"], (off, mul, sc, bg)):     # frame-parallel after the all-to-all: one GPU's own numbers, bit for bit
+        assert np.array_equal(a, b)
     finalize_factors(args, off.copy(), mul.copy(), sc.copy())
     for a, b in zip(got["coeff"], (args.coeff.offset, args.coeff.mul, args.coeff.scale)):
         assert np.allclose(a, b, rtol=1e-12, atol=1e-300)
