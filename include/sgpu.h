@@ -246,6 +246,15 @@ int sgpu_stack_host(sgpu_ctx *ctx, const sgpu_block_desc *desc, const void *cons
 int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, const int *shifty,
 		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
 
+/* FITS sequence files (SEQ_FITSEQ: one frame per HDU, io/fits_sequence.c): the frames _find_hdus keeps (:39-150 — image HDUs
+ * with NAXIS > 1 that are not ICC profiles, thumbnails, HDRLET / WCS / D2IM extensions; an HDU whose layer count or sample type
+ * differs from the first image's is skipped, a different width or height fails the file), each with the offset of its data
+ * unit: sgpu_block_upload_fits_fd reads them as it reads single-image files.  infos may be NULL to count. */
+int sgpu_fitseq_probe(const char *path, sgpu_fits_info *infos, int max_frames, int *nb_frames);
+/* sgpu_stack_fits over frames of one sequence file; frame_indices (NULL: 0 .. nb_frames - 1) index the probed frames */
+int sgpu_stack_fitseq(sgpu_ctx *ctx, const char *path, int nb_frames, const int *frame_indices, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
+
 /* norm_to_0_1_range (median_and_mean.c:557-582) split for row shards: min/max over non-zero
  * samples (skip_first: the reference's scan starts at index 1 — set it on the shard that holds
  * element 0), then the rescale with the globally reduced min/max. */

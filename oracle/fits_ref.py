@@ -51,6 +51,68 @@ def write_fits(path, data, bzero=None, datamax=None, extra_cards=()):
     return len(hdr)
 
 
+def _hdu_bytes(data, primary, extname=None, bzero=None, datamax=None):
+    a = np.asarray(data)
+    if a.ndim == 2:
+        a = a[None]
+    c, h, w = a.shape
+    if a.dtype == np.uint16:
+        bitpix, raw = 16, (a.astype(np.int32) - 32768).astype(">i2")
+        bzero = 32768 if bzero is None else bzero
+    elif a.dtype == np.int16:
+        bitpix, raw = 16, a.astype(">i2")
+    elif a.dtype == np.uint8:
+        bitpix, raw = 8, a
+    elif a.dtype == np.float32:
+        bitpix, raw = -32, a.astype(">f4")
+    else:
+        raise TypeError(a.dtype)
+    first = f"{'SIMPLE':<8}= {'T':>20}" if primary else f"{'XTENSION':<8}= {repr('IMAGE   '):<20}"
+    cards = [first, f"{'BITPIX':<8}= {bitpix:>20d}", f"{'NAXIS':<8}= {3 if c > 1 else 2:>20d}",
+             f"{'NAXIS1':<8}= {w:>20d}", f"{'NAXIS2':<8}= {h:>20d}"]
+    if c > 1:
+        cards.append(f"{'NAXIS3':<8}= {c:>20d}")
+    if not primary:
+        cards += [f"{'PCOUNT':<8}= {0:>20d}", f"{'GCOUNT':<8}= {1:>20d}"]
+    if bzero is not None:
+        cards += [f"{'BZERO':<8}= {float(bzero):>20.1f}", f"{'BSCALE':<8}= {1.0:>20.1f}"]
+    if datamax is not None:
+        cards.append(f"{'DATAMAX':<8}= {float(datamax):>20.6E}")
+    if extname:
+        cards.append(f"{'EXTNAME':<8}= {repr(extname):<20}")
+    cards.append("END")
+    hdr = "".join(f"{x:<80}" for x in cards)
+    hdr += " " * (-len(hdr) % 2880)
+    body = raw.tobytes()
+    return hdr.encode("ascii") + body + b"\0" * (-len(body) % 2880)
+
+
+def write_fitseq(path, hdus, empty_primary=True):
+    """a FITS sequence file (SEQ_FITSEQ, io/fits_sequence.c): `hdus` is a list of (data [layer][row][col], extname or None,
+    datamax or None) image HDUs, or ("table", nbytes) for a binary table the reader must step over; with empty_primary the
+    primary HDU holds no data (NAXIS = 0), as astronomy pipelines write it"""
+    with open(path, "wb") as f:
+        first = True
+        if empty_primary:
+            cards = [f"{'SIMPLE':<8}= {'T':>20}", f"{'BITPIX':<8}= {8:>20d}", f"{'NAXIS':<8}= {0:>20d}", f"{'EXTEND':<8}= {'T':>20}", "END"]
+            hdr = "".join(f"{x:<80}" for x in cards)
+            f.write((hdr + " " * (-len(hdr) % 2880)).encode("ascii"))
+            first = False
+        for h in hdus:
+            if isinstance(h[0], str) and h[0] == "table":
+                nbytes = int(h[1])
+                cards = [f"{'XTENSION':<8}= {repr('BINTABLE'):<20}", f"{'BITPIX':<8}= {8:>20d}", f"{'NAXIS':<8}= {2:>20d}",
+                         f"{'NAXIS1':<8}= {nbytes:>20d}", f"{'NAXIS2':<8}= {1:>20d}", f"{'PCOUNT':<8}= {0:>20d}", f"{'GCOUNT':<8}= {1:>20d}",
+                         f"{'TFIELDS':<8}= {0:>20d}", "END"]
+                hdr = "".join(f"{x:<80}" for x in cards)
+                f.write((hdr + " " * (-len(hdr) % 2880)).encode("ascii"))
+                f.write(b"\x7f" * nbytes + b"\0" * (-nbytes % 2880))
+                continue
+            data, extname, datamax = h
+            f.write(_hdu_bytes(data, first, extname=extname, datamax=datamax))
+            first = False
+
+
 def parse_header(path):
     """BITPIX, (w, h, c), BZERO, DATAMAX or None, data offset"""
     kv, off = {}, 0

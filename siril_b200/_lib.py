@@ -103,6 +103,8 @@ SIGNATURES = {
     "sgpu_stack_block": (C.c_int, [P, P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_stack_host": (C.c_int, [P, C.POINTER(BlockDesc), C.POINTER(P), P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_stack_fits": (C.c_int, [P, C.c_int, C.POINTER(C.c_char_p), P, C.POINTER(StackArgs), P, P, P, P]),
+    "sgpu_fitseq_probe": (C.c_int, [C.c_char_p, P, C.c_int, C.POINTER(C.c_int)]),
+    "sgpu_stack_fitseq": (C.c_int, [P, C.c_char_p, C.c_int, P, P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_minmax_nonzero_static": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_rescale_0_1": (C.c_int, [P, P, C.c_size_t, C.c_float, C.c_float]),

@@ -230,7 +230,120 @@ static bool card_value(const char *card, const char *key, double *v) {
 	return true;
 }
 
+// a string-valued card: KEY     = 'value   '  (trailing blanks dropped)
+static bool card_string(const char *card, const char *key, char out[72]) {
+	const size_t kl = strlen(key);
+	if (strncmp(card, key, kl) != 0) return false;
+	for (size_t i = kl; i < 8; i++) if (card[i] != ' ') return false;
+	if (card[8] != '=') return false;
+	const char *q = (const char *) memchr(card + 10, '\'', 70);
+	if (!q) return false;
+	size_t n = 0;
+	for (const char *p = q + 1; p < card + 80 && *p != '\'' && n < 71; p++) out[n++] = *p;
+	while (n && out[n - 1] == ' ') n--;
+	out[n] = 0;
+	return true;
+}
+
+// One header-data unit starting at byte `off` of an open file: the image keywords into `info` (data_offset = first byte
+// behind the header), whether it is an image HDU (the primary, or XTENSION = 'IMAGE'), its EXTNAME, ZIMAGE (a tile-
+// compressed image stored as a binary table) and where the next HDU starts (the data unit is |BITPIX| / 8 * GCOUNT *
+// (PCOUNT + NAXIS1 * ... * NAXISn) bytes, padded to 2880).  false: no HDU here (end of file, or not FITS).
+struct HduScan { sgpu_fits_info info; int naxis; bool is_image, compressed; char extname[72]; long next; };
+static bool scan_hdu(int fd, long off, long file_size, bool primary, HduScan *h) {
+	memset(h, 0, sizeof *h);
+	h->info.bscale = 1.0; h->naxis = -1;
+	h->info.naxes[0] = h->info.naxes[1] = h->info.naxes[2] = 1;
+	long axes[10]; for (long &a : axes) a = 1;
+	long pcount = 0, gcount = 1;
+	char blk[2880];
+	bool first = true, done = false;
+	while (!done) {
+		size_t got = 0;
+		while (got < sizeof blk) {
+			const ssize_t r = pread(fd, blk + got, sizeof blk - got, off + (long) got);
+			if (r < 0 && errno == EINTR) continue;
+			if (r <= 0) break;
+			got += (size_t) r;
+		}
+		if (got < sizeof blk) return false;
+		if (first) {
+			char xt[72];
+			if (primary) { if (strncmp(blk, "SIMPLE  =", 9) != 0) return false; h->is_image = true; }
+			else { if (!card_string(blk, "XTENSION", xt)) return false; h->is_image = strcmp(xt, "IMAGE") == 0; }
+		}
+		first = false;
+		off += (long) sizeof blk;
+		for (int c = 0; c < 36; c++) {
+			const char *card = blk + 80 * c;
+			double v; char sv[72];
+			if (strncmp(card, "END     ", 8) == 0) { done = true; break; }
+			if (card_value(card, "BITPIX", &v)) h->info.bitpix = (int) v;
+			else if (card_value(card, "NAXIS", &v)) h->naxis = (int) v;
+			else if (strncmp(card, "NAXIS", 5) == 0 && card[5] >= '1' && card[5] <= '9' && card[6] == ' ') {
+				char key[8] = "NAXIS0"; key[5] = card[5];
+				if (card_value(card, key, &v)) { axes[card[5] - '0'] = (long) v; if (card[5] <= '3') h->info.naxes[card[5] - '1'] = (long) v; }
+			}
+			else if (card_value(card, "PCOUNT", &v)) pcount = (long) v;
+			else if (card_value(card, "GCOUNT", &v)) gcount = (long) v;
+			else if (card_value(card, "BZERO", &v)) h->info.bzero = v;
+			else if (card_value(card, "BSCALE", &v)) h->info.bscale = v;
+			else if (card_value(card, "DATAMAX", &v)) { h->info.datamax = v; h->info.has_datamax = 1; }
+			else if (card_string(card, "EXTNAME", sv)) memcpy(h->extname, sv, sizeof sv);
+			else if (strncmp(card, "ZIMAGE  =", 9) == 0 && memchr(card + 10, 'T', 21)) h->compressed = true;
+		}
+	}
+	if (h->naxis < 0 || h->naxis > 9 || h->info.bitpix == 0) return false;
+	long n = h->naxis ? 1 : 0;
+	for (int k = 1; k <= h->naxis; k++) n *= axes[k];
+	const long bytes = (labs((long) h->info.bitpix) / 8) * gcount * (pcount + n);
+	h->info.data_offset = off;
+	h->next = off + (bytes + 2879) / 2880 * 2880;
+	if (off + bytes > file_size) return false;
+	const bool plain = h->info.bscale == 1.0;
+	h->info.device_readable = h->is_image && !h->compressed && plain && ((h->info.bitpix == 8 && h->info.bzero == 0.0) ||
+			(h->info.bitpix == 16 && (h->info.bzero == 0.0 || h->info.bzero == 32768.0)) ||
+			(h->info.bitpix == -32 && h->info.bzero == 0.0));
+	return true;
+}
+
 extern "C" {
+
+/* The frames of a FITS sequence file (SEQ_FITSEQ: one image per HDU), chosen as _find_hdus does (io/fits_sequence.c:39-150):
+ * image HDUs with NAXIS > 1, not named ICCProfile / Thumbnail / HDRLET / WCS / D2IM; an HDU whose layer count or sample
+ * type differs from the first image's is skipped, one whose width or height differs fails the file. */
+int sgpu_fitseq_probe(const char *path, sgpu_fits_info *infos, int max_frames, int *nb_frames) {
+	if (!path || !nb_frames) return SGPU_GENERIC_ERROR;
+	*nb_frames = 0;
+	const int fd = open(path, O_RDONLY);
+	if (fd < 0) return SGPU_SEQUENCE_ERROR;
+	struct stat st;
+	if (fstat(fd, &st) != 0) { close(fd); return SGPU_SEQUENCE_ERROR; }
+	long off = 0; bool primary = true, have_ref = false; int rv = SGPU_OK, count = 0;
+	sgpu_fits_info ref; memset(&ref, 0, sizeof ref);
+	auto kind = [](const sgpu_fits_info &i) { return i.bitpix == 16 && i.bzero == 32768.0 ? 20 : i.bitpix; };	// manage_bitpix: USHORT_IMG
+	while (off < (long) st.st_size) {
+		HduScan h;
+		if (!scan_hdu(fd, off, (long) st.st_size, primary, &h)) { if (primary) rv = SGPU_SEQUENCE_ERROR; break; }
+		primary = false; off = h.next;
+		if (!h.is_image) continue;
+		static const char *skip[] = { "ICCProfile", "Thumbnail", "HDRLET", "WCS", "D2IM" };
+		bool skipped = false;
+		for (const char *sname : skip) if (strncmp(h.extname, sname, strlen(sname)) == 0) skipped = true;
+		if (skipped || h.naxis <= 1) continue;
+		if (!have_ref) { ref = h.info; have_ref = true; }
+		else {
+			if (h.info.naxes[2] != ref.naxes[2] || kind(h.info) != kind(ref)) continue;
+			if (h.info.naxes[0] != ref.naxes[0] || h.info.naxes[1] != ref.naxes[1]) { rv = SGPU_SEQUENCE_ERROR; break; }	// "different parameters, which is not allowed"
+		}
+		if (infos && count < max_frames) infos[count] = h.info;
+		count++;
+	}
+	close(fd);
+	if (rv) return rv;
+	*nb_frames = count;
+	return SGPU_OK;
+}
 
 int sgpu_fits_probe(const char *path, sgpu_fits_info *info) {
 	if (!path || !info) return SGPU_GENERIC_ERROR;
@@ -303,29 +416,23 @@ int sgpu_block_upload_fits_fd(sgpu_block *b, int frame, int fd, long data_offset
 	return upload_raw(b, frame, src, bitpix, frame_height, row0, shifty, rescale_ushrt);
 }
 
-int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, const int *shifty,
+// the block loop over frames that are data units of open files: fds[f] / fi[f] (several frames may share a descriptor)
+static int stack_fits_units(sgpu_ctx *ctx, int nb_frames, const std::vector<int> &fds, const std::vector<sgpu_fits_info> &fi, const int *shifty,
 		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
-	if (!ctx || !paths || nb_frames < 1 || !out) return SGPU_GENERIC_ERROR;
-	std::vector<sgpu_fits_info> fi(nb_frames);
-	std::vector<int> fds(nb_frames, -1);
-	auto close_all = [&](int code) { for (int fd : fds) if (fd >= 0) close(fd); return code; };
 	for (int f = 0; f < nb_frames; f++) {
-		if (!paths[f] || sgpu_fits_probe(paths[f], &fi[f])) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d of the sequence as FITS", f));
-		if (!fi[f].device_readable) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d (BITPIX %d, BZERO %g, BSCALE %g) needs cfitsio", f, fi[f].bitpix, fi[f].bzero, fi[f].bscale));
+		if (!fi[f].device_readable) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d (BITPIX %d, BZERO %g, BSCALE %g) needs cfitsio", f, fi[f].bitpix, fi[f].bzero, fi[f].bscale);
 		// "stacking an image sequence with different image sizes is not possible" (median_and_mean.c:1300-1310)
 		if (fi[f].bitpix != fi[0].bitpix || fi[f].naxes[0] != fi[0].naxes[0] || fi[f].naxes[1] != fi[0].naxes[1] || fi[f].naxes[2] != fi[0].naxes[2])
-			return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d differs in size or sample type from the first image", f));
-		fds[f] = open(paths[f], O_RDONLY);
-		if (fds[f] < 0) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open image %d", f));
+			return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "image %d differs in size or sample type from the first image", f);
 	}
-	if (fi[0].naxes[2] > 3) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "more than three layers"));
+	if (fi[0].naxes[2] > 3) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "more than three layers");
 	const sgpu_block_desc desc = { nb_frames, (int) fi[0].naxes[2], (int) fi[0].naxes[0], (int) fi[0].naxes[1],
 			fi[0].bitpix == -32 ? SGPU_F32 : SGPU_U16 };
 	const int H = desc.height;
 	// Float data without a DATAMAX key: the reference guesses the range from three or four samples of
 	// whatever region it has just read (image_format_fits.c:997-1003), so its answer depends on ITS
 	// block plan.  The row blocks here are not the reference's, and a frame must not be scaled in one
-	// block and left alone in another: the guess is made ONCE per file, on the samples the reference
+	// block and left alone in another: the guess is made ONCE per frame, on the samples the reference
 	// would look at when it reads the first layer whole.
 	std::vector<int> rescale(nb_frames, 0);
 	for (int f = 0; f < nb_frames; f++) {
@@ -336,7 +443,7 @@ int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, cons
 		double data_max = 0.;
 		for (size_t i = 0; i < nbdata; i += nbdata / 3) {
 			unsigned char q[4];
-			if (pread(fds[f], q, 4, (off_t) (fi[f].data_offset + i * 4)) != 4) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d", f));
+			if (pread(fds[f], q, 4, (off_t) (fi[f].data_offset + i * 4)) != 4) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d", f);
 			const uint32_t w = ((uint32_t) q[0] << 24) | ((uint32_t) q[1] << 16) | ((uint32_t) q[2] << 8) | q[3];
 			float x; memcpy(&x, &w, 4);
 			data_max = (data_max > x) ? data_max : x;	// the reference's max() macro, NaN included
@@ -345,11 +452,46 @@ int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, cons
 	}
 	sgpu_stack_args with_bitpix = *args;
 	with_bitpix.source_bitpix = fi[0].bitpix;	// BYTE_IMG sequences: normalize_to16bit
-	const int rv = sgpu_stack_host_impl(ctx, &desc, [&](sgpu_block *b, int f, int row0) {
+	return sgpu_stack_host_impl(ctx, &desc, [&](sgpu_block *b, int f, int row0) {
 		RawSource src; src.fd = fds[f]; src.base = (off_t) fi[f].data_offset;
 		return upload_raw(b, f, src, fi[f].bitpix, H, row0, shifty ? shifty[f] : 0, rescale[f]);
 	}, &with_bitpix, out, rej_low, rej_high, irej);
-	return close_all(rv);
+}
+
+int sgpu_stack_fits(sgpu_ctx *ctx, int nb_frames, const char *const *paths, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !paths || nb_frames < 1 || !out) return SGPU_GENERIC_ERROR;
+	std::vector<sgpu_fits_info> fi(nb_frames);
+	std::vector<int> fds(nb_frames, -1);
+	auto close_all = [&](int code) { for (int fd : fds) if (fd >= 0) close(fd); return code; };
+	for (int f = 0; f < nb_frames; f++) {
+		if (!paths[f] || sgpu_fits_probe(paths[f], &fi[f])) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read image %d of the sequence as FITS", f));
+		fds[f] = open(paths[f], O_RDONLY);
+		if (fds[f] < 0) return close_all(sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open image %d", f));
+	}
+	return close_all(stack_fits_units(ctx, nb_frames, fds, fi, shifty, args, out, rej_low, rej_high, irej));
+}
+
+/* sgpu_stack_fits for a FITS sequence file: frame_indices (or NULL: all, in file order) select among the frames
+ * sgpu_fitseq_probe finds (args->image_indices over fitseq->hdu_index, io/fits_sequence.c:285-300) */
+int sgpu_stack_fitseq(sgpu_ctx *ctx, const char *path, int nb_frames, const int *frame_indices, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !path || nb_frames < 1 || !out) return SGPU_GENERIC_ERROR;
+	int total = 0;
+	if (sgpu_fitseq_probe(path, nullptr, 0, &total) || total < 1) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read %s as a FITS sequence", path);
+	std::vector<sgpu_fits_info> all(total), fi(nb_frames);
+	if (sgpu_fitseq_probe(path, all.data(), total, &total)) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read %s as a FITS sequence", path);
+	for (int f = 0; f < nb_frames; f++) {
+		const int k = frame_indices ? frame_indices[f] : f;
+		if (k < 0 || k >= total) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d is not in the sequence file (%d frames)", k, total);
+		fi[f] = all[k];
+	}
+	const int fd = open(path, O_RDONLY);
+	if (fd < 0) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open %s", path);
+	std::vector<int> fds(nb_frames, fd);
+	const int rv = stack_fits_units(ctx, nb_frames, fds, fi, shifty, args, out, rej_low, rej_high, irej);
+	close(fd);
+	return rv;
 }
 
 }	// extern "C"

@@ -77,16 +77,36 @@ def read_block_data(ctx, paths, row0=0, height=None, shifty=None, source="fd"):
     return out
 
 
-def stack_fits(args, paths, is_mean=True):
+def fitseq_probe(path):
+    """the frames of a FITS sequence file (sgpu_fitseq_probe; _find_hdus, io/fits_sequence.c:39-150) as FitsInfo records"""
+    L = _lib.lib()
+    n = C.c_int(0)
+    if L.sgpu_fitseq_probe(os.fsencode(path), None, 0, C.byref(n)):
+        raise _lib.SgpuError(-2, f"{path}: not a FITS sequence file")
+    infos = (_lib.FitsInfo * max(n.value, 1))()
+    if L.sgpu_fitseq_probe(os.fsencode(path), infos, n.value, C.byref(n)):
+        raise _lib.SgpuError(-2, f"{path}: not a FITS sequence file")
+    return [infos[i] for i in range(n.value)]
+
+
+def stack_fits(args, paths, is_mean=True, frame_indices=None):
     """stack_mean_or_median (median_and_mean.c:1261-1826) for a sequence of FITS files on disk:
     sgpu_stack_fits.  `args` is a StackingArgs without frames; the result lands in args.result as
     numpy arrays, like the host-frame path of stack_mean_or_median."""
     from . import stacking
     L = _lib.lib()
     ctx = stacking._context(args)
-    i0 = fits_probe(paths[0])
+    fitseq = isinstance(paths, (str, bytes, os.PathLike))     # one FITS sequence file instead of a list of files
+    if fitseq:
+        frames = fitseq_probe(paths)
+        idx = list(range(len(frames))) if frame_indices is None else [int(i) for i in frame_indices]
+        if not frames or any(i < 0 or i >= len(frames) for i in idx):
+            args.retval = -2
+            return -2
+        i0, n = frames[idx[0]], len(idx)
+    else:
+        i0, n = fits_probe(paths[0]), len(paths)
     w, h, c = i0.naxes[0], i0.naxes[1], i0.naxes[2]
-    n = len(paths)
     keep = []
     try:
         ca = stacking._fill_cargs(args, n, c, is_mean, keep)
@@ -100,12 +120,15 @@ def stack_fits(args, paths, is_mean=True):
     rh = np.zeros((c, h, w), dtype=np.uint16) if nmaps == 2 else None
     irej = np.zeros(6, dtype=np.uint64)
     sy = np.ascontiguousarray(args.shifty, dtype=np.int32) if args.shifty is not None else None
-    cp = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
-    rv = L.sgpu_stack_fits(ctx.h, n, cp, sy.ctypes.data_as(C.c_void_p) if sy is not None else None, C.byref(ca),
-                           out.ctypes.data_as(C.c_void_p),
-                           rl.ctypes.data_as(C.c_void_p) if rl is not None else None,
-                           rh.ctypes.data_as(C.c_void_p) if rh is not None else None,
-                           irej.ctypes.data_as(C.c_void_p))
+    outs = (out.ctypes.data_as(C.c_void_p), rl.ctypes.data_as(C.c_void_p) if rl is not None else None,
+            rh.ctypes.data_as(C.c_void_p) if rh is not None else None, irej.ctypes.data_as(C.c_void_p))
+    syp = sy.ctypes.data_as(C.c_void_p) if sy is not None else None
+    if fitseq:
+        ia = np.ascontiguousarray(idx, dtype=np.int32)
+        rv = L.sgpu_stack_fitseq(ctx.h, os.fsencode(paths), n, ia.ctypes.data_as(C.c_void_p), syp, C.byref(ca), *outs)
+    else:
+        cp = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
+        rv = L.sgpu_stack_fits(ctx.h, n, cp, syp, C.byref(ca), *outs)
     args.retval = rv
     if rv:
         args.error = (L.sgpu_last_error(ctx.h) or b"").decode()

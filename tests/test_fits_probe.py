@@ -56,3 +56,32 @@ def test_oracle_decode_known_bytes(tmp_path):
     fits_ref.write_fits(p, np.array([[1.0, 65535.0, 0.5, 20.0]], np.float32), datamax=65535.0)
     got = fits_ref.read_block([p])[0, 0, 0]
     assert got[1] == np.float32(65535.0) * np.float32(.000015259022)
+
+
+def test_fitseq_probe_follows_find_hdus(tmp_path):
+    """FITS sequence files (io/fits_sequence.c:39-150): which HDUs are frames, and where their data units start"""
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    rng = np.random.default_rng(8)
+    fr = [(rng.random((1, 11, 17)) * 60000).astype(np.uint16) for _ in range(4)]
+    p = str(tmp_path / "seq.fit")
+    hdus = [(fr[0], None, None), ("table", 3000), (fr[1], "SCI", None), ((rng.random((3, 11, 17)) * 100).astype(np.uint16), None, None),
+            ((rng.random((1, 5, 5)) * 100).astype(np.uint16), "Thumbnail", None), (fr[2], None, None),
+            (rng.random((1, 11, 17)).astype(np.float32), None, 1.0), (fr[3], "ICCProfile", None)]
+    fits_ref.write_fitseq(p, hdus)
+    infos = fitsread.fitseq_probe(p)
+    assert len(infos) == 3          # the RGB HDU, the thumbnail, the float HDU and the ICC profile are not frames; the table is stepped over
+    raw = open(p, "rb").read()
+    for info, want in zip(infos, fr[:3]):
+        assert (info.bitpix, info.bzero, info.naxes[0], info.naxes[1], info.naxes[2], info.device_readable) == (16, 32768.0, 17, 11, 1, 1)
+        got = np.frombuffer(raw, dtype=">i2", count=11 * 17, offset=info.data_offset).astype(np.int32) + 32768
+        assert np.array_equal(got.reshape(11, 17), want[0])
+    # an image of another size fails the file ("different parameters, which is not allowed")
+    q = str(tmp_path / "bad.fit")
+    fits_ref.write_fitseq(q, [(fr[0], None, None), ((rng.random((1, 12, 17)) * 100).astype(np.uint16), None, None)])
+    with pytest.raises(Exception):
+        fitsread.fitseq_probe(q)
+    # image in the primary HDU, extensions after it
+    r = str(tmp_path / "prim.fit")
+    fits_ref.write_fitseq(r, [(fr[0], None, None), (fr[1], None, None)], empty_primary=False)
+    assert len(fitsread.fitseq_probe(r)) == 2

@@ -212,3 +212,35 @@ def test_stack_fits_rejects_mixed_sequences(tmp_path):
     args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None)
     assert fitsread.stack_fits(args, [a, b, a]) == sb.ST_SEQUENCE_ERROR
     assert fitsread.stack_fits(args, [a, str(tmp_path / "missing.fit")]) == sb.ST_SEQUENCE_ERROR
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.uint16], ids=["f32", "u16"])
+def test_stack_fitseq_file(tmp_path, orc, dtype):
+    """sgpu_stack_fitseq: the frames of ONE FITS sequence file (one image per HDU), a subset of them by index, through the
+    same raw reader; against the oracle on the decoded frames"""
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    rng = np.random.default_rng(33)
+    N, C, H, W = 11, 1, 30, 70
+    fr = 0.1 + 0.01 * rng.standard_normal((N, C, H, W))
+    fr[rng.random(fr.shape) < 0.01] += 0.4
+    fr = fr.astype(np.float32) if dtype == np.float32 else np.round(fr * 65535).astype(np.uint16)
+    p = str(tmp_path / "seq.fit")
+    hdus = []
+    for f in range(N):
+        hdus.append((fr[f], None, 1.0 if dtype == np.float32 else None))
+        if f == 3:
+            hdus.append(("table", 5000))
+            hdus.append(((rng.random((1, 4, 4)) * 10).astype(fr.dtype), "Thumbnail", None))
+    fits_ref.write_fitseq(p, hdus)
+    idx = [0, 2, 3, 4, 5, 7, 8, 10]
+    sy = rng.integers(-2, 3, len(idx)).astype(np.int32)
+    args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.SIGMA,
+                           sig=(3.0, 3.0), create_rejmaps=True, shifty=sy)
+    assert fitsread.stack_fits(args, p, frame_indices=idx) == 0, getattr(args, "error", "")
+    ref = orc.stack(fr[idx], rejection=sb.SIGMA, sig=(3.0, 3.0), create_rejmaps=True, shifty=sy)
+    assert np.array_equal(args.result.irej, ref["irej"])
+    assert np.array_equal(args.result.rejmap_low, ref["rej_low"]) and np.array_equal(args.result.rejmap_high, ref["rej_high"])
+    rel = np.abs(args.result.data - ref["out"]) / np.maximum(np.abs(ref["out"]), 1e-30)
+    assert rel.max() <= 1e-6
