@@ -255,6 +255,25 @@ int sgpu_fitseq_probe(const char *path, sgpu_fits_info *infos, int max_frames, i
 int sgpu_stack_fitseq(sgpu_ctx *ctx, const char *path, int nb_frames, const int *frame_indices, const int *shifty,
 		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
 
+/* SER files (SEQ_SER, io/ser.c): a 178-byte header, then frame_count frames of height x width samples, rows TOP-DOWN, 8-bit
+ * or 16-bit in the byte order the header names — its "LittleEndian" field read the way Siril and the first SER programs read
+ * it: 0 = little-endian data, 1 = big-endian (io/ser.h:71-80).  8-bit samples become WORDs unscaled and 16-bit ones are
+ * byte-swapped as needed (ser_manage_endianess_and_depth, ser.c:521-539); the reads are read_area_from_image's (:1054-1090).
+ * device_readable: one plane per frame (mono, or a colour filter array taken as mono — no demosaicing, no RGB / BGR). */
+typedef struct {
+	int color_id, little_endian, width, height, bit_depth, frame_count;	/* header fields as stored */
+	int byte_depth, planes;		/* 1 | 2 bytes per sample; 1 | 3 planes (ser.c:345-352) */
+	long data_offset;		/* SER_HEADER_LEN */
+	int device_readable;
+} sgpu_ser_info;
+int sgpu_ser_probe(const char *path, sgpu_ser_info *info);
+/* frame `ser_frame` of an open SER file into frame `frame` of a one-layer SGPU_U16 block: geometry as sgpu_block_upload_frame
+ * (memory order is bottom-up: the file's rows are turned over on the device) */
+int sgpu_block_upload_ser_fd(sgpu_block *blk, int frame, int fd, const sgpu_ser_info *info, int ser_frame, int row0, int shifty);
+/* sgpu_stack_fits for frames of one SER file; frame_indices NULL: 0 .. nb_frames - 1; out is WORD or float [1][height][width] */
+int sgpu_stack_ser(sgpu_ctx *ctx, const char *path, int nb_frames, const int *frame_indices, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]);
+
 /* norm_to_0_1_range (median_and_mean.c:557-582) split for row shards: min/max over non-zero
  * samples (skip_first: the reference's scan starts at index 1 — set it on the shard that holds
  * element 0), then the rescale with the globally reduced min/max. */

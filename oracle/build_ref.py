@@ -69,6 +69,9 @@ RANGES = {
     # --- statistics records of the .seq file ---
     "seq_stats_write":   ("src/io/seqfile.c", 838, 853, None),
     "seq_stats_read":    ("src/io/seqfile.c", 584, 600, None),
+    # --- SER frames ---
+    "ser_enums":         ("src/io/ser.h", 70, 85, None),
+    "ser_endian_depth":  ("src/io/ser.c", 521, 539, None),
     "reg_translation_from_H": ("src/registration/registration.c", 301, 304, None),
     # --- sum / min / max stackers (ref_simple.c) ---
     "sum_pixel_loop":    ("src/stacking/sum.c", 186, 231, None),

@@ -113,6 +113,22 @@ def write_fitseq(path, hdus, empty_primary=True):
             first = False
 
 
+def write_ser(path, frames, bit_depth, big_endian=False, color_id=0):
+    """a SER file (io/ser.c): frames [n][rows][cols] of uint8 / uint16 samples in DISPLAY order (row 0 = top row, as the
+    format stores them); the header's LittleEndian field is written the way Siril and the first SER programs use it
+    (0 = little-endian data, 1 = big-endian, io/ser.h:71-80)"""
+    import struct
+    a = np.asarray(frames)
+    n, h, w = a.shape
+    hdr = b"LUCAM-RECORDER" + struct.pack("<7i", 0, color_id, 1 if big_endian else 0, w, h, bit_depth, n)
+    hdr += b"obs".ljust(40) + b"instr".ljust(40) + b"scope".ljust(40) + struct.pack("<2q", 0, 0)
+    assert len(hdr) == 178
+    raw = a.astype(np.uint8) if bit_depth <= 8 else a.astype(">u2" if big_endian else "<u2")
+    with open(path, "wb") as f:
+        f.write(hdr)
+        f.write(raw.tobytes())
+
+
 def parse_header(path):
     """BITPIX, (w, h, c), BZERO, DATAMAX or None, data offset"""
     kv, off = {}, 0

@@ -425,6 +425,19 @@ int ref_reg_weights(int use_nbstars, int nb_layers, int N, const float *wfwhm, c
 	return rv;
 }
 
+/* ---- SER frames: the reference's own sample conversion (io/ser.c:521-539, enums io/ser.h:70-85) ---- */
+#include <endian.h>
+#define be16_to_cpu(x) be16toh(x)
+#define le16_to_cpu(x) le16toh(x)
+#include "gen/ser_enums.inc"
+struct ser_struct { ser_pixdepth byte_pixel_depth; ser_endian little_endian; };
+#include "gen/ser_endian_depth.inc"
+/* data: frame_size samples as read from the file into a WORD buffer (8-bit samples packed at its start) */
+void ref_ser_convert(int byte_depth, int little_endian_field, WORD *data, long frame_size) {
+	struct ser_struct s = { (ser_pixdepth) byte_depth, (ser_endian) little_endian_field };
+	ser_manage_endianess_and_depth(&s, data, frame_size);
+}
+
 /* ---- maximized framing: the reference's own lines of stack_open_all_files (median_and_mean.c:161-170 per frame,
  * :182-189 after the loop) around in-RAM registration data ---- */
 #include <float.h>

@@ -57,6 +57,11 @@ class OverlapStats(C.Structure):
                                                                    "scaij", "scaji")]
 
 
+class SerInfo(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("color_id", "little_endian", "width", "height", "bit_depth", "frame_count", "byte_depth",
+                                       "planes")] + [("data_offset", C.c_long), ("device_readable", C.c_int)]
+
+
 class ImageBlock(C.Structure):
     _fields_ = [("channel", C.c_long), ("start_row", C.c_long), ("end_row", C.c_long), ("height", C.c_long)]
 
@@ -105,6 +110,9 @@ SIGNATURES = {
     "sgpu_stack_fits": (C.c_int, [P, C.c_int, C.POINTER(C.c_char_p), P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_fitseq_probe": (C.c_int, [C.c_char_p, P, C.c_int, C.POINTER(C.c_int)]),
     "sgpu_stack_fitseq": (C.c_int, [P, C.c_char_p, C.c_int, P, P, C.POINTER(StackArgs), P, P, P, P]),
+    "sgpu_ser_probe": (C.c_int, [C.c_char_p, C.POINTER(SerInfo)]),
+    "sgpu_block_upload_ser_fd": (C.c_int, [P, C.c_int, C.c_int, C.POINTER(SerInfo), C.c_int, C.c_int, C.c_int]),
+    "sgpu_stack_ser": (C.c_int, [P, C.c_char_p, C.c_int, P, P, C.POINTER(StackArgs), P, P, P, P]),
     "sgpu_minmax_nonzero": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_minmax_nonzero_static": (C.c_int, [P, P, C.c_size_t, C.c_int, C.POINTER(C.c_float)]),
     "sgpu_rescale_0_1": (C.c_int, [P, P, C.c_size_t, C.c_float, C.c_float]),

@@ -65,6 +65,21 @@ __global__ void __launch_bounds__(256) fits_decode_byte_kernel(const unsigned ch
 	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += nth) dst[i] = raw[i];
 }
 
+// SER frames (io/ser.c): rows are stored top-down, samples are 8-bit or 16-bit in the byte order the header names.
+// `raw` holds `rows` whole file rows; file row k of the chunk goes to block row r_first - k (memory order is bottom-up).
+// mode 0: 8-bit -> WORD, unscaled (ser_manage_endianess_and_depth, ser.c:524-527); 1: 16-bit little-endian; 2: big-endian
+__global__ void __launch_bounds__(256) ser_decode_kernel(const unsigned char *__restrict__ raw, uint16_t *__restrict__ dst_row0,
+		int width, long rows, long r_first, int mode) {
+	const size_t n = (size_t) rows * width, nth = (size_t) gridDim.x * blockDim.x;
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += nth) {
+		const long k = (long) (i / (size_t) width); const int col = (int) (i - (size_t) k * width);
+		uint16_t v;
+		if (mode == 0) v = raw[i];
+		else { const unsigned lo = raw[2 * i], hi = raw[2 * i + 1]; v = (uint16_t) (mode == 1 ? (lo | (hi << 8)) : (hi | (lo << 8))); }
+		dst_row0[(size_t) (r_first - k) * width + col] = v;
+	}
+}
+
 // ---- staging -------------------------------------------------------------------------------------
 static int ensure_stage(sgpu_ctx *ctx) {
 	if (ctx->h_stage[0] && ctx->h_stage[1] && ctx->d_stage[0] && ctx->d_stage[1] && ctx->stage_ev[0] && ctx->stage_ev[1]) return SGPU_OK;
@@ -490,6 +505,96 @@ int sgpu_stack_fitseq(sgpu_ctx *ctx, const char *path, int nb_frames, const int 
 	if (fd < 0) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open %s", path);
 	std::vector<int> fds(nb_frames, fd);
 	const int rv = stack_fits_units(ctx, nb_frames, fds, fi, shifty, args, out, rej_low, rej_high, irej);
+	close(fd);
+	return rv;
+}
+
+/* ---- SER files (io/ser.c) ---- */
+int sgpu_ser_probe(const char *path, sgpu_ser_info *info) {
+	if (!path || !info) return SGPU_GENERIC_ERROR;
+	memset(info, 0, sizeof *info);
+	const int fd = open(path, O_RDONLY);
+	if (fd < 0) return SGPU_SEQUENCE_ERROR;
+	unsigned char h[178];
+	struct stat st;
+	const bool ok = pread(fd, h, sizeof h, 0) == (ssize_t) sizeof h && fstat(fd, &st) == 0;
+	close(fd);
+	if (!ok) return SGPU_SEQUENCE_ERROR;
+	auto le32 = [&](int off) { return (int) ((uint32_t) h[off] | ((uint32_t) h[off + 1] << 8) | ((uint32_t) h[off + 2] << 16) | ((uint32_t) h[off + 3] << 24)); };
+	info->color_id = le32(18); info->little_endian = le32(22); info->width = le32(26); info->height = le32(30);
+	info->bit_depth = le32(34); info->frame_count = le32(38);
+	info->byte_depth = info->bit_depth <= 8 ? 1 : 2;				// ser.c:345-347
+	info->planes = (info->color_id == 100 || info->color_id == 101) ? 3 : 1;	// SER_RGB / SER_BGR (:349-352)
+	info->data_offset = 178;
+	if (info->width < 1 || info->height < 1 || info->frame_count < 1 || info->bit_depth < 1 || info->bit_depth > 16) return SGPU_SEQUENCE_ERROR;
+	const long long frame = (long long) info->width * info->height * info->planes * info->byte_depth;
+	if ((long long) st.st_size < 178 + frame * info->frame_count) return SGPU_SEQUENCE_ERROR;
+	// one plane per frame read as it is (mono, or a colour filter array taken as mono: no demosaicing here)
+	info->device_readable = info->planes == 1;
+	return SGPU_OK;
+}
+
+int sgpu_block_upload_ser_fd(sgpu_block *b, int frame, int fd, const sgpu_ser_info *info, int ser_frame, int row0, int shifty) {
+	if (!b || fd < 0 || !info) return SGPU_GENERIC_ERROR;
+	sgpu_ctx *ctx = b->ctx;
+	const sgpu_block_desc &d = b->d;
+	if (frame < 0 || frame >= d.nb_frames) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d out of range", frame);
+	if (ser_frame < 0 || ser_frame >= info->frame_count) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "SER frame %d out of range", ser_frame);
+	if (!info->device_readable || d.nb_layers != 1 || d.dtype != SGPU_U16 || d.width != info->width)
+		return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "this SER file does not fit the block (one 16-bit layer, %d wide)", d.width);
+	SGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+	int rv = ensure_stage(ctx); if (rv) return rv;
+	const int H = info->height, W = info->width;
+	const size_t bpp = (size_t) info->byte_depth, rrow = (size_t) W * bpp, rowb = (size_t) W * 2;
+	long lo = (long) shifty - row0; if (lo < 0) lo = 0;		// as sgpu_block_upload_frame, in memory (bottom-up) rows
+	long hi = (long) H + shifty - row0; if (hi > d.height) hi = d.height;
+	unsigned char *dst = (unsigned char *) b->dev + ((size_t) frame * b->plane()) * 2;
+	if (hi <= lo) { SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) d.height * rowb, ctx->stream)); return SGPU_OK; }
+	if (lo > 0) SGPU_CUDA(ctx, cudaMemsetAsync(dst, 0, (size_t) lo * rowb, ctx->stream));
+	if (hi < d.height) SGPU_CUDA(ctx, cudaMemsetAsync(dst + (size_t) hi * rowb, 0, (size_t) (d.height - hi) * rowb, ctx->stream));
+	// block row r holds memory row m = row0 + r - shifty of the frame = FILE row H - 1 - m (SER rows are top-down): block rows
+	// [lo, hi) are the file rows [f0, f0 + hi - lo) read forwards and written backwards from block row hi - 1
+	const long f0 = (long) H - 1 - ((long) row0 + hi - 1 - shifty);
+	const int mode = info->byte_depth == 1 ? 0 : (info->little_endian == 1 ? 2 : 1);	// header value 1 = big-endian DATA (ser.h:71-80)
+	const off_t base = (off_t) info->data_offset + (off_t) ((size_t) H * rrow) * ser_frame + (off_t) f0 * (off_t) rrow;
+	RawSource src; src.fd = fd; src.base = base;
+	const long rows_per_chunk = (long) (SGPU_STAGE_CHUNK / rrow) > 0 ? (long) (SGPU_STAGE_CHUNK / rrow) : 1;
+	if (rrow > SGPU_STAGE_CHUNK) return sgpu_fail(ctx, SGPU_GENERIC_ERROR, "SER rows of %zu bytes exceed the staging chunk", rrow);
+	for (long done = 0; done < hi - lo; done += rows_per_chunk) {
+		const long nr = (hi - lo - done) < rows_per_chunk ? (hi - lo - done) : rows_per_chunk;
+		const size_t n = (size_t) nr * rrow;
+		const int k = ctx->stage_idx; ctx->stage_idx ^= 1;
+		SGPU_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));
+		rv = fill_from(ctx, src, (size_t) done * rrow, ctx->h_stage[k], n); if (rv) return rv;
+		SGPU_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage[k], ctx->h_stage[k], n, cudaMemcpyHostToDevice, ctx->stream));
+		size_t grid = ((size_t) nr * W + 255) / 256; const size_t cap = (size_t) ctx->sm_count * 8;
+		if (grid > cap) grid = cap;
+		ser_decode_kernel<<<(unsigned) grid, 256, 0, ctx->stream>>>((const unsigned char *) ctx->d_stage[k], (uint16_t *) dst, W, nr, hi - 1 - done, mode);
+		ctx->launches++;
+		SGPU_CUDA(ctx, cudaGetLastError());
+		SGPU_CUDA(ctx, cudaEventRecord(ctx->stage_ev[k], ctx->stream));
+	}
+	return SGPU_OK;
+}
+
+int sgpu_stack_ser(sgpu_ctx *ctx, const char *path, int nb_frames, const int *frame_indices, const int *shifty,
+		const sgpu_stack_args *args, void *out, uint16_t *rej_low, uint16_t *rej_high, uint64_t irej[6]) {
+	if (!ctx || !path || nb_frames < 1 || !out) return SGPU_GENERIC_ERROR;
+	sgpu_ser_info si;
+	if (sgpu_ser_probe(path, &si)) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot read %s as a SER file", path);
+	if (!si.device_readable) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "%s holds colour frames (ColorID %d): Siril's reader", path, si.color_id);
+	for (int f = 0; f < nb_frames; f++) {
+		const int k = frame_indices ? frame_indices[f] : f;
+		if (k < 0 || k >= si.frame_count) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "frame %d is not in the SER file (%d frames)", k, si.frame_count);
+	}
+	const int fd = open(path, O_RDONLY);
+	if (fd < 0) return sgpu_fail(ctx, SGPU_SEQUENCE_ERROR, "cannot open %s", path);
+	const sgpu_block_desc desc = { nb_frames, 1, si.width, si.height, SGPU_U16 };
+	sgpu_stack_args with_bitpix = *args;
+	with_bitpix.source_bitpix = si.byte_depth == 1 ? 8 : 16;	// stack_open_all_files: BYTE_IMG or USHORT_IMG (median_and_mean.c:220)
+	const int rv = sgpu_stack_host_impl(ctx, &desc, [&](sgpu_block *b, int f, int row0) {
+		return sgpu_block_upload_ser_fd(b, f, fd, &si, frame_indices ? frame_indices[f] : f, row0, shifty ? shifty[f] : 0);
+	}, &with_bitpix, out, rej_low, rej_high, irej);
 	close(fd);
 	return rv;
 }

@@ -77,6 +77,45 @@ def read_block_data(ctx, paths, row0=0, height=None, shifty=None, source="fd"):
     return out
 
 
+def stack_ser(args, path, frame_indices=None, is_mean=True):
+    """stack_mean_or_median for frames of a SER file (sgpu_stack_ser); results as stack_fits"""
+    from . import stacking
+    L = _lib.lib()
+    ctx = stacking._context(args)
+    si = _lib.SerInfo()
+    if L.sgpu_ser_probe(os.fsencode(path), C.byref(si)):
+        args.retval = -2
+        return -2
+    idx = list(range(si.frame_count)) if frame_indices is None else [int(i) for i in frame_indices]
+    n, c, h, w = len(idx), 1, si.height, si.width
+    keep = []
+    try:
+        ca = stacking._fill_cargs(args, n, c, is_mean, keep)
+    except _lib.SgpuError as e:
+        args.retval = e.code
+        return e.code
+    out32 = bool(args.use_32bit_output)
+    nmaps = (1 if args.merge_lowhigh_rejmaps else 2) if (is_mean and args.create_rejmaps) else 0
+    out = np.empty((c, h, w), dtype=np.float32 if out32 else np.uint16)
+    rl = np.zeros((c, h, w), dtype=np.uint16) if nmaps >= 1 else None
+    rh = np.zeros((c, h, w), dtype=np.uint16) if nmaps == 2 else None
+    irej = np.zeros(6, dtype=np.uint64)
+    sy = np.ascontiguousarray(args.shifty, dtype=np.int32) if args.shifty is not None else None
+    ia = np.ascontiguousarray(idx, dtype=np.int32)
+    rv = L.sgpu_stack_ser(ctx.h, os.fsencode(path), n, ia.ctypes.data_as(C.c_void_p),
+                          sy.ctypes.data_as(C.c_void_p) if sy is not None else None, C.byref(ca), out.ctypes.data_as(C.c_void_p),
+                          rl.ctypes.data_as(C.c_void_p) if rl is not None else None,
+                          rh.ctypes.data_as(C.c_void_p) if rh is not None else None, irej.ctypes.data_as(C.c_void_p))
+    args.retval = rv
+    if rv:
+        args.error = (L.sgpu_last_error(ctx.h) or b"").decode()
+        return rv
+    res = stacking.StackResult()
+    res.data, res.rejmap_low, res.rejmap_high, res.irej = out, rl, rh, irej.reshape(3, 2)
+    args.result = res
+    return rv
+
+
 def fitseq_probe(path):
     """the frames of a FITS sequence file (sgpu_fitseq_probe; _find_hdus, io/fits_sequence.c:39-150) as FitsInfo records"""
     L = _lib.lib()

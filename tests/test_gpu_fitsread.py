@@ -244,3 +244,68 @@ def test_stack_fitseq_file(tmp_path, orc, dtype):
     assert np.array_equal(args.result.rejmap_low, ref["rej_low"]) and np.array_equal(args.result.rejmap_high, ref["rej_high"])
     rel = np.abs(args.result.data - ref["out"]) / np.maximum(np.abs(ref["out"]), 1e-30)
     assert rel.max() <= 1e-6
+
+
+@pytest.mark.parametrize("kind", ["u8", "u16le", "u16be", "u12le"])
+def test_stack_ser_file(tmp_path, ref, kind):
+    """sgpu_stack_ser: frames of a SER file (rows top-down, 8 / 16-bit, either byte order) through the raw reader; the
+    samples the stack must see are the reference's own conversion (ser_manage_endianess_and_depth, compiled into
+    oracle/_ref) of the bytes read_area_from_image reads, turned bottom-up as Siril holds images"""
+    import ctypes as C
+    import siril_b200 as sb
+    from siril_b200 import fitsread
+    from oracle import fits_ref
+    rng = np.random.default_rng(44)
+    N, H, W = 12, 37, 90
+    depth = {"u8": 8, "u16le": 16, "u16be": 16, "u12le": 12}[kind]
+    level = 0.3 + 0.02 * rng.standard_normal((N, H, W))
+    level[rng.random(level.shape) < 0.01] += 0.4
+    disp = np.clip(np.round(level * (2 ** depth - 1)), 1, 2 ** depth - 1).astype(np.uint8 if depth == 8 else np.uint16)
+    p = str(tmp_path / "movie.ser")
+    fits_ref.write_ser(p, disp, depth, big_endian=kind == "u16be")
+    si = sb._lib.SerInfo()
+    assert sb._lib.lib().sgpu_ser_probe(p.encode(), C.byref(si)) == 0
+    assert (si.width, si.height, si.frame_count, si.byte_depth, si.planes, si.device_readable) == (W, H, N, 1 if depth == 8 else 2, 1, 1)
+    # the reference's view of the file: raw bytes of every frame -> WORDs by its own conversion, then bottom-up
+    raw = open(p, "rb").read()[178:]
+    bpp = si.byte_depth
+    frames = np.zeros((N, 1, H, W), dtype=np.uint16)
+    R = ref.lib
+    R.ref_ser_convert.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_long]
+    for f in range(N):
+        buf = np.zeros(H * W, dtype=np.uint16)
+        chunk = np.frombuffer(raw, dtype=np.uint8, count=H * W * bpp, offset=f * H * W * bpp)
+        buf.view(np.uint8)[: chunk.size] = chunk
+        R.ref_ser_convert(bpp, si.little_endian, buf.ctypes.data, H * W)
+        frames[f, 0] = buf.reshape(H, W)[::-1]
+    assert np.array_equal(frames[:, 0, ::-1], disp.astype(np.uint16))
+    idx = [0, 1, 2, 4, 5, 6, 8, 9, 10, 11]
+    sy = rng.integers(-3, 4, len(idx)).astype(np.int32)
+    for out32 in (True, False):
+        args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=None, type_of_rejection=sb.WINSORIZED,
+                               sig=(3.0, 3.0), create_rejmaps=True, shifty=sy, use_32bit_output=out32)
+        assert fitsread.stack_ser(args, p, frame_indices=idx) == 0, getattr(args, "error", "")
+        o = ref.stack(frames[idx], rejection=sb.WINSORIZED, sig=(3.0, 3.0), create_rejmaps=True, shifty=sy, use_32bit_output=out32,
+                      source_bitpix=8 if depth == 8 else 16)
+        assert np.array_equal(args.result.irej, o["irej"])
+        assert np.array_equal(args.result.rejmap_low, o["rej_low"]) and np.array_equal(args.result.rejmap_high, o["rej_high"])
+        if out32:
+            rel = np.abs(args.result.data - o["out"]) / np.maximum(np.abs(o["out"]), 1e-30)
+            assert rel.max() <= 1e-6
+        else:
+            assert np.array_equal(args.result.data, o["out"])
+
+
+def test_ser_probe_rejects_colour_and_truncated(tmp_path):
+    import ctypes as C
+    import siril_b200 as sb
+    from oracle import fits_ref
+    L = sb._lib.lib()
+    si = sb._lib.SerInfo()
+    p = str(tmp_path / "rgb.ser")
+    fits_ref.write_ser(p, np.zeros((2, 4, 12), dtype=np.uint8), 8, color_id=100)      # RGB: 3 planes, the file is too short for that
+    assert L.sgpu_ser_probe(p.encode(), C.byref(si)) == -2
+    q = str(tmp_path / "bayer.ser")
+    fits_ref.write_ser(q, np.ones((2, 4, 12), dtype=np.uint8), 8, color_id=8)         # a colour filter array: read as mono
+    assert L.sgpu_ser_probe(q.encode(), C.byref(si)) == 0 and si.device_readable == 1
+    assert L.sgpu_ser_probe(str(tmp_path / "none.ser").encode(), C.byref(si)) == -2
