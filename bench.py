@@ -519,7 +519,10 @@ def run_ours(args, wl):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
             "dtype": dt, "data": "synthetic",
             "config": config_of(args, wl, world),
-            "detail": {"rows_on_rank0": h, "stats_ms": stats_ms, "handed_to_exact_engine_px": int(handed[0])},
+            "detail": {"rows_on_rank0": h, "stats_ms": stats_ms, "handed_to_exact_engine_px": int(handed[0]),
+                       # the second headline: normalization statistics + coefficients + stack, for workloads that normalize
+                       "normalize_plus_stack_ms": (stats_ms + ms_per_step) if stats_ms is not None else None,
+                       "px_frames_per_s_with_normalization": (units / ((stats_ms + ms_per_step) * 1e-3)) if stats_ms is not None else None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": kernel_name, "kernel_ms": kernel_ms_max,
                          "algorithmic_bytes": B, "frac_of_8TBs_nominal": achieved / 8000.0,
