@@ -84,8 +84,31 @@ struct PselLane {
 	}
 
 	__device__ __forceinline__ void sums(int is_mean, int *n, double *S1, double *S2, float *mn, float *mx) {
-		double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
 		float lo = SGPU_INF, hi = -SGPU_INF;
+		if (!is_mean) {
+			// median stack: no sample is dropped and the sums only PLACE the windows (no result depends on them), so float
+			// accumulators do: FADD + FFMA per sample instead of F2F.F64 + DADD + DFMA, the first of which runs on the
+			// conversion pipe at an eighth of the rate and bounds this pass in mean mode
+			float a1 = 0.f, a2 = 0.f, b1 = 0.f, b2 = 0.f;
+			if (coef) {
+				each([&](int k, float x, int row, unsigned a) {
+					const double2 c = coef[row];
+					x = norm_mode == 1 ? normalize_sample<float, 1>(x, c.x, c.y) : normalize_sample<float, 2>(x, c.x, c.y);
+					sts_f32(a, x);
+					if (k & 1) { b1 += x; b2 = fmaf(x, x, b2); } else { a1 += x; a2 = fmaf(x, x, a2); }
+					lo = fminf(lo, x); hi = fmaxf(hi, x);
+				});
+			} else {
+				each([&](int k, float x, int, unsigned) {
+					if (k & 1) { b1 += x; b2 = fmaf(x, x, b2); } else { a1 += x; a2 = fmaf(x, x, a2); }
+					lo = fminf(lo, x); hi = fmaxf(hi, x);
+				});
+			}
+			*S1 = (double) gsum(a1 + b1); *S2 = (double) gsum(a2 + b2);
+			*n = N; *mn = gmin(lo); *mx = gmax(hi);
+			return;
+		}
+		double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
 		if (coef) {	// raw samples in the tile: normalize (median_and_mean.c:1644-1686) and park the result
 			each([&](int k, float x, int row, unsigned a) {
 				const double2 c = coef[row];
