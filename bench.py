@@ -66,7 +66,7 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.i0 = index, [], None, 0
 
     def start(self):
         try:
@@ -76,6 +76,10 @@ class ClockSampler:
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
+
+    def mark(self):
+        """the timed region starts here: only what is sampled from now on counts"""
+        self.i0 = len(self.rows)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -89,7 +93,7 @@ class ClockSampler:
             except Exception:
                 pass
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for r in (self.rows[self.i0:] or self.rows[-1:]):   # (a region shorter than one sampling period: the sample before it)
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
@@ -406,18 +410,19 @@ def run_ours(args, wl):
         if world > 1:
             gather()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()     # (nvidia-smi takes a moment to come up: started before the warm-up, counted from the timed region on)
     for _ in range(args.warmup):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     launches0 = ctx.launches
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     kev = []
     torch.cuda.synchronize()
+    sampler.mark()
     ev[0].record(stream)
     for i in range(args.steps):
         k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
