@@ -104,6 +104,166 @@ __device__ __forceinline__ int lsort_pixel(int r, int g) {
 	return r * (32 >> LT) + g;					// 2 or 1 px / round
 }
 
+
+// ---- GESDT with the lanes of a small group (sorted.cuh: fast_gesdt is the one-thread form and says what is computed) ----
+// Only the DECISION of an iteration — which end of the window goes — is serial, and it needs no more than the window's sum:
+// one thread per pixel walks it (gesdt_decide; every lane of the warp busy) and leaves one bit per iteration in shared
+// memory.  The Grubbs tests of all iterations are then evaluated side by side by GL lanes per pixel (coop_gesdt): every
+// lane takes a contiguous chunk of iterations, sums what its chunk removes, an exclusive scan over the lanes gives each the
+// sums its chunk starts from, and it replays the tests of its chunk from there.  The last iteration that certainly beat its
+// critical value (and the last too close to call) is a maximum over the lanes; lane 0 then collects what the reference
+// keeps up to that iteration.  The one-thread form is a chain of ~100 dependent instructions per iteration walked by one
+// warp per CTA; here the serial part is a chain of a dozen.
+#define SGPU_GESDT_COOP_MAX 128
+#define SGPU_GESDT_WORDS (SGPU_GESDT_COOP_MAX / 32 + 1)	// per pixel in shared memory: the decision bits, then a flag (the float mean sat on a rounding boundary)
+template <bool U16>
+__device__ __forceinline__ bool gesdt_exact_sums(const SubStack &s, int n) { return U16 || (s(0) > 0.f && s(n - 1) <= s(0) * 65536.f && n <= 2048); }
+
+// word w of the pixel goes to out[w * stride]
+template <bool U16>
+__device__ __forceinline__ void gesdt_decide(const SubStack &s, int n, int max_out, const RejCfg &c, const Sums &S, unsigned *out, int stride) {
+	const bool exact_sums = gesdt_exact_sums<U16>(s, n);
+	int fail = 0;
+	double a = S.S1 + (double) n * S.K;	// the window's sum; its roundings are far inside the room `tiny` leaves
+	int lo = 0, size = n;
+#pragma unroll
+	for (int w = 0; w < SGPU_GESDT_COOP_MAX / 32; w++) {
+		unsigned word = 0;
+		const int lim = min(32, max_out - 32 * w);
+		for (int j = 0; j < lim; j++, size--) {
+			const float xl = s(lo), xh = s(lo + size - 1);
+			const double r0 = rcp_t(c.rcp, size), b = (double) size, al = a - (double) xl, ah = a - (double) xh;
+			double avg_d = a * r0;
+			avg_d = fma(fma(-avg_d, b, a), r0, avg_d);
+			const float avg = (float) avg_d;
+			if (!exact_sums) {
+				const double tiny = fabs(avg_d) * 1e-12;
+				if ((float) (avg_d + tiny) != avg || (float) (avg_d - tiny) != avg) fail = 1;
+			}
+			const bool low_end = !(xh - avg > avg - xl);
+			word |= (unsigned) low_end << j;
+			lo += low_end;
+			a = low_end ? al : ah;
+		}
+		out[w * stride] = word;
+	}
+	out[(SGPU_GESDT_COOP_MAX / 32) * stride] = (unsigned) fail;
+}
+
+// `active` false: the lane only takes part in the shuffles
+template <bool U16, int GL>
+__device__ __forceinline__ void coop_gesdt(const SubStack &s, int n, int removed, int max_out, const RejCfg &c, const Sums &S, int q, bool active,
+		const unsigned *dec, int stride, int rej[2], FastRes &o) {
+	o.status = FAST_FALLBACK;
+	double median = 0.0;
+	unsigned bits[SGPU_GESDT_COOP_MAX / 32] = { 0, 0, 0, 0 };	// (every index below is a compile-time one: the words stay in registers)
+	int fail = 0;
+	if (active) {
+		if (n & 1) median = (double) s(n / 2);
+		else if (U16) median = ((double) s((n - 1) / 2) + (double) s(n / 2)) / 2.0;
+		else median = (s((n - 1) / 2) + s(n / 2)) / 2.0;
+		if (U16) median = (double) (float) median;
+#pragma unroll
+		for (int w = 0; w < SGPU_GESDT_COOP_MAX / 32; w++) bits[w] = dec[w * stride];
+		fail = (int) dec[(SGPU_GESDT_COOP_MAX / 32) * stride];
+	}
+	const double K = S.K;
+	auto bit = [&](int it) {
+		const unsigned w01 = it < 32 ? bits[0] : bits[1], w23 = it < 96 ? bits[2] : bits[3];
+		return ((it < 64 ? w01 : w23) >> (it & 31)) & 1u;
+	};
+	auto lows_before = [&](int it) {	// low-end removals among iterations [0, it)
+		int k = 0;
+#pragma unroll
+		for (int w = 0; w < SGPU_GESDT_COOP_MAX / 32; w++) {
+			const int left = it - 32 * w;
+			if (left > 0) k += __popc(left >= 32 ? bits[w] : (bits[w] & ((1u << left) - 1u)));
+		}
+		return k;
+	};
+	// ---- the tests, a chunk of iterations per lane ----
+	const int ch = (max_out + GL - 1) / GL;
+	const int it0 = active ? min(q * ch, max_out) : 0, it1 = active ? min(it0 + ch, max_out) : 0;
+	double A1 = 0.0, A2 = 0.0;
+	{
+		int lo = lows_before(it0);
+		for (int it = it0; it < it1; it++) {
+			const bool low = bit(it);
+			const float xrem = low ? s(lo) : s(n - 1 - (it - lo));
+			lo += low;
+			const double y = (double) xrem - K;
+			A1 += y; A2 = fma(y, y, A2);
+		}
+	}
+	double P1 = A1, P2 = A2;	// inclusive scan over the group's lanes, then made exclusive
+#pragma unroll
+	for (int d = 1; d < GL; d <<= 1) {
+		const double u1 = __shfl_up_sync(0xffffffffu, P1, d, GL), u2 = __shfl_up_sync(0xffffffffu, P2, d, GL);
+		if (q >= d) { P1 += u1; P2 += u2; }
+	}
+	double S1 = S.S1 - (P1 - A1), S2 = S.S2 - (P2 - A2);
+	int last = -1, amb = -1;
+	bool bad = false;
+	{
+		int lo = lows_before(it0);
+		for (int it = it0; it < it1; it++) {
+			const int size = n - it;
+			const bool low = bit(it);
+			const float xrem = low ? s(lo) : s(n - 1 - (it - lo));
+			if (it > 1) {
+				const double r0 = rcp_t(c.rcp, size), r1 = rcp_t(c.rcp, size - 1), b = (double) size, a = S1 + b * K;
+				double avg_d = a * r0;
+				avg_d = fma(fma(-avg_d, b, a), r0, avg_d);
+				const float avg = (float) avg_d;
+				const float dev = low ? avg - xrem : xrem - avg;
+				const double var = (S2 - S1 * S1 * r0) * r1;
+				if (!(var >= 0.0)) { bad = true; break; }
+				const double e = fabs(avg_d) * 5.9604645e-08;
+				const double var_hi = var + e * e * 2.0;
+				const double cr = (double) c.crit[it + removed], d2 = (double) dev * (double) dev, c2 = cr * cr;
+				const bool normal = var > 1e-30 && var_hi < 1e30;
+				// (the sums of a chunk come from a scan, not from the serial down-dating: their last bits differ, which the
+				// room left around the float path's roundings covers many times over)
+				if (normal && d2 > c2 * var_hi * (1.0 + 4.0e-6)) last = it;
+				else if (!normal || !(d2 < c2 * var * (1.0 - 4.0e-6))) {
+					float slo, shi;
+					if (!sd_interval(var, avg_d, size, SGPU_DELTA_SD, 1.f, &slo, &shi)) { bad = true; break; }
+					const float crf = c.crit[it + removed];
+					if (dev / shi > crf) last = it;
+					else if (dev / slo > crf) amb = it;
+				}
+			}
+			lo += low;
+			const double y = (double) xrem - K;
+			S1 -= y; S2 = fma(-y, y, S2);
+		}
+	}
+#pragma unroll
+	for (int d = 1; d < GL; d <<= 1) {
+		last = max(last, __shfl_xor_sync(0xffffffffu, last, d, GL));
+		amb = max(amb, __shfl_xor_sync(0xffffffffu, amb, d, GL));
+		bad = __shfl_xor_sync(0xffffffffu, (int) bad, d, GL) || bad;
+	}
+	if (!active || q != 0 || fail || bad) return;
+	last = max(last, min(1, max_out - 1));	// iterations 0 and 1 are always taken (confirm_outliers never keeps fewer than two)
+	if (amb > last) return;
+	// ---- what the reference keeps up to iteration `last` (lane 0) ----
+	int lo = 0, clo = 0, chi = 0, first_low = -1;
+	double fsum = 0.0;
+	for (int it = 0; it <= last; it++) {
+		const bool low = bit(it);
+		const float xrem = low ? s(lo) : s(n - 1 - (it - lo));
+		const float xflag = low ? xrem : s(n - 1 - it);	// a high-end removal flags index size - 1 of the SHRUNK window in the original stack
+		if (low) { if (first_low < 0) first_low = it; lo++; }
+		if ((double) xrem >= median) chi++; else clo++;
+		fsum += (double) xflag;
+	}
+	rej[0] += clo; rej[1] += chi;
+	o.status = FAST_DONE; o.kept = n - (last + 1); o.sum = S.sum(n) - fsum;
+	o.pmin = s(lo);
+	o.pmax = (first_low >= 0) ? s(n - 1 - first_low) : s(n - last - 2);
+}
+
 template <int LT, int RE, int RS, int RF, int SUB, int NW>
 __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) / (NW * 32)) stack_lsort_kernel(const StackParams p, const __grid_constant__ CUtensorMap tmap) {
 	constexpr int T = 1 << LT, Q = 32 >> LT, PXC = SUB * TILE_PX;
@@ -226,6 +386,74 @@ __global__ void __launch_bounds__(NW * 32, (RE <= 24 && RE >= 20 ? 1024 : 768) /
 		for (int i = threadIdx.x; i < ((N + 7) & ~7); i += NW * 32) xf[i] = 1.f / (float) (i + 1);
 		rc.xf = xf;
 		__syncthreads();
+	}
+	// ---- GESDT: GL lanes per pixel (coop_gesdt); the pixels it does not take (too few samples, budgets that could
+	// collide, very deep budgets) go through the one-thread code below, by the group's first lane ----
+	constexpr int GL = 4;
+	if (p.is_mean && rc.type == SGPU_GESDT && NW * 32 >= GL * PXC) {
+		if ((int) threadIdx.x >= GL * PXC) return;
+		unsigned *dec = (unsigned *) (coef + N);	// [SGPU_GESDT_WORDS][PXC]
+		if ((int) threadIdx.x < PXC) {	// the decisions: thread i = pixel i
+			const int pd = (int) threadIdx.x, nd = cnt[pd];
+			int mo = (int) ((float) N * rc.s0);
+			const int rem = N - nd;
+			const bool ok = pix0 + pd < npix && !bad[pd] && nd >= 2 && rem < mo;
+			mo -= rem;
+			if (ok && !(2 * mo >= nd || nd - mo < 3) && mo >= 1 && mo <= SGPU_GESDT_COOP_MAX) {
+				SubStack sd(rows + (pd >> 5) * sub_floats, pd & 31);
+				if (p.is_u16) gesdt_decide<true>(sd, nd, mo, rc, sums[pd], dec + pd, PXC);
+				else gesdt_decide<false>(sd, nd, mo, rc, sums[pd], dec + pd, PXC);
+			}
+		}
+		asm volatile("bar.sync 1, %0;" :: "r"(GL * PXC) : "memory");	// (the warps past GL * PXC have left)
+		const int pxi = (int) threadIdx.x / GL, q = (int) threadIdx.x % GL, sbq = pxi >> 5;
+		const size_t pixq = pix0 + pxi;
+		const bool valid = pixq < npix;
+		SubStack st(rows + sbq * sub_floats, pxi & 31);
+		const int n = cnt[pxi];
+		int status = (valid && !bad[pxi]) ? FAST_DONE : FAST_FALLBACK;
+		int max_out = (int) ((float) N * rc.s0);
+		const int removed = N - n;
+		const bool budget = status == FAST_DONE && n >= 2 && removed < max_out;
+		max_out -= removed;
+		const bool main_case = budget && !(2 * max_out >= n || n - max_out < 3) && max_out >= 1 && max_out <= SGPU_GESDT_COOP_MAX;
+		int rejq[2] = { 0, 0 };
+		FastRes o; o.status = FAST_FALLBACK; o.kept = 0; o.sum = 0.0; o.pmin = o.pmax = 0.f;
+		const Sums Sq = sums[pxi];
+		if (p.is_u16) coop_gesdt<true, GL>(st, n, removed, max_out, rc, Sq, q, main_case, dec + pxi, PXC, rejq, o);
+		else coop_gesdt<false, GL>(st, n, removed, max_out, rc, Sq, q, main_case, dec + pxi, PXC, rejq, o);
+		if (q == 0 && valid) {
+			const int x = (int) (pixq % p.W);
+			const double *fw = p.weights ? p.weights + (size_t) layer * N : nullptr;
+			const PixWeights w = { fw, p.mask ? p.mask + pixq : nullptr, nullptr, npix, 0, p.shiftx };
+			double result = 0.0;
+			if (status == FAST_DONE && main_case) {
+				status = (o.status == FAST_DONE && o.kept > 0) ? FAST_DONE : FAST_FALLBACK;
+				if (status == FAST_DONE) {
+					if (p.is_u16) { auto orig = [&](int ff) { return (float) load_norm<u16>(p, ff, layer, pixq, x); }; result = fast_combine(o, N, w, orig); }
+					else { auto orig = [&](int ff) { return load_norm<float>(p, ff, layer, pixq, x); }; result = fast_combine(o, N, w, orig); }
+				}
+			} else if (status == FAST_DONE) {	// the cases the group does not take: the one-thread code
+				const Sums *S0 = n > 0 ? &sums[pxi] : nullptr;
+				if (p.is_u16) { auto orig = [&](int ff) { return (float) load_norm<u16>(p, ff, layer, pixq, x); }; result = fast_mean_and_reject<true>(st, n, N, rc, w, orig, S0, rejq, &status); }
+				else { auto orig = [&](int ff) { return load_norm<float>(p, ff, layer, pixq, x); }; result = fast_mean_and_reject<false>(st, n, N, rc, w, orig, S0, rejq, &status); }
+			}
+			if (status == FAST_DONE) {
+				if (p.is_u16) store_result<u16>(p, (size_t) layer * p.out_plane + pixq, result, rejq);
+				else store_result<float>(p, (size_t) layer * p.out_plane + pixq, result, rejq);
+			} else {
+				rejq[0] = rejq[1] = 0;
+				p.list[atomicAdd(p.list_count, 1u)] = ((unsigned) layer << 30) | (unsigned) pixq;
+			}
+		} else { rejq[0] = rejq[1] = 0; }
+		__syncwarp();
+		unsigned lo = rejq[0], hi = rejq[1];
+		lo = __reduce_add_sync(0xffffffffu, lo); hi = __reduce_add_sync(0xffffffffu, hi);
+		if (lane == 0 && (lo | hi)) {
+			atomicAdd(&p.irej[layer * 2], (unsigned long long) lo);
+			atomicAdd(&p.irej[layer * 2 + 1], (unsigned long long) hi);
+		}
+		return;
 	}
 	if (threadIdx.x >= PXC) return;
 
