@@ -79,7 +79,7 @@ int sgpu_launch_lsort(sgpu_ctx *ctx, sgpu_block *blk, const sgpu_stack_args *a, 
 		else { p.tile_rows = d.nb_frames; p.box_rows = d.nb_frames; }
 	}
 	const int pxc = var->sub * TILE_PX;
-	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * ((p.tile_rows + 7) & ~7) * sizeof(float) + (size_t) pxc * (sizeof(Sums) + 2 * sizeof(int)) + 16 + (size_t) d.nb_frames * 16 + (size_t) pxc * SGPU_GESDT_WORDS * sizeof(unsigned);	// (the last term: coop_gesdt's decision bits)
+	const size_t shm = 1024 + (size_t) var->sub * TILE_PX * ((p.tile_rows + 7) & ~7) * sizeof(float) + (size_t) pxc * (sizeof(Sums) + 2 * sizeof(int)) + 16 + (size_t) d.nb_frames * 16 + (a->is_mean && a->type_of_rejection == SGPU_GESDT ? (size_t) pxc * SGPU_GESDT_WORDS * sizeof(unsigned) : 0);	// (the last term: coop_gesdt's decision bits)
 	if (shm > ctx->smem_optin) return sgpu_fail(ctx, SGPU_ALLOC_ERROR, "stack too deep for the lane-sort engine");
 	dim3 grid((unsigned) ((npix + pxc - 1) / pxc), (unsigned) d.nb_layers);
 	rv = var->launch(ctx, p, p.use_tma ? &tmap : nullptr, grid, shm);
