@@ -281,3 +281,35 @@ def test_gesdt_outlier_budget_is_a_float_product(orc, N, s0):
     args = sb.StackingArgs(method=sb.stack_mean_with_rejection, frames=to_dev(fr), type_of_rejection=O.GESDT, sig=(s0, 0.05),
                            critical_value=crit[:-1], engine=ENGINE)
     assert sb.main_stack(args) == sb.ST_GENERIC_ERROR and "critical values" in args.error
+
+
+@pytest.mark.parametrize("case", [
+    # N, dtype, sig0, zeros, what
+    (450, np.float32, 0.3, 0.001, "budget past the 128 removals the lane groups take: one-thread code"),
+    (300, np.float32, 0.3, 0.06, "many nulls: every pixel its own budget"),
+    (64, np.uint16, 0.3, 0.03, "16-bit samples, nulls"),
+    (12, np.float32, 0.3, 0.3, "budget spent on the nulls, stacks of one and two samples"),
+    (33, np.float32, 0.47, 0.0, "flagged positions could collide: exact engine"),
+    (200, np.float32, 0.3, 0.002, "frame weights"),
+    (100, np.float32, 0.3, 0.002, "samples of both signs: the sums are not exact"),
+    (128, np.float32, 0.3, 0.0, "a full 32-bit word of decisions and some"),
+    (428, np.uint16, 0.3, 0.0, "128 removals exactly"),
+], ids=lambda c: f"{c[0]}-{np.dtype(c[1]).name}-{c[2]}-{c[3]}")
+def test_gesdt_lane_groups(orc, case):
+    """GESDT in the lane-sort engine (stack_lsort.cuh: gesdt_decide / coop_gesdt): the decisions of one thread per pixel and the
+    Grubbs tests of four lanes per pixel against rejection_float.c:301-348 + confirm_outliers, at the edges of what the
+    groups take.  The image is not a multiple of the tile, so the last CTA has lanes without a pixel."""
+    N, dtype, s0, zeros, what = case
+    rng = np.random.default_rng(7 * N + 1)
+    fr = synth(rng, N, 1, 5, 75, dtype, zeros=zeros, hot=0.03)
+    kw = dict(rejection=O.GESDT, sig=(s0, 0.05), create_rejmaps=True)
+    if "weights" in what:
+        kw["weights"] = rng.uniform(0.5, 1.5, (1, N))
+    if "both signs" in what:
+        kw.update(normalize=O.ADDITIVE, scale=np.ones((1, N)), mul=np.ones((1, N)),
+                  offset=0.12 + 0.002 * rng.standard_normal((1, N)))
+    g = run_gpu(fr, **dict(kw))
+    o = orc.stack(fr, **kw)
+    compare(g, o, what)
+    if s0 < 0.4 and zeros < 0.1:
+        assert g["irej"][0].sum() > 0, what
